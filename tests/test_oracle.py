@@ -1,0 +1,157 @@
+"""Pin the CPU oracle (oracle/logmodel_oracle.py) to the reference's own outputs.
+
+The golden vectors in tests/golden/*.npz were produced by the unmodified reference
+(tests/golden/make_golden.py).  No GPU needed.
+"""
+import numpy as np
+import pytest
+
+from oracle import logmodel_oracle as orc
+
+
+def rel(a, b):
+    return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.mark.parametrize("its", [1, 2, 3, 5, 50])
+def test_two_pass_iterates_match_reference(golden, its):
+    g = golden("solver_n100")
+    w, info = orc.solve_two_pass(g["z"] * g["theta"], maxit=its, threshold=False)
+    assert info.n_iter == its
+    assert rel(orc.to_square(w), g[f"w_raw_it{its}"]) < 1e-14
+
+
+def test_two_pass_converged_matches_reference(golden):
+    g = golden("solver_n100")
+    w, info = orc.solve_two_pass(g["z"] * g["theta"])
+    assert info.converged and 1 < info.n_iter < 1000
+    ref = g["w_final"]
+    assert rel(orc.to_square(w), ref) < 1e-13
+    assert np.array_equal(orc.to_square(w) > 0, ref > 0)
+
+
+def test_one_pass_equals_two_pass(golden):
+    """The single-sweep schedule the CUDA kernels use is the same iteration."""
+    g = golden("solver_n100")
+    z = g["z"] * g["theta"]
+    for its in (1, 2, 5, 50):
+        w1, _ = orc.solve_one_pass(z, maxit=its, threshold=False)
+        assert rel(orc.to_square(w1), g[f"w_raw_it{its}"]) < 1e-13
+    w1, i1 = orc.solve_one_pass(z)
+    w2, i2 = orc.solve_two_pass(z)
+    assert i1.n_iter == i2.n_iter
+    assert rel(w1, w2) < 1e-12
+    assert rel(orc.to_square(w1), g["w_final"]) < 1e-12
+
+
+def test_alt_parameters_and_warm_start(golden):
+    g = golden("solver_n100")
+    z = g["z"] * g["theta"]
+    for solve in (orc.solve_two_pass, orc.solve_one_pass):
+        w, _ = solve(z, 0.7, 1.9, maxit=400, tol=1e-6, step_size=0.8, edge_tol=1e-4)
+        assert rel(orc.to_square(w), g["w_alt"]) < 1e-12
+        w, _ = solve(z, edge_init=g["edge_init"].copy(), maxit=30)
+        assert rel(orc.to_square(w), g["w_warm"]) < 1e-12
+
+
+def test_batched_shared_stop(golden):
+    g = golden("batched_n30")
+    z = g["z"] * g["theta"]
+    for solve in (orc.solve_two_pass, orc.solve_one_pass):
+        for its in (1, 2, 7, 40):
+            w, _ = solve(z, maxit=its, threshold=False)
+            assert rel(w, g[f"w_raw_it{its}"]) < 1e-13
+        w, info = solve(z)
+        assert rel(w, g["w"]) < 1e-12
+        w, _ = solve(z, edge_init=g["edge_init"].copy(), maxit=25)
+        assert rel(w, g["w_warm"]) < 1e-12
+    # the batch is NOT K independent solves (spectral norm + one stop for all graphs)
+    assert rel(g["w"], g["w_single"]) > 1e-7
+
+
+def test_ndim_error():
+    with pytest.raises(ValueError, match="vector or matrix"):
+        orc.solve_two_pass(np.zeros((2, 2, 3)))
+    with pytest.raises(ValueError, match="vector or matrix"):
+        orc.solve_one_pass(np.zeros((2, 2, 3)))
+
+
+def test_theta(golden):
+    g = golden("theta_n40")
+    with np.errstate(divide="ignore", invalid="ignore"):
+        got = np.array([orc.theta_for_degree(g["zsq"], int(k)) for k in g["ks"]])
+    assert np.isinf(got[0]) and np.isinf(g["thetas"][0])  # avg_degree=1 quirk (zero diagonal)
+    np.testing.assert_allclose(got[1:], g["thetas"][1:], rtol=1e-14)
+    np.testing.assert_allclose(orc.theta_for_degree(g["zsq"], 3, blocks=g["blocks"]), g["theta_blocks"], rtol=1e-14)
+    deg = {(0, 0): 2, (0, 1): 3, (0, 2): 2, (1, 1): 4, (1, 2): 2, (2, 2): 3}
+    np.testing.assert_allclose(
+        orc.theta_for_degree(g["zsq"], deg, blocks=g["blocks"]), g["theta_blocks_dict"], rtol=1e-14
+    )
+
+
+def test_pdist_and_logmodel_fit(golden):
+    for tag in ("n60", "n33"):
+        g = golden(f"logmodel_{tag}")
+        z = orc.pdist_sq(g["x"])
+        assert rel(z, g["pdist_sq"]) < 1e-14
+        theta = orc.theta_for_degree(orc.to_square(z), int(g["avg_degree"]))
+        assert abs(theta - float(g["theta"])) < 1e-13 * abs(theta)
+        w, _ = orc.solve_one_pass(z * theta)
+        assert rel(orc.to_square(w), g["weights"]) < 1e-11
+        w, _ = orc.solve_one_pass(z, maxit=40)
+        assert rel(orc.to_square(w), g["weights_none"]) < 1e-11
+
+
+def test_operator_pair(golden):
+    g = golden("operators_n23")
+    n = 23
+    s, st = orc.sum_operator(n)
+    assert np.array_equal(s.toarray(), g["s_dense"])
+    np.testing.assert_allclose(s @ g["w"].T, g["s_w"], rtol=1e-13, atol=1e-13)
+    np.testing.assert_allclose(st @ g["dn"], g["st_d"], rtol=1e-13, atol=1e-13)
+    np.testing.assert_allclose(orc.laplacian_from_packed(g["w"]), g["lap_vec"], atol=1e-13)
+    np.testing.assert_allclose(orc.laplacian_from_packed(g["w"][0]), g["lap_single"], atol=1e-13)
+    np.testing.assert_allclose(orc.laplacian_adjoint(g["dual"]), g["adj_vec"], atol=1e-13)
+    np.testing.assert_allclose(orc.laplacian_adjoint(g["dual"][0]), g["adj_single"], atol=1e-13)
+    np.testing.assert_array_equal(orc.to_packed(g["dual"]), g["sq2vec"])
+    # exact facts used by the design: ||S||_2^2 = 2(n-1), S S^T = (n-2) I + 1 1^T
+    sst = (s @ st).toarray()
+    assert np.array_equal(sst, (n - 2) * np.eye(n) + np.ones((n, n)))
+
+
+def test_adjoint_identity_property():
+    """<L, Lap(w)> == <w, Lap*(L)>, the reference's own operator test
+    (tests/test_operators.py:44-72), on the oracle's forms."""
+    for seed in range(50):
+        rng = np.random.default_rng(seed)
+        n = int(rng.integers(20, 100))
+        k = int(rng.integers(1, 10))
+        w = rng.standard_normal((k, n * (n - 1) // 2))
+        dual = rng.standard_normal((k, n, n))
+        lhs = np.sum(dual * orc.laplacian_from_packed(w))
+        rhs = np.sum(w * orc.laplacian_adjoint(dual))
+        assert np.isclose(lhs, rhs)
+
+
+def test_knn_complete_support_equals_dense(golden):
+    """Config 5 has no reference code; with the complete edge list the kNN restatement must
+    reproduce the dense solver (same gamma because d_max = n-1)."""
+    g = golden("batched_n30")
+    z = g["z"][0] * g["theta"][0, 0]
+    n = 30
+    ei, ej = orc.edge_index(n)
+    wk, ik = orc.solve_knn(ei, ej, z, n)
+    wd, idn = orc.solve_one_pass(z)
+    assert ik.n_iter == idn.n_iter
+    assert rel(wk, wd) < 1e-13
+
+
+def test_knn_support_symmetric():
+    rng = np.random.default_rng(0)
+    pts = rng.standard_normal((50, 3))
+    zsq = ((pts[:, None] - pts[None]) ** 2).sum(-1)
+    ei, ej = orc.knn_support(zsq, 4)
+    assert np.all(ei < ej)
+    deg = np.bincount(ei, minlength=50) + np.bincount(ej, minlength=50)
+    assert deg.min() >= 4
+    assert np.all(np.diff(ei * 50 + ej) > 0)
