@@ -1,0 +1,364 @@
+// edge_pass.cu -- K3: the fused per-iteration sweep over the tiled edge vector.
+//
+// Replaces the edge-sized work of the reference loop body, graph_learn/smooth_learning.py:147-164,
+// together with all four applications of the sum operator S / S^T (smooth_learning.py:13-44):
+//
+//   y  = (1-2 gamma beta) w - gamma (d_i + d_j)        :147   (S^T d is a gather of two node values)
+//   p  = max(0, y - 2 gamma z)                         :150
+//   q  = (1-2 gamma beta) p - gamma (pb_i + pb_j)      :153   (pb = dual prox output, known up front)
+//   w' = w - y + q                                     :163
+//   S p, S w'   accumulated per node                   :154, next iteration's :148
+//   ||q - y||^2, ||w'||^2                              :158 (numerator; next iteration's denominator)
+//
+// One CTA owns one 128x128 tile (I,J) of the node-pair triangle: 8 warps x 16 rows, each lane
+// owns 4 columns (one 16-byte vector per row for fp32, two for fp64).  Column partial sums live
+// in registers for the whole tile, row partial sums are reduced across the warp with a
+// reduce-scatter butterfly (31 shuffles per 16 rows x 2 quantities), and each tile issues exactly
+// one float64 atomic per (node, quantity): 2 x 128 row atomics + 2 x 128 column atomics.
+// Algorithmic traffic: read w, read z, write w = 12 B/edge fp32, 24 B/edge fp64.
+#include "solver.cuh"
+
+namespace gl {
+
+template <typename F> struct EdgeArgs {
+  F *w;
+  const F *z;
+  F *r;  // batch mode: q - y
+  int64_t gstride;
+  const F *a, *b;          // gamma*d, gamma*pb   [K][npad]
+  double *sp, *sw;         // degree accumulators [K][npad]
+  double *cta_partial;     // [ntl][2]
+  double *gsum;            // xch: G_r, G_w (K == 1: two scalars)
+  const int2 *tile_ij;
+  int *flags;
+  int n, npad, ntl;
+  F c, tgz;
+};
+
+// one stage of a reduce-scatter butterfly over `CNT` values held per lane
+template <typename F, int CNT> __device__ __forceinline__ void rs_stage(F *v, int lane, int mask) {
+  const bool upper = (lane & mask) != 0;
+#pragma unroll
+  for (int i = 0; i < CNT / 2; ++i) {
+    const F send = upper ? v[i] : v[i + CNT / 2];
+    const F keep = upper ? v[i + CNT / 2] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
+  }
+}
+
+template <typename F, bool BATCH, bool MASKED>
+__device__ __forceinline__ void edge_tile(const EdgeArgs<F> &A, F *__restrict__ wt,
+                                          const F *__restrict__ zt, F *__restrict__ rt, int I, int J,
+                                          const F (*s_ab)[2], const F *aj, const F *bj, F *csp, F *csw,
+                                          F *rowfinal, F &res, F &wsq) {
+  using V = typename Vec<F>::type;
+  constexpr int VEC = Vec<F>::N;
+  constexpr int NV = T / (32 * VEC);
+  constexpr int CH = 4;                       // rows per chunk
+  constexpr int NCH = ROWS_PER_WARP / CH;     // 4 chunks
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  const bool diag = I == J;
+  const F c = A.c, tgz = A.tgz;
+  const F zero = F(0);
+
+  V wv[2][CH][NV], zv[2][CH][NV];
+  F hold[NCH];
+
+  auto active = [&](int ch, int v) -> bool {
+    // in a diagonal tile a vector is live only if its last column lies right of the chunk's first row
+    const int r0 = wp * ROWS_PER_WARP + ch * CH;
+    return !MASKED || !diag || (v * 32 * VEC + lane * VEC + VEC - 1 > r0);
+  };
+  auto load_chunk = [&](int buf, int ch) {
+    const int r0 = wp * ROWS_PER_WARP + ch * CH;
+#pragma unroll
+    for (int rr = 0; rr < CH; ++rr)
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        const int off = (r0 + rr) * T + v * 32 * VEC + lane * VEC;
+        if (active(ch, v)) {
+          wv[buf][rr][v] = ld_stream(reinterpret_cast<const V *>(wt + off));
+          zv[buf][rr][v] = ld_stream(reinterpret_cast<const V *>(zt + off));
+        } else {
+          F zz[VEC];
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) zz[e] = zero;
+          wv[buf][rr][v] = vec_pack<F>(zz);
+          zv[buf][rr][v] = vec_pack<F>(zz);
+        }
+      }
+  };
+
+  load_chunk(0, 0);
+#pragma unroll
+  for (int ch = 0; ch < NCH; ++ch) {
+    if (ch + 1 < NCH) load_chunk((ch + 1) & 1, ch + 1);
+    const int buf = ch & 1;
+    const int r0 = wp * ROWS_PER_WARP + ch * CH;
+    F rowv[2 * CH];
+#pragma unroll
+    for (int rr = 0; rr < CH; ++rr) {
+      const int r = r0 + rr;
+      const F ai = s_ab[r][0], bi = s_ab[r][1];
+      F rsp = zero, rsw = zero;
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        F wq[VEC], zq[VEC], wn[VEC], rq[VEC];
+        vec_unpack<F>(wv[buf][rr][v], wq);
+        vec_unpack<F>(zv[buf][rr][v], zq);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+          const int ci = v * VEC + e;
+          const F wo = wq[e];
+          const F y = c * wo - (ai + aj[ci]);                 // :147
+          F p = y - tgz * zq[e];                              // :150
+          p = p > zero ? p : zero;
+          const F q = c * p - (bi + bj[ci]);                  // :153
+          F rr_ = q - y;
+          F wnew = (wo - y) + q;                              // :163
+          if (MASKED) {
+            const int gi = I * T + r, gj = J * T + v * 32 * VEC + lane * VEC + e;
+            const bool ok = (gj > gi) && (gj < A.n);
+            p = ok ? p : zero;
+            rr_ = ok ? rr_ : zero;
+            wnew = ok ? wnew : zero;
+          }
+          res += rr_ * rr_;
+          wsq += wnew * wnew;
+          rsp += p;
+          rsw += wnew;
+          csp[ci] += p;
+          csw[ci] += wnew;
+          wn[e] = wnew;
+          rq[e] = rr_;
+        }
+        if (active(ch, v)) {
+          const int off = r * T + v * 32 * VEC + lane * VEC;
+          st_stream(reinterpret_cast<V *>(wt + off), vec_pack<F>(wn));
+          if (BATCH) st_stream(reinterpret_cast<V *>(rt + off), vec_pack<F>(rq));
+        }
+      }
+      rowv[2 * rr] = rsp;
+      rowv[2 * rr + 1] = rsw;
+    }
+    // reduce-scatter the chunk's 8 row values over lane bits 4,3,2
+    rs_stage<F, 8>(rowv, lane, 16);
+    rs_stage<F, 4>(rowv, lane, 8);
+    rs_stage<F, 2>(rowv, lane, 4);
+    hold[ch] = rowv[0];
+  }
+  // finish over lane bits 1,0: lane ends with the total of
+  //   row = wp*16 + (lane&3)*4 + ((lane>>3)&3),  quantity = (lane>>2)&1  (0: S p, 1: S w')
+  rs_stage<F, 4>(hold, lane, 2);
+  rs_stage<F, 2>(hold, lane, 1);
+  *rowfinal = hold[0];
+}
+
+template <typename F, bool BATCH>
+__global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pass_kernel(const EdgeArgs<F> A) {
+  using V = typename Vec<F>::type;
+  constexpr int VEC = Vec<F>::N;
+  constexpr int NV = T / (32 * VEC);
+  constexpr int NC = NV * VEC;
+  __shared__ F s_ab[T][2];
+  __shared__ F s_col[EDGE_THREADS / 32][2][T];
+  __shared__ double s_red[EDGE_THREADS / 32][2];
+  __shared__ int s_last;
+
+  if (*reinterpret_cast<volatile int *>(A.flags + FLAG_DONE)) return;
+
+  const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+  const int t = blockIdx.x, k = blockIdx.y;
+  const int2 ij = A.tile_ij[t];
+  const int I = ij.x, J = ij.y;
+  const bool masked = (I == J) || ((J + 1) * T > A.n);
+  const F *a = A.a + (int64_t)k * A.npad, *b = A.b + (int64_t)k * A.npad;
+  if (tid < T) {
+    s_ab[tid][0] = a[I * T + tid];
+    s_ab[tid][1] = b[I * T + tid];
+  }
+  F aj[NC], bj[NC], csp[NC], csw[NC];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    const int col = J * T + v * 32 * VEC + lane * VEC;
+    vec_unpack<F>(*reinterpret_cast<const V *>(a + col), aj + v * VEC);
+    vec_unpack<F>(*reinterpret_cast<const V *>(b + col), bj + v * VEC);
+  }
+#pragma unroll
+  for (int i = 0; i < NC; ++i) csp[i] = csw[i] = F(0);
+  __syncthreads();
+
+  const int64_t base = (int64_t)k * A.gstride + (int64_t)t * TT;
+  F *wt = A.w + base;
+  const F *zt = A.z + base;
+  F *rt = BATCH ? A.r + base : nullptr;
+  F rowfinal, res = F(0), wsq = F(0);
+  if (masked)
+    edge_tile<F, BATCH, true>(A, wt, zt, rt, I, J, s_ab, aj, bj, csp, csw, &rowfinal, res, wsq);
+  else
+    edge_tile<F, BATCH, false>(A, wt, zt, rt, I, J, s_ab, aj, bj, csp, csw, &rowfinal, res, wsq);
+
+  // ---- row totals: one float64 atomic per (row, quantity) -----------------------------------
+  {
+    const int r = wp * ROWS_PER_WARP + (lane & 3) * 4 + ((lane >> 3) & 3);
+    const int qty = (lane >> 2) & 1;
+    const int gi = I * T + r;
+    if (gi < A.n) atomicAdd((qty ? A.sw : A.sp) + (int64_t)k * A.npad + gi, (double)rowfinal);
+  }
+  // ---- column totals: 8 warps -> shared -> one atomic per (column, quantity) ------------------
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    const int col = v * 32 * VEC + lane * VEC;
+    *reinterpret_cast<V *>(&s_col[wp][0][col]) = vec_pack<F>(csp + v * VEC);
+    *reinterpret_cast<V *>(&s_col[wp][1][col]) = vec_pack<F>(csw + v * VEC);
+  }
+  if (!BATCH) {
+    const double r2 = warp_sum((double)res), w2 = warp_sum((double)wsq);
+    if (lane == 0) {
+      s_red[wp][0] = r2;
+      s_red[wp][1] = w2;
+    }
+  }
+  __syncthreads();
+  {
+    const int qty = tid >> 7, col = tid & (T - 1);
+    double acc = 0.0;
+#pragma unroll
+    for (int q = 0; q < EDGE_THREADS / 32; ++q) acc += (double)s_col[q][qty][col];
+    const int gj = J * T + col;
+    if (gj < A.n) atomicAdd((qty ? A.sw : A.sp) + (int64_t)k * A.npad + gj, acc);
+  }
+  if (BATCH) return;
+
+  // ---- residual sums: fixed-order two-stage reduction (deterministic) -------------------------
+  if (tid == 0) {
+    double r2 = 0.0, w2 = 0.0;
+#pragma unroll
+    for (int q = 0; q < EDGE_THREADS / 32; ++q) {
+      r2 += s_red[q][0];
+      w2 += s_red[q][1];
+    }
+    A.cta_partial[2 * t] = r2;
+    A.cta_partial[2 * t + 1] = w2;
+    __threadfence();
+    const int ticket = atomicAdd(A.flags + FLAG_EDGE_TICKET, 1);
+    s_last = (ticket == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double r2 = 0.0, w2 = 0.0;
+  for (int i = tid; i < A.ntl; i += EDGE_THREADS) {
+    r2 += __ldcg(A.cta_partial + 2 * i);
+    w2 += __ldcg(A.cta_partial + 2 * i + 1);
+  }
+  r2 = warp_sum(r2);
+  w2 = warp_sum(w2);
+  __syncthreads();
+  if (lane == 0) {
+    s_red[wp][0] = r2;
+    s_red[wp][1] = w2;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    r2 = w2 = 0.0;
+    for (int q = 0; q < EDGE_THREADS / 32; ++q) {
+      r2 += s_red[q][0];
+      w2 += s_red[q][1];
+    }
+    A.gsum[0] += r2;  // xch slot is zeroed by the node tail; += keeps the sharded sum convention
+    A.gsum[1] += w2;
+    A.flags[FLAG_EDGE_TICKET] = 0;
+  }
+}
+
+// ---- initial degrees: d0 = S w0 and ||w0||^2 (smooth_learning.py:144) ---------------------------
+// Not on the per-iteration path; one warp per tile row, plain shuffles.
+template <typename F>
+__global__ void __launch_bounds__(EDGE_THREADS) edge_init_kernel(const F *w, int64_t gstride,
+                                                                 const int2 *tile_ij, double *sw,
+                                                                 double *gw, int n, int npad, int K) {
+  __shared__ double s_col[T];
+  __shared__ double s_sq;
+  const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+  const int t = blockIdx.x, k = blockIdx.y;
+  const int2 ij = tile_ij[t];
+  const int I = ij.x, J = ij.y;
+  if (tid < T) s_col[tid] = 0.0;
+  if (tid == 0) s_sq = 0.0;
+  __syncthreads();
+  const F *wt = w + (int64_t)k * gstride + (int64_t)t * TT;
+  double colacc[4] = {0, 0, 0, 0}, sq = 0.0;
+  for (int r = wp; r < T; r += EDGE_THREADS / 32) {
+    const int gi = I * T + r;
+    double rs = 0.0;
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      const int col = cc * 32 + lane, gj = J * T + col;
+      const double v = (gj > gi && gj < n) ? (double)wt[r * T + col] : 0.0;
+      rs += v;
+      colacc[cc] += v;
+      sq += v * v;
+    }
+    rs = warp_sum(rs);
+    if (lane == 0 && gi < n) atomicAdd(sw + (int64_t)k * npad + gi, rs);
+  }
+#pragma unroll
+  for (int cc = 0; cc < 4; ++cc) atomicAdd(&s_col[cc * 32 + lane], colacc[cc]);
+  sq = warp_sum(sq);
+  if (lane == 0) atomicAdd(&s_sq, sq);
+  __syncthreads();
+  if (tid < T && J * T + tid < n) atomicAdd(sw + (int64_t)k * npad + J * T + tid, s_col[tid]);
+  // Gram diagonal only here; the off-diagonal entries of Gram(W0) come from gram_edges (K > 1)
+  if (tid == 0 && K == 1) atomicAdd(gw, s_sq);
+}
+
+template <typename F> static int edge_pass_t(gl_solver *s, cudaStream_t st) {
+  EdgeArgs<F> A;
+  A.w = static_cast<F *>(s->w);
+  A.z = static_cast<const F *>(s->z);
+  A.r = static_cast<F *>(s->r);
+  A.gstride = s->gstride;
+  A.a = static_cast<const F *>(s->a);
+  A.b = static_cast<const F *>(s->b);
+  A.sp = s->xch;
+  A.sw = s->xch + (int64_t)s->K * s->npad;
+  A.cta_partial = s->cta_partial;
+  A.gsum = s->xch + 2 * (int64_t)s->K * s->npad;
+  A.tile_ij = s->tile_ij;
+  A.flags = s->flags;
+  A.n = s->n;
+  A.npad = s->npad;
+  A.ntl = s->ntl;
+  A.c = (F)s->c;
+  A.tgz = (F)(2.0 * s->gamma);
+  if (s->ntl == 0) return GL_OK;
+  dim3 grid(s->ntl, s->K);
+  if (s->K == 1)
+    edge_pass_kernel<F, false><<<grid, EDGE_THREADS, 0, st>>>(A);
+  else
+    edge_pass_kernel<F, true><<<grid, EDGE_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+int launch_edge_pass(gl_solver *s, cudaStream_t st) {
+  return s->dtype == GL_F32 ? edge_pass_t<float>(s, st) : edge_pass_t<double>(s, st);
+}
+
+int launch_edge_init(gl_solver *s, cudaStream_t st) {
+  if (s->ntl == 0) return GL_OK;
+  dim3 grid(s->ntl, s->K);
+  double *sw = s->xch + (int64_t)s->K * s->npad;
+  double *gw = s->xch + 2 * (int64_t)s->K * s->npad + (int64_t)s->K * s->K;
+  if (s->dtype == GL_F32)
+    edge_init_kernel<float><<<grid, EDGE_THREADS, 0, st>>>(static_cast<const float *>(s->w), s->gstride,
+                                                          s->tile_ij, sw, gw, s->n, s->npad, s->K);
+  else
+    edge_init_kernel<double><<<grid, EDGE_THREADS, 0, st>>>(static_cast<const double *>(s->w), s->gstride,
+                                                           s->tile_ij, sw, gw, s->n, s->npad, s->K);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+}  // namespace gl

@@ -1,0 +1,343 @@
+// node_tail.cu -- K4: the n-vector tail of every iteration, and the batch Gram kernel.
+//
+// Replaces the node-sized work of the reference loop body, graph_learn/smooth_learning.py:
+//   qb = pb + gamma S p                       :154
+//   rel_dual numerator / denominator          :159     (spectral norm for a (n,K) batch)
+//   d  <- d - yb + qb                         :164
+//   stop rule                                 :156-161, :166
+// and prepares the NEXT iteration's dual prox, whose input is known as soon as S w' is:
+//   yb' = d' + gamma S w'                     :148
+//   pb' = (yb' - sqrt(yb'^2 + 4 alpha gamma))/2   :151
+// Node arithmetic is float64 in both dtype modes (n values; negligible traffic).  The last CTA
+// to finish evaluates the residual norms and sets the device-side stop flag, so a captured graph
+// of iterations needs no host round trip (SURVEY 7.2 "stopping rule must match exactly").
+#include <math_constants.h>
+
+#include "solver.cuh"
+
+namespace gl {
+
+constexpr int NODE_THREADS = 256;
+
+struct NodeArgs {
+  double *d, *yb, *pb, *rb;
+  void *a, *b;
+  double *xch;     // [sp | sw | G_r | G_w]
+  double *gprev;   // [Gram(W) | Gram(D)] of the previous iterate
+  double *resid;   // rel_primal, rel_dual
+  double *eig;     // scratch 4 x 2 x K*K
+  int *flags;
+  int n, npad, K, f32, init, maxit;
+  double gamma, four_ag, tol;
+};
+
+// lambda_max of four symmetric PSD K x K matrices at once (quarter of the block each) by repeated
+// squaring B <- B^2 / tr(B^2) followed by a Rayleigh quotient with the original matrix.  With 26
+// squarings the quotient's relative error is below 1e-8 for ANY spectrum (worst case over the
+// gap is 1/(e*2^27)); sigma_max = sqrt(lambda_max), what np.linalg.norm(., ord=2) returns for
+// the (E,K) / (n,K) operands at smooth_learning.py:158-159.
+__device__ void lambda_max4(const double *const *G, int K, double *scratch, double *out) {
+  const int q = threadIdx.x / (NODE_THREADS / 4), lt = threadIdx.x % (NODE_THREADS / 4);
+  constexpr int L = NODE_THREADS / 4;
+  const int KK = K * K;
+  const double *g = G[q];
+  if (K == 1) {
+    if (lt == 0) out[q] = g[0];
+    __syncthreads();
+    return;
+  }
+  double *B = scratch + (int64_t)q * 2 * KK, *C = B + KK;
+  __shared__ double s_tr[4];
+  __shared__ int s_bad[4];
+  if (lt == 0) {
+    double tr = 0.0;
+    for (int i = 0; i < K; ++i) tr += g[i * K + i];
+    s_tr[q] = tr;
+    s_bad[q] = !(tr > 0.0) || !isfinite(tr);
+  }
+  __syncthreads();
+  if (!s_bad[q])
+    for (int e = lt; e < KK; e += L) B[e] = g[e] / s_tr[q];
+  __syncthreads();
+  for (int it = 0; it < 26; ++it) {
+    if (!s_bad[q])
+      for (int e = lt; e < KK; e += L) {
+        const int i = e / K, j = e % K;
+        double acc = 0.0;
+        for (int m = 0; m < K; ++m) acc += B[i * K + m] * B[m * K + j];
+        C[e] = acc;
+      }
+    __syncthreads();
+    if (lt == 0 && !s_bad[q]) {
+      double tr = 0.0;
+      for (int i = 0; i < K; ++i) tr += C[i * K + i];
+      s_tr[q] = tr;
+    }
+    __syncthreads();
+    if (!s_bad[q])
+      for (int e = lt; e < KK; e += L) B[e] = C[e] / s_tr[q];
+    __syncthreads();
+  }
+  if (lt == 0) {
+    if (s_bad[q]) {
+      double tr = 0.0;
+      for (int i = 0; i < K; ++i) tr += g[i * K + i];
+      out[q] = (tr == 0.0) ? 0.0 : CUDART_NAN;
+    } else {
+      int col = 0;
+      for (int i = 1; i < K; ++i)
+        if (B[i * K + i] > B[col * K + col]) col = i;
+      double num = 0.0, den = 0.0;
+      for (int i = 0; i < K; ++i) {
+        double gv = 0.0;
+        for (int j = 0; j < K; ++j) gv += g[i * K + j] * B[j * K + col];
+        num += B[i * K + col] * gv;
+        den += B[i * K + col] * B[i * K + col];
+      }
+      out[q] = num / den;
+    }
+  }
+  __syncthreads();
+}
+
+// Gram matrices over the node axis of x (K, npad): out[k*K+l] = sum_v x[k][v] x[l][v], for two
+// arrays at once.  Fixed summation order (deterministic).
+__device__ void node_gram2(const double *x0, const double *x1, int K, int n, int npad, double *out0,
+                           double *out1) {
+  __shared__ double s_part[2][NODE_THREADS];
+  const int KK = K * K;
+  const int tid = threadIdx.x;
+  if (KK <= NODE_THREADS) {
+    const int L = NODE_THREADS / KK;  // lanes per pair
+    const int p = tid / L, l = tid % L;
+    double a0 = 0.0, a1 = 0.0;
+    if (p < KK) {
+      const int k = p / K, m = p % K;
+      for (int v = l; v < n; v += L) {
+        a0 += __ldcg(x0 + (int64_t)k * npad + v) * __ldcg(x0 + (int64_t)m * npad + v);
+        a1 += __ldcg(x1 + (int64_t)k * npad + v) * __ldcg(x1 + (int64_t)m * npad + v);
+      }
+    }
+    s_part[0][tid] = a0;
+    s_part[1][tid] = a1;
+    __syncthreads();
+    // tree over the L lanes of each pair (L is not a power of two in general: sequential halves)
+    if (p < KK && l == 0) {
+      double t0 = 0.0, t1 = 0.0;
+      for (int i = 0; i < L; ++i) {
+        t0 += s_part[0][tid + i];
+        t1 += s_part[1][tid + i];
+      }
+      out0[p] = t0;
+      out1[p] = t1;
+    }
+  } else {
+    for (int p = tid; p < KK; p += NODE_THREADS) {
+      const int k = p / K, m = p % K;
+      double a0 = 0.0, a1 = 0.0;
+      for (int v = 0; v < n; ++v) {
+        a0 += __ldcg(x0 + (int64_t)k * npad + v) * __ldcg(x0 + (int64_t)m * npad + v);
+        a1 += __ldcg(x1 + (int64_t)k * npad + v) * __ldcg(x1 + (int64_t)m * npad + v);
+      }
+      out0[p] = a0;
+      out1[p] = a1;
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs A) {
+  __shared__ int s_last;
+  __shared__ double s_lam[4];
+  if (!A.init && *reinterpret_cast<volatile int *>(A.flags + FLAG_DONE)) return;
+  const int tid = threadIdx.x;
+  const int64_t total = (int64_t)A.K * A.npad;
+  const int64_t idx = (int64_t)blockIdx.x * NODE_THREADS + tid;
+  if (idx < total) {
+    const int v = (int)(idx % A.npad);
+    const double sp = A.xch[idx], sw = A.xch[total + idx];
+    A.xch[idx] = 0.0;
+    A.xch[total + idx] = 0.0;
+    double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
+    if (v < A.n) {
+      if (A.init) {
+        dn = sw;                                   // d0 = S w0            :144
+      } else {
+        const double dv = A.d[idx], ybv = A.yb[idx];
+        const double qb = A.pb[idx] + A.gamma * sp;  //                    :154
+        rbv = qb - ybv;
+        dn = (dv - ybv) + qb;                       //                      :164
+      }
+      ybn = dn + A.gamma * sw;                       //                      :148
+      pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;  //                   :151
+    }
+    A.d[idx] = dn;
+    A.yb[idx] = ybn;
+    A.pb[idx] = pbn;
+    A.rb[idx] = rbv;
+    if (A.f32) {
+      static_cast<float *>(A.a)[idx] = (float)(A.gamma * dn);
+      static_cast<float *>(A.b)[idx] = (float)(A.gamma * pbn);
+    } else {
+      static_cast<double *>(A.a)[idx] = A.gamma * dn;
+      static_cast<double *>(A.b)[idx] = A.gamma * pbn;
+    }
+  }
+  // ---- last CTA: residual norms, stop rule --------------------------------------------------
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const int ticket = atomicAdd(A.flags + FLAG_NODE_TICKET, 1);
+    s_last = (ticket == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+
+  const int KK = A.K * A.K;
+  double *g_r = A.xch + 2 * total, *g_w = g_r + KK;   // edge-side Grams (summed over shards)
+  double *g_rb = A.eig + 8 * (int64_t)KK, *g_d = g_rb + KK;  // node-side Grams, computed here
+  node_gram2(A.rb, A.d, A.K, A.n, A.npad, g_rb, g_d);
+
+  const int it = A.flags[FLAG_IT];
+  if (!A.init && it >= 1) {
+    const double *G[4] = {g_r, A.gprev, g_rb, A.gprev + KK};
+    lambda_max4(G, A.K, A.eig, s_lam);
+  }
+  __syncthreads();
+  // rotate the denominators and clear the exchange slots
+  for (int e = tid; e < KK; e += NODE_THREADS) {
+    A.gprev[e] = __ldcg(g_w + e);
+    A.gprev[KK + e] = g_d[e];
+  }
+  __syncthreads();
+  for (int e = tid; e < 2 * KK; e += NODE_THREADS) g_r[e] = 0.0;
+  if (tid == 0) {
+    A.flags[FLAG_NODE_TICKET] = 0;
+    if (A.init) {
+      A.flags[FLAG_IT] = 0;
+      A.flags[FLAG_CONVERGED] = 0;
+      A.flags[FLAG_DONE] = (A.maxit <= 0);
+      A.resid[0] = CUDART_INF;
+      A.resid[1] = CUDART_INF;
+    } else {
+      bool conv = false;
+      if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+        const double rp = sqrt(s_lam[0]) / sqrt(s_lam[1]);
+        const double rd = sqrt(s_lam[2]) / sqrt(s_lam[3]);
+        A.resid[0] = rp;
+        A.resid[1] = rd;
+        conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
+      }
+      A.flags[FLAG_IT] = it + 1;
+      if (conv) A.flags[FLAG_CONVERGED] = 1;
+      if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
+    }
+  }
+}
+
+int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
+  NodeArgs A;
+  A.d = s->d; A.yb = s->yb; A.pb = s->pb; A.rb = s->rb;
+  A.a = s->a; A.b = s->b;
+  A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.eig = s->eig_scratch;
+  A.flags = s->flags;
+  A.n = s->n; A.npad = s->npad; A.K = s->K; A.f32 = (s->dtype == GL_F32);
+  A.init = init ? 1 : 0;
+  A.maxit = s->maxit;
+  A.gamma = s->gamma;
+  A.four_ag = 4.0 * s->alpha * s->gamma;
+  A.tol = s->tol;
+  const int64_t total = (int64_t)s->K * s->npad;
+  const int grid = (int)((total + NODE_THREADS - 1) / NODE_THREADS);
+  node_tail_kernel<<<grid, NODE_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+// ---- batch mode: Gram matrices of R = Q - Y and of W' over the local edge shard --------------
+// 8 x 8 register-blocked; grid = (chunks, graph-block pairs kb <= lb, {R, W}).
+constexpr int GRAM_THREADS = 128;
+constexpr int GB = 8;
+
+template <typename F>
+__global__ void __launch_bounds__(GRAM_THREADS) gram_edges_kernel(const F *r, const F *w, int64_t gstride,
+                                                                   int64_t len, int K, double *g_r,
+                                                                   double *g_w, const int *flags,
+                                                                   int check_done) {
+  if (check_done && *reinterpret_cast<const volatile int *>(flags + FLAG_DONE)) return;
+  __shared__ double s_acc[GRAM_THREADS / 32][GB * GB];
+  const int nb = (K + GB - 1) / GB;
+  // decode pair index blockIdx.y -> (kb <= lb)
+  int kb = 0, rem = blockIdx.y;
+  while (rem >= nb - kb) {
+    rem -= nb - kb;
+    ++kb;
+  }
+  const int lb = kb + rem;
+  const F *x = blockIdx.z == 0 ? r : w;
+  double *g = blockIdx.z == 0 ? g_r : g_w;
+  double acc[GB][GB];
+#pragma unroll
+  for (int i = 0; i < GB; ++i)
+#pragma unroll
+    for (int j = 0; j < GB; ++j) acc[i][j] = 0.0;
+  const int64_t per = (len + gridDim.x - 1) / gridDim.x;
+  const int64_t e0 = (int64_t)blockIdx.x * per, e1 = e0 + per < len ? e0 + per : len;
+  for (int64_t e = e0 + threadIdx.x; e < e1; e += GRAM_THREADS) {
+    double xa[GB], xb[GB];
+#pragma unroll
+    for (int i = 0; i < GB; ++i) {
+      const int k = kb * GB + i, l = lb * GB + i;
+      xa[i] = k < K ? (double)x[(int64_t)k * gstride + e] : 0.0;
+      xb[i] = l < K ? (double)x[(int64_t)l * gstride + e] : 0.0;
+    }
+#pragma unroll
+    for (int i = 0; i < GB; ++i)
+#pragma unroll
+      for (int j = 0; j < GB; ++j) acc[i][j] += xa[i] * xb[j];
+  }
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < GB; ++i)
+#pragma unroll
+    for (int j = 0; j < GB; ++j) {
+      const double v = warp_sum(acc[i][j]);
+      if (lane == 0) s_acc[wp][i * GB + j] = v;
+    }
+  __syncthreads();
+  if (threadIdx.x < GB * GB) {
+    const int i = threadIdx.x / GB, j = threadIdx.x % GB;
+    const int k = kb * GB + i, l = lb * GB + j;
+    if (k < K && l < K) {
+      double v = 0.0;
+      for (int q = 0; q < GRAM_THREADS / 32; ++q) v += s_acc[q][threadIdx.x];
+      atomicAdd(g + (int64_t)k * K + l, v);
+      if (kb != lb) atomicAdd(g + (int64_t)l * K + k, v);
+    }
+  }
+}
+
+int launch_gram_edges(gl_solver *s, cudaStream_t st) {
+  if (s->K == 1 || s->ntl == 0) return GL_OK;
+  const int nb = (s->K + GB - 1) / GB;
+  const int64_t len = s->gstride;
+  int chunks = (int)((len + 8191) / 8192);
+  if (chunks > 592) chunks = 592;
+  if (chunks < 1) chunks = 1;
+  dim3 grid(chunks, nb * (nb + 1) / 2, 2);
+  const int64_t total = (int64_t)s->K * s->npad;
+  double *g_r = s->xch + 2 * total, *g_w = g_r + (int64_t)s->K * s->K;
+  if (s->dtype == GL_F32)
+    gram_edges_kernel<float><<<grid, GRAM_THREADS, 0, st>>>(static_cast<const float *>(s->r),
+                                                           static_cast<const float *>(s->w), s->gstride,
+                                                           len, s->K, g_r, g_w, s->flags, s->begun ? 1 : 0);
+  else
+    gram_edges_kernel<double><<<grid, GRAM_THREADS, 0, st>>>(static_cast<const double *>(s->r),
+                                                            static_cast<const double *>(s->w), s->gstride,
+                                                            len, s->K, g_r, g_w, s->flags, s->begun ? 1 : 0);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+}  // namespace gl

@@ -1,0 +1,55 @@
+// solver.cuh -- workspace of the LogModel primal-dual solver (opaque `gl_solver` of the C-ABI).
+#pragma once
+#include "common.cuh"
+
+// Device flag words (int): see node_tail / edge_pass.
+enum {
+  FLAG_DONE = 0,        // stop rule or maxit fired: later launches are no-ops
+  FLAG_IT = 1,          // iterations completed
+  FLAG_CONVERGED = 2,   // stop rule (smooth_learning.py:166) fired
+  FLAG_EDGE_TICKET = 3, // last-CTA-done counter of the edge pass
+  FLAG_NODE_TICKET = 4, // last-CTA-done counter of the node tail
+  FLAG_COUNT = 8
+};
+
+struct gl_solver {
+  int n = 0, K = 0, dtype = 0;
+  int nt = 0, npad = 0;
+  int tile_begin = 0, tile_end = 0, ntl = 0;  // local tile range / count
+  size_t esz = 4;
+  int64_t gstride = 0;  // elements per graph in the local tiled buffers
+  int device = 0;
+
+  // edge state (edge dtype), [K][ntl*TT]
+  void *w = nullptr, *z = nullptr, *r = nullptr /* K>1 only: q - y of the last pass */;
+  int2 *tile_ij = nullptr;  // [ntl] global (I, J) of each local tile
+  // node state
+  double *d = nullptr, *yb = nullptr, *pb = nullptr, *rb = nullptr;  // [K][npad]
+  void *a = nullptr, *b = nullptr;  // [K][npad] edge dtype: gamma*d, gamma*pb
+  // exchange buffer (float64): [sp K*npad | sw K*npad | G_r K*K | G_w K*K]
+  double *xch = nullptr;
+  int64_t xch_len = 0;
+  double *cta_partial = nullptr;  // [ntl][2] per-CTA residual sums of the edge pass (K == 1)
+  double *gprev = nullptr;        // [2][K*K]: Gram(W), Gram(D) of the previous iterate (denominators)
+  double *resid = nullptr;        // [2]: rel_primal, rel_dual of the last checked iteration
+  double *eig_scratch = nullptr;  // [4][2][K*K] repeated-squaring buffers
+  int *flags = nullptr;           // [FLAG_COUNT]
+
+  // parameters of the current solve
+  double alpha = 1, beta = 1, step = 0.5, gamma = 0, c = 0, tol = 1e-5;
+  int maxit = 1000;
+  bool begun = false;
+
+  // captured iteration graph (single-GPU driver)
+  cudaGraphExec_t graph_exec = nullptr;
+  int graph_iters = 0;
+  cudaStream_t graph_stream_tag = nullptr;
+};
+
+namespace gl {
+int launch_edge_pass(gl_solver *s, cudaStream_t st);
+int launch_edge_init(gl_solver *s, cudaStream_t st);
+int launch_gram_edges(gl_solver *s, cudaStream_t st);
+int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
+int fill_tile_table(gl_solver *s);
+}  // namespace gl

@@ -1,0 +1,462 @@
+"""Learning graphs from smooth signals -- B200-native drop-in for the reference module
+``graph_learn/smooth_learning.py`` (LTS4/graph-learning).
+
+Same public names and call semantics as the reference:
+
+* :func:`sum_squareform`               (reference :13-44)
+* :func:`gsp_learn_graph_log_degrees`  (reference :47-174)
+* :func:`get_theta`                    (reference :177-235)
+* :class:`LogModel`                    (reference :238-300)
+
+All arithmetic runs in hand-written sm_100a kernels behind the C-ABI of ``include/gl_b200.h``
+(``libgl_b200.so``); torch is used only to own device memory and streams.  Inputs may be NumPy
+arrays (results come back as NumPy, like the reference) or CUDA torch tensors (results stay on
+the device).  Extra keyword-only arguments (``dtype``, ``return_info``) default to the reference
+behaviour.  There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from itertools import combinations_with_replacement
+from typing import Optional
+
+import numpy as np
+import torch
+from sklearn.base import BaseEstimator
+
+from . import _native as nat
+
+__all__ = [
+    "sum_squareform",
+    "gsp_learn_graph_log_degrees",
+    "get_theta",
+    "LogModel",
+    "Solver",
+    "pdist_sq",
+    "SolveInfo",
+]
+
+
+# --------------------------------------------------------------------------------------------
+# device plumbing
+# --------------------------------------------------------------------------------------------
+def _device() -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError(
+            "graph_learning_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback"
+        )
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream() -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _torch_dtype(dtype) -> torch.dtype:
+    if dtype in (None, "float64", "f64", np.float64, torch.float64, float):
+        return torch.float64
+    if dtype in ("float32", "f32", np.float32, torch.float32):
+        return torch.float32
+    raise ValueError(f"dtype must be float32 or float64, got {dtype!r}")
+
+
+def _gl_dtype(t: torch.dtype) -> int:
+    return nat.GL_F32 if t == torch.float32 else nat.GL_F64
+
+
+def _to_device(a, dtype: torch.dtype) -> torch.Tensor:
+    """NumPy / torch -> contiguous CUDA tensor of ``dtype`` (copy only when needed)."""
+    if isinstance(a, torch.Tensor):
+        return a.to(device=_device(), dtype=dtype).contiguous()
+    arr = np.ascontiguousarray(a)
+    t = torch.from_numpy(arr)
+    if arr.dtype != (np.float32 if dtype == torch.float32 else np.float64):
+        t = t.to(dtype)
+    return t.to(_device(), non_blocking=False).contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]) -> ctypes.c_void_p:
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _n_from_edges(n_edges: int) -> int:
+    # smooth_learning.py:133
+    n = int(np.round((1 + np.sqrt(1 + 8 * n_edges)) / 2))
+    if n * (n - 1) // 2 != n_edges:
+        raise ValueError(f"{n_edges} is not a triangular number of edges")
+    return n
+
+
+class SolveInfo:
+    """Iteration count and last relative residuals of a solve (the reference returns neither)."""
+
+    def __init__(self, n_iter: int, rel_primal: float, rel_dual: float, converged: bool):
+        self.n_iter, self.rel_primal, self.rel_dual, self.converged = n_iter, rel_primal, rel_dual, converged
+
+    def __repr__(self):
+        return (f"SolveInfo(n_iter={self.n_iter}, rel_primal={self.rel_primal:.3e}, "
+                f"rel_dual={self.rel_dual:.3e}, converged={self.converged})")
+
+
+# --------------------------------------------------------------------------------------------
+# solver workspace (handle API)
+# --------------------------------------------------------------------------------------------
+class Solver:
+    """Resident state of the primal-dual iteration for K graphs on n nodes (``gl_solver``).
+
+    ``tile_range`` restricts the workspace to a shard of the triangle's 128x128 tiles; the
+    caller then sums :meth:`exchange` over shards between :meth:`edge_pass` and
+    :meth:`node_tail` (see ``graph_learning_b200/sharded.py``).
+    """
+
+    def __init__(self, n: int, n_graphs: int = 1, dtype=torch.float64, tile_range=None):
+        self.lib = nat.lib()
+        self.n, self.K, self.dtype = int(n), int(n_graphs), _torch_dtype(dtype)
+        self.device = _device()
+        total = self.lib.gl_num_tiles(self.n)
+        self.tile_begin, self.tile_end = (0, total) if tile_range is None else map(int, tile_range)
+        h = ctypes.c_void_p()
+        nat.check(self.lib.gl_solver_create(ctypes.byref(h), self.n, self.K, _gl_dtype(self.dtype),
+                                            self.tile_begin, self.tile_end))
+        self._h = h
+        self.n_edges = self.n * (self.n - 1) // 2
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.gl_solver_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def load(self, z_packed: torch.Tensor, z_scale=None, w_packed: Optional[torch.Tensor] = None):
+        assert z_packed.is_cuda and z_packed.dtype == self.dtype and z_packed.is_contiguous()
+        assert z_packed.numel() == self.K * self.n_edges
+        sc = None
+        if z_scale is not None:
+            sc = (ctypes.c_double * self.K)(*[float(v) for v in np.broadcast_to(np.asarray(z_scale, dtype=np.float64).ravel(), (self.K,))])
+        nat.check(self.lib.gl_solver_load(self._h, _ptr(z_packed), sc, _ptr(w_packed), _stream()))
+
+    def z_tiles_ptr(self, k: int = 0) -> int:
+        return self.lib.gl_solver_z_tiles(self._h, k)
+
+    def w_tiles_ptr(self, k: int = 0) -> int:
+        return self.lib.gl_solver_w_tiles(self._h, k)
+
+    def scale_z(self, z_scale):
+        sc = (ctypes.c_double * self.K)(*[float(v) for v in np.broadcast_to(np.asarray(z_scale, dtype=np.float64).ravel(), (self.K,))])
+        nat.check(self.lib.gl_solver_scale_z(self._h, sc, _stream()))
+
+    def begin(self, alpha=1.0, beta=1.0, step_size=0.5, maxit=1000, tol=1e-5, finish=True):
+        nat.check(self.lib.gl_solver_begin(self._h, float(alpha), float(beta), float(step_size), int(maxit),
+                                           float(tol), _stream()))
+        if finish:
+            self.begin_finish()
+
+    def begin_finish(self):
+        nat.check(self.lib.gl_solver_begin_finish(self._h, _stream()))
+
+    def edge_pass(self):
+        nat.check(self.lib.gl_solver_edge_pass(self._h, _stream()))
+
+    def node_tail(self):
+        nat.check(self.lib.gl_solver_node_tail(self._h, _stream()))
+
+    def exchange(self) -> torch.Tensor:
+        """float64 view of the exchange buffer (degree partials + residual Grams)."""
+        n = ctypes.c_int64()
+        p = self.lib.gl_solver_exchange_ptr(self._h, ctypes.byref(n))
+        return _wrap_device_memory(p, n.value, torch.float64, self.device, owner=self)
+
+    def run(self, poll_every: int = 0):
+        nat.check(self.lib.gl_solver_run(self._h, int(poll_every), _stream()))
+
+    def status(self) -> SolveInfo:
+        it, conv = ctypes.c_int(), ctypes.c_int()
+        rp, rd = ctypes.c_double(), ctypes.c_double()
+        nat.check(self.lib.gl_solver_status(self._h, ctypes.byref(it), ctypes.byref(rp), ctypes.byref(rd),
+                                            ctypes.byref(conv), _stream()))
+        return SolveInfo(it.value, rp.value, rd.value, bool(conv.value))
+
+    def store(self, edge_tol: float = 1e-3, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Packed (K, E) weights with the edge_tol threshold (smooth_learning.py:169).  For a
+        sharded workspace only the shard's edges are written (``out`` should start zeroed)."""
+        if out is None:
+            out = torch.zeros((self.K, self.n_edges), dtype=self.dtype, device=self.device)
+        nat.check(self.lib.gl_solver_store(self._h, _ptr(out), float(edge_tol), _stream()))
+        return out
+
+    def square(self, edge_tol: float = 1e-3) -> torch.Tensor:
+        """Dense symmetric (n, n) weights of graph 0 straight from the tiled state."""
+        assert self.tile_begin == 0 and self.tile_end == self.lib.gl_num_tiles(self.n)
+        out = torch.empty((self.n, self.n), dtype=self.dtype, device=self.device)
+        nat.check(self.lib.gl_tiles_to_square(ctypes.c_void_p(self.w_tiles_ptr(0)), _ptr(out), self.n,
+                                              _gl_dtype(self.dtype), float(edge_tol), _stream()))
+        return out
+
+    def node_state(self) -> torch.Tensor:
+        d = torch.empty((self.K, self.n), dtype=torch.float64, device=self.device)
+        nat.check(self.lib.gl_solver_node_state(self._h, _ptr(d), _stream()))
+        return d
+
+
+def _wrap_device_memory(ptr: int, numel: int, dtype: torch.dtype, device: torch.device, owner=None):
+    """Zero-copy torch view of library-owned device memory (via __cuda_array_interface__)."""
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    typestr = {torch.float64: "<f8", torch.float32: "<f4", torch.int32: "<i4"}[dtype]
+    h.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+    h._owner = owner
+    return torch.as_tensor(h, device=device)
+
+
+# --------------------------------------------------------------------------------------------
+# the edge <-> degree operator pair (reference sum_squareform, :13-44)
+# --------------------------------------------------------------------------------------------
+class _SumOperator:
+    """Matrix-free S (n x E) or S^T (E x n).  Supports ``@`` on (E,), (E,K), (n,), (n,K) NumPy
+    arrays or CUDA tensors, ``.shape`` and ``.T`` -- what the reference's callers use
+    (smooth_learning.py:136,144-154; temporal/graph_factor.py:101; dictionary/log_model.py:28)."""
+
+    def __init__(self, n: int, transposed: bool):
+        self.n, self.transposed = int(n), transposed
+        e = self.n * (self.n - 1) // 2
+        self.shape = (e, self.n) if transposed else (self.n, e)
+
+    @property
+    def T(self):
+        return _SumOperator(self.n, not self.transposed)
+
+    def __matmul__(self, v):
+        is_np = not isinstance(v, torch.Tensor)
+        dt = torch.float32 if (getattr(v, "dtype", None) in (np.float32, torch.float32)) else torch.float64
+        x = _to_device(v, dt)
+        if x.shape[0] != self.shape[1]:
+            raise ValueError(f"dimension mismatch: operator {self.shape} @ operand {tuple(x.shape)}")
+        vec = x.ndim == 1
+        xk = (x[None, :] if vec else x.t()).contiguous()  # (K, len)
+        k = xk.shape[0]
+        lib = nat.lib()
+        out = torch.empty((k, self.shape[0]), dtype=dt, device=x.device)
+        fn = lib.gl_sum_op_adj if self.transposed else lib.gl_sum_op
+        nat.check(fn(_ptr(xk), _ptr(out), self.n, k, _gl_dtype(dt), _stream()))
+        res = out[0] if vec else out.t().contiguous()
+        return res.cpu().numpy() if is_np else res
+
+
+def sum_squareform(n: int):
+    """Operator S with ``S @ w`` = weighted degrees of the packed edge vector w, and its
+    transpose (``St @ d`` = d_i + d_j per edge).  Reference :13-44 materialises both as CSR
+    matrices with O(n^2) Python list work; here they are matrix-free CUDA kernels."""
+    return _SumOperator(n, False), _SumOperator(n, True)
+
+
+# --------------------------------------------------------------------------------------------
+# pairwise squared distances (reference :278) and theta (reference :177-235)
+# --------------------------------------------------------------------------------------------
+def pdist_sq(x, row_scale=None, col_shift=None, dtype=None) -> torch.Tensor:
+    """Packed squared distances between the COLUMNS of x (m, n): ``pdist(x.T) ** 2``.
+
+    With ``row_scale`` (m,) / ``col_shift`` (n,) the signals are first mapped to
+    ``row_scale[:, None] * (x - col_shift)`` -- the GLMM M-step form (glmm.py:61-68).
+    Returns a CUDA tensor of shape (E,).
+    """
+    dt = _torch_dtype(dtype if dtype is not None else (x.dtype if getattr(x, "dtype", None) in (np.float32, torch.float32) else None))
+    xd = _to_device(x, dt)
+    if xd.ndim != 2:
+        raise ValueError("signals must be a (n_samples, n_nodes) matrix")
+    m, n = xd.shape
+    rs = None if row_scale is None else _to_device(row_scale, dt)
+    cs = None if col_shift is None else _to_device(col_shift, dt)
+    out = torch.empty((n * (n - 1) // 2,), dtype=dt, device=xd.device)
+    nat.check(nat.lib().gl_pdist_sq(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
+                                    nat.LAYOUT_PACKED, 0, 0, _gl_dtype(dt), _stream()))
+    return out
+
+
+def _theta_dense(mat: torch.Tensor, avg_degree: int) -> float:
+    th = ctypes.c_double()
+    rows, cols = mat.shape
+    nat.check(nat.lib().gl_theta_dense(_ptr(mat), rows, cols, mat.stride(0), int(avg_degree),
+                                       _gl_dtype(mat.dtype), ctypes.byref(th), _stream()))
+    return th.value
+
+
+def _theta_packed(z_packed: torch.Tensor, n: int, avg_degree: int) -> float:
+    th = ctypes.c_double()
+    nat.check(nat.lib().gl_theta(_ptr(z_packed), nat.LAYOUT_PACKED, n, int(avg_degree),
+                                 _gl_dtype(z_packed.dtype), ctypes.byref(th), _stream()))
+    return th.value
+
+
+def get_theta(sq_pdists, avg_degree, blocks=None):
+    """Theta giving the requested average degree (Kalofolias & Perraudin 2019).
+
+    ``sq_pdists`` is the SQUARE (n, n) matrix of squared distances, as in the reference
+    (:177-235); rows are ranked with their zero diagonal included (:202).  With ``blocks`` the
+    result is the packed (E,) vector of per-block-pair thetas (:220-235).
+    """
+    dt = torch.float32 if getattr(sq_pdists, "dtype", None) in (np.float32, torch.float32) else torch.float64
+    is_np = not isinstance(sq_pdists, torch.Tensor)
+    sq = _to_device(sq_pdists, dt)
+    if blocks is None:
+        return _theta_dense(sq, avg_degree)
+    blocks = np.asarray(blocks.cpu() if isinstance(blocks, torch.Tensor) else blocks)
+    n = blocks.size
+    thetas = torch.zeros((n, n), dtype=dt, device=sq.device)
+    for pair in combinations_with_replacement(np.unique(blocks).tolist(), 2):
+        idx1 = torch.as_tensor(np.where(blocks == pair[0])[0], device=sq.device)
+        idx2 = torch.as_tensor(np.where(blocks == pair[1])[0], device=sq.device)
+        block_degree = avg_degree[pair] if isinstance(avg_degree, dict) else avg_degree
+        sub = sq[idx1[:, None], idx2[None, :]].contiguous()
+        theta = _theta_dense(sub, block_degree)
+        thetas[idx1[:, None], idx2[None, :]] = theta
+        thetas[idx2[:, None], idx1[None, :]] = theta
+    iu = torch.triu_indices(n, n, 1, device=sq.device)
+    packed = thetas[iu[0], iu[1]]
+    return packed.cpu().numpy() if is_np else packed
+
+
+# --------------------------------------------------------------------------------------------
+# the solver (reference :47-174)
+# --------------------------------------------------------------------------------------------
+def gsp_learn_graph_log_degrees(
+    distances,
+    alpha: float,
+    beta: float,
+    edge_init=None,
+    maxit: int = 1000,
+    tol: float = 1e-5,
+    step_size: float = 0.5,
+    edge_tol: float = 1e-3,
+    *,
+    dtype=None,
+    return_info: bool = False,
+):
+    r"""Weighted adjacency from squared pairwise distances under the smoothness prior
+    (Kalofolias 2016): minimise :math:`\sum_{ij} w_{ij} z_{ij} - \alpha \sum_i \log(\sum_j w_{ij})
+    + \beta \|w\|^2` over :math:`w \ge 0` with the forward-backward-forward primal-dual method.
+
+    Call-compatible with the reference (:47-56): ``distances`` is (E,) -> returns the dense
+    symmetric (n, n) matrix, or (K, E) -> returns (K, E) (K graphs sharing ONE stopping decision
+    with spectral-norm residuals, :128-129, :158-159); more dimensions raise ``ValueError``
+    (:130-131).  ``edge_init`` uses the reference's internal layout: (E,) or (E, K) (:140-141).
+    Entries below ``edge_tol`` are zeroed (:169).
+
+    ``dtype`` (extra): arithmetic type of the edge arrays, default float64 (the reference's);
+    float32 halves the memory traffic.  ``return_info`` (extra): also return a :class:`SolveInfo`.
+    """
+    is_np = not isinstance(distances, torch.Tensor)
+    n_dim = len(distances.shape)
+    if n_dim > 2:
+        raise ValueError("Distances must be vector or matrix")
+    if n_dim == 0:
+        raise ValueError("Distances must be vector or matrix")
+    if dtype is None and getattr(distances, "dtype", None) in (np.float32, torch.float32):
+        dtype = torch.float32
+    dt = _torch_dtype(dtype)
+    z = _to_device(distances, dt)
+    zk = z[None, :] if n_dim == 1 else z
+    n_graphs, n_edges = zk.shape
+    n = _n_from_edges(n_edges)
+
+    w0 = None
+    if edge_init is not None:
+        w0 = _to_device(edge_init, dt)
+        w0 = (w0[None, :] if n_dim == 1 else w0.t()).contiguous()  # internal (E,K) -> (K,E)
+        if tuple(w0.shape) != (n_graphs, n_edges):
+            raise ValueError(f"edge_init has shape {tuple(edge_init.shape)}, expected "
+                             f"{(n_edges,) if n_dim == 1 else (n_edges, n_graphs)}")
+
+    solver = Solver(n, n_graphs, dt)
+    try:
+        solver.load(zk.contiguous(), None, w0)
+        solver.begin(alpha, beta, step_size, maxit, tol)
+        solver.run()
+        info = solver.status()
+        out = solver.square(edge_tol) if n_dim == 1 else solver.store(edge_tol)
+    finally:
+        solver.close()
+    if is_np:
+        out = out.cpu().numpy()
+    return (out, info) if return_info else out
+
+
+# --------------------------------------------------------------------------------------------
+# the estimator (reference :238-300)
+# --------------------------------------------------------------------------------------------
+class LogModel(BaseEstimator):
+    """Extract the graph on which data is smooth (Kalofolias 2016 model, Kalofolias & Perraudin
+    2019 parametrisation).  Drop-in for the reference ``LogModel`` (:238-300).
+
+    Parameters:
+        avg_degree (int, optional): Desired average number of neighbours per node.
+        edge_init (array, optional): Prior on graph weights, packed (E,).
+        maxit (int): Max optimisation iterations. Defaults to 1000.
+        tol (float): Optimisation tolerance. Defaults to 1e-5.
+        step_size (float): Optimisation step size. Defaults to 0.5.
+        edge_tol (float): Tolerance to keep positive edges. Defaults to 1e-3.
+        dtype (extra, keyword-only): "float64" (reference arithmetic, default) or "float32".
+
+    Attributes:
+        theta_ (float): Sparsity parameter rescaling the pairwise distances.
+        weights_ (ndarray): Dense symmetric (n, n) edge weights of the learned graph.
+        n_iter_ (int), rel_primal_ (float), rel_dual_ (float), converged_ (bool): extras.
+    """
+
+    def __init__(
+        self,
+        avg_degree: int = None,
+        *,
+        edge_init=None,
+        maxit: int = 1000,
+        tol: float = 1e-5,
+        step_size: float = 0.5,
+        edge_tol: float = 1e-3,
+        dtype="float64",
+    ) -> None:
+        self.avg_degree = avg_degree
+        self.edge_init = edge_init
+        self.maxit = maxit
+        self.tol = tol
+        self.step_size = step_size
+        self.edge_tol = edge_tol
+        self.dtype = dtype
+
+    def _initialize(self, x):
+        """Squared pairwise distances (packed, on the device) and ``theta_`` (:277-284)."""
+        sq_pdists = pdist_sq(x, dtype=self.dtype)
+        if self.avg_degree is None:
+            self.theta_ = 1
+        else:
+            n = x.shape[1]
+            self.theta_ = _theta_packed(sq_pdists, n, self.avg_degree)
+        return sq_pdists
+
+    def fit(self, x):
+        """x: (n_samples, n_nodes) signals, nodes are COLUMNS (:286-300)."""
+        is_np = not isinstance(x, torch.Tensor)
+        sq_pdists = self._initialize(x)
+        if not isinstance(sq_pdists, torch.Tensor):
+            sq_pdists = _to_device(sq_pdists, _torch_dtype(self.dtype))
+        theta = self.theta_
+        if isinstance(theta, np.ndarray):
+            theta = _to_device(theta, sq_pdists.dtype)
+        weights, info = gsp_learn_graph_log_degrees(
+            sq_pdists * theta,
+            1,
+            1,
+            edge_init=self.edge_init,
+            maxit=self.maxit,
+            tol=self.tol,
+            step_size=self.step_size,
+            edge_tol=self.edge_tol,
+            dtype=self.dtype,
+            return_info=True,
+        )
+        self.weights_ = weights.cpu().numpy() if is_np else weights
+        self.n_iter_, self.rel_primal_, self.rel_dual_ = info.n_iter, info.rel_primal, info.rel_dual
+        self.converged_ = info.converged
+        return self

@@ -1,0 +1,181 @@
+/* gl_b200.h -- C-ABI of the B200-native LogModel hot path (libgl_b200.so).
+ *
+ * The reference (LTS4/graph-learning) is pure Python: it has no FFI layer.  The boundary it
+ * offers for this path is a set of Python call surfaces; every entry point below sits directly
+ * underneath one of them and names the reference lines it replaces (paths relative to the
+ * reference tree).  INTEGRATION.md shows the ctypes stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no torch / C++ types.
+ *   - Every pointer named *_dev is a CUDA device pointer on the current device; *_host is host
+ *     memory.  `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - dtype: GL_F32 = 0, GL_F64 = 1.  Edge arrays (w, z) are stored and computed in that type;
+ *     node vectors (degrees, dual variable) and all residual sums are always float64.
+ *   - Return value 0 = success.  Non-zero = error code (GL_E_*); gl_last_error() returns the
+ *     message of the calling thread's last failure.  The Python layer maps GL_E_SHAPE to
+ *     ValueError (the reference raises ValueError for ndim > 2, smooth_learning.py:130-131)
+ *     and everything else to RuntimeError.
+ *   - "packed" = the reference's edge order: row-major strict upper triangle,
+ *     k(i,j) = i*n - i*(i+1)/2 + (j-i-1)  (operators.py:39-41, scipy squareform).
+ *   - "tiled" = this library's resident layout: 128x128 tiles (I<=J) of the upper triangle of
+ *     the node-pair grid, tiles in row-major triangle order, each tile row-major and contiguous
+ *     (64 KiB fp32).  Invalid slots (i>=j or j>=n) hold 0.  gl_tiled_elems(n) gives the size.
+ *   - There is NO CPU fallback: every compute entry point fails with GL_E_CUDA when no device
+ *     is usable.
+ */
+#ifndef GL_B200_H
+#define GL_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GL_F32 0
+#define GL_F64 1
+
+#define GL_OK 0
+#define GL_E_SHAPE 1   /* bad sizes / ndim  -> ValueError */
+#define GL_E_ARG 2     /* bad argument value */
+#define GL_E_CUDA 3    /* CUDA runtime error (message has the cudaError string) */
+#define GL_E_ALLOC 4
+#define GL_E_STATE 5   /* call order / workspace state */
+
+#define GL_TILE 128
+
+#define GL_LAYOUT_PACKED 0
+#define GL_LAYOUT_TILED 1
+
+typedef struct gl_solver gl_solver; /* opaque solver workspace (one per n, K, dtype, shard) */
+
+/* ---- library --------------------------------------------------------------------------- */
+int gl_version(void);
+const char *gl_last_error(void);
+/* Number of kernels this library has launched in this process (all threads).  bench.py reads
+ * it before/after the timed region to fill "gpu_launches".  Kernels replayed from a CUDA graph
+ * are counted per replay. */
+int64_t gl_launch_count(void);
+
+/* ---- sizes / layout -------------------------------------------------------------------- */
+int64_t gl_num_edges(int n);        /* n(n-1)/2 */
+int gl_nodes_from_edges(int64_t e); /* inverse, smooth_learning.py:133; -1 if not triangular */
+int gl_num_tiles(int n);            /* nT(nT+1)/2, nT = ceil(n/128) */
+int64_t gl_tiled_elems(int n);      /* gl_num_tiles(n) * 128 * 128 */
+/* Work-balanced contiguous tile range of shard `rank` out of `world` (diagonal tiles weigh
+ * half).  SURVEY 8(e): each GPU owns a contiguous edge shard. */
+int gl_shard_tiles(int n, int rank, int world, int *tile_begin, int *tile_end);
+
+/* packed <-> tiled for K graphs stored (K, E) / (K, tiled_elems).  Tiles [tile_begin,tile_end)
+ * only; `tiled_dev` points at the first tile of the shard. */
+int gl_pack_to_tiles(const void *packed_dev, void *tiled_dev, int n, int K, int dtype,
+                     int tile_begin, int tile_end, void *stream);
+int gl_tiles_to_packed(const void *tiled_dev, void *packed_dev, int n, int K, int dtype,
+                       int tile_begin, int tile_end, void *stream);
+/* tiled -> dense symmetric (n,n) with zero diagonal: scipy squareform(w), the return shape of
+ * the 1-D call (smooth_learning.py:171-172).  Entries below edge_tol are written as 0
+ * (smooth_learning.py:169); pass -INFINITY to keep everything. */
+int gl_tiles_to_square(const void *tiled_dev, void *square_dev, int n, int dtype, double edge_tol,
+                       void *stream);
+
+/* ---- edge <-> degree operator pair (smooth_learning.py:13-44, sum_squareform) ----------- */
+/* S w : (K,E) packed -> (K,n) weighted degrees.  Replaces `sum_op @ edge_w`
+ * (smooth_learning.py:144,148,154). */
+int gl_sum_op(const void *w_packed_dev, void *deg_dev, int n, int K, int dtype, void *stream);
+/* S^T d : (K,n) -> (K,E) packed, d_i + d_j per edge.  Replaces `sum_op_t @ d`
+ * (smooth_learning.py:147,153). */
+int gl_sum_op_adj(const void *d_dev, void *edge_packed_dev, int n, int K, int dtype, void *stream);
+/* Dense-Laplacian forms (operators.py:44-94).  lap (K,n,n), w (K,E) packed. */
+int gl_laplacian_from_packed(const void *w_packed_dev, void *lap_dev, int n, int K, int dtype,
+                             void *stream);                 /* operators.py:44-70 */
+int gl_laplacian_adjoint(const void *lap_dev, void *edge_packed_dev, int n, int K, int dtype,
+                         void *stream);                     /* operators.py:73-94 */
+
+/* ---- pairwise squared distances (smooth_learning.py:278: pdist(x.T)**2) ------------------ */
+/* X is (m, n) row-major with leading dimension ldx (elements), nodes are COLUMNS.
+ * row_scale (nullable, (m,)) and col_shift (nullable, (n,)) give
+ *   y[t, i] = row_scale[t] * (X[t, i] - col_shift[i])
+ * i.e. the responsibility-weighted, mean-centred signals of the GLMM M-step
+ * (clustering/glmm.py:61-68); Z_ij = sum_t (y[t,i] - y[t,j])^2.
+ * Output layout GL_LAYOUT_PACKED ((E,)) or GL_LAYOUT_TILED (tiles [tile_begin,tile_end)). */
+int gl_pdist_sq(const void *X_dev, int64_t m, int n, int64_t ldx, const void *row_scale_dev,
+                const void *col_shift_dev, void *Z_dev, int layout, int tile_begin, int tile_end,
+                int dtype, void *stream);
+
+/* ---- theta heuristic (smooth_learning.py:201-219, get_theta without blocks) --------------- */
+/* Z in either layout (full triangle).  Writes theta to *theta_host (synchronises). */
+int gl_theta(const void *Z_dev, int layout, int n, int avg_degree, int dtype, double *theta_host,
+             void *stream);
+/* Same statistic on a general dense (rows, cols) matrix with leading dimension ld, rows used as
+ * stored (no implicit diagonal): the per-block-pair call of the block form
+ * (smooth_learning.py:220-235, get_theta(sq_pdists[slice1, slice2], ...)). */
+int gl_theta_dense(const void *M_dev, int rows, int cols, int64_t ld, int avg_degree, int dtype,
+                   double *theta_host, void *stream);
+
+/* ---- the solver (smooth_learning.py:47-174, gsp_learn_graph_log_degrees) ----------------- */
+/* Workspace for K graphs on n nodes owning tiles [tile_begin, tile_end) of the triangle
+ * (0, gl_num_tiles(n) for a single GPU).  Allocates w, z (tiled) and all node vectors. */
+int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, int tile_end);
+int gl_solver_destroy(gl_solver *s);
+/* Device pointers of the resident tiled state of graph k (for zero-copy producers/consumers). */
+void *gl_solver_z_tiles(gl_solver *s, int k);
+void *gl_solver_w_tiles(gl_solver *s, int k);
+/* Load (theta-scaled) distances / initial weights from packed (K,E) device arrays.
+ * z_scale: nullable host array of K doubles multiplied into Z on load (theta per graph,
+ * smooth_learning.py:289, glmm.py:79, kgraphs.py:102).  w_packed_dev NULL = zeros
+ * (smooth_learning.py:140-143). */
+int gl_solver_load(gl_solver *s, const void *z_packed_dev, const double *z_scale_host,
+                   const void *w_packed_dev, void *stream);
+/* Same, when Z already sits in the solver's tiled buffer (gl_pdist_sq wrote it there). */
+int gl_solver_scale_z(gl_solver *s, const double *z_scale_host, void *stream);
+/* Set parameters and initialise the dual state d = S w (smooth_learning.py:135-144).
+ * For a sharded solver this leaves the LOCAL partial degrees in the exchange buffer; the
+ * caller all-reduces gl_solver_exchange_ptr() and then calls gl_solver_begin_finish(). */
+int gl_solver_begin(gl_solver *s, double alpha, double beta, double step_size, int maxit,
+                    double tol, void *stream);
+int gl_solver_begin_finish(gl_solver *s, void *stream);
+/* One iteration = edge pass, [all-reduce of the exchange buffer by the caller when sharded],
+ * node tail.  Both are stream-ordered kernel launches, capturable in a CUDA graph; they are
+ * no-ops on the device once the stop rule (smooth_learning.py:166) or maxit has fired. */
+int gl_solver_edge_pass(gl_solver *s, void *stream);
+int gl_solver_node_tail(gl_solver *s, void *stream);
+/* Exchange buffer: float64 [K*2*npad degrees partials | K*2 residual sums], to be summed over
+ * shards between edge pass and node tail.  *n_doubles receives its length. */
+void *gl_solver_exchange_ptr(gl_solver *s, int64_t *n_doubles);
+/* Single-GPU driver: runs iterations from an internally captured CUDA graph until the device
+ * stop flag is set; polls every `poll_every` iterations (<=0: default).  Synchronises. */
+int gl_solver_run(gl_solver *s, int poll_every, void *stream);
+/* Read back iteration count and the last relative residuals (synchronises the stream). */
+int gl_solver_status(gl_solver *s, int *n_iter, double *rel_primal, double *rel_dual,
+                     int *converged, void *stream);
+/* Results: packed (K,E) with the edge_tol threshold applied (smooth_learning.py:169); or the
+ * raw node state for tests. */
+int gl_solver_store(gl_solver *s, void *w_packed_dev, double edge_tol, void *stream);
+int gl_solver_node_state(gl_solver *s, double *d_dev /*(K,n)*/, void *stream);
+
+/* ---- one-shot conveniences (what the Python function calls) ------------------------------ */
+/* gsp_learn_graph_log_degrees on device arrays: distances (K,E) packed -> weights (K,E). */
+int gl_logmodel_solve(const void *z_packed_dev, const double *z_scale_host, int n, int K, int dtype,
+                      double alpha, double beta, const void *edge_init_packed_dev, int maxit,
+                      double tol, double step_size, double edge_tol, void *w_packed_dev,
+                      int *n_iter, double *rel_primal, double *rel_dual, void *stream);
+/* Same with HOST buffers (pageable or pinned): H2D of Z (and edge_init), solve, D2H of W.
+ * This is the end-to-end path bench.py times as "e2e". */
+int gl_logmodel_solve_host(const void *z_packed_host, const double *z_scale_host, int n, int K,
+                           int dtype, double alpha, double beta,
+                           const void *edge_init_packed_host, int maxit, double tol,
+                           double step_size, double edge_tol, void *w_packed_host, int *n_iter,
+                           double *rel_primal, double *rel_dual);
+
+/* ---- kNN-restricted support (config 5; no reference code) ---------------- */
+/* Edge list (ei < ej), nnz entries, z = theta-scaled squared distances of those edges.
+ * gamma = step / (2 beta + sqrt(2 d_max)).  w_dev in: initial (or zeros), out: result. */
+int gl_knn_logmodel_solve(const int32_t *ei_dev, const int32_t *ej_dev, const void *z_dev,
+                          int64_t nnz, int n, int dtype, double alpha, double beta, int maxit,
+                          double tol, double step_size, double edge_tol, void *w_dev, int *n_iter,
+                          double *rel_primal, double *rel_dual, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GL_B200_H */

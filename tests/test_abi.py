@@ -1,0 +1,79 @@
+"""The C-ABI library loads without a GPU and exports every symbol include/gl_b200.h declares;
+host-only entry points (sizes, shard planning) are checked against closed forms."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from graph_learning_b200 import _native
+    if not os.path.exists(_native.LIB_PATH):
+        _native.build()
+    return _native
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "gl_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gl_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported_and_bound(nat):
+    lib = nat.lib()
+    names = header_symbols()
+    assert len(names) >= 30
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in gl_b200.h but not exported"
+        assert name in nat.SIGNATURES, f"{name} has no ctypes signature in _native.py"
+    assert sorted(nat.SIGNATURES) == names
+
+
+def test_sizes(nat):
+    lib = nat.lib()
+    assert lib.gl_version() >= 100
+    for n in (2, 100, 128, 129, 2000, 20000):
+        e = n * (n - 1) // 2
+        nt = -(-n // 128)
+        assert lib.gl_num_edges(n) == e
+        assert lib.gl_nodes_from_edges(e) == n
+        assert lib.gl_num_tiles(n) == nt * (nt + 1) // 2
+        assert lib.gl_tiled_elems(n) == nt * (nt + 1) // 2 * 128 * 128
+    assert lib.gl_nodes_from_edges(7) == -1
+
+
+@pytest.mark.parametrize("n,world", [(100, 2), (2000, 2), (20000, 8), (20000, 3), (300, 8)])
+def test_shards_partition_the_triangle(nat, n, world):
+    lib = nat.lib()
+    total = lib.gl_num_tiles(n)
+    nt = -(-n // 128)
+    weights = np.array([1 if i == j else 2 for i in range(nt) for j in range(i, nt)])
+    prev_end, loads = 0, []
+    for r in range(world):
+        b, e = ctypes.c_int(), ctypes.c_int()
+        assert lib.gl_shard_tiles(n, r, world, ctypes.byref(b), ctypes.byref(e)) == 0
+        assert b.value == prev_end and e.value >= b.value
+        prev_end = e.value
+        loads.append(weights[b.value:e.value].sum())
+    assert prev_end == total
+    if total >= 8 * world:
+        assert max(loads) - min(loads) <= 0.02 * weights.sum() / world + 4
+
+
+def test_errors_without_device(nat):
+    """Argument errors are reported before any CUDA call; codes map to the reference's exceptions."""
+    lib = nat.lib()
+    h = ctypes.c_void_p()
+    assert lib.gl_solver_create(ctypes.byref(h), 1, 1, 0, 0, 0) == nat.GL_E_SHAPE
+    assert b"at least 2 nodes" in lib.gl_last_error()
+    with pytest.raises(ValueError):
+        nat.check(nat.GL_E_SHAPE)
+    assert lib.gl_solver_create(ctypes.byref(h), 100, 1, 7, 0, 1) == nat.GL_E_ARG
+    with pytest.raises(nat.GLError):
+        nat.check(nat.GL_E_ARG)
+    assert lib.gl_shard_tiles(100, 3, 2, None, None) == nat.GL_E_ARG

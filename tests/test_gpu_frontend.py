@@ -1,0 +1,174 @@
+"""GPU parity tests of the front end and the stand-alone operators: pairwise distances (K1),
+theta (K2), S / S^T and the dense-Laplacian pair, layout conversions, and LogModel.fit end to end
+against the reference's golden outputs.
+"""
+import numpy as np
+import pytest
+
+from oracle import logmodel_oracle as orc
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def sl():
+    import graph_learning_b200.smooth_learning as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import graph_learning_b200.operators as m
+    return m
+
+
+# ---- operators (reference tests/test_operators.py:25-72 properties + golden values) --------------
+def test_sum_operator_golden(golden, sl):
+    g = golden("operators_n23")
+    s, st = sl.sum_squareform(23)
+    assert s.shape == (23, 253) and st.shape == (253, 23)
+    assert rel(s @ g["w"].T, g["s_w"]) < 1e-14
+    assert rel(st @ g["dn"], g["st_d"]) < 1e-14
+    assert rel(s @ g["w"][0], g["s_w"][:, 0]) < 1e-14
+    assert rel(s.T @ g["dn"][:, 1], g["st_d"][:, 1]) < 1e-14
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_sum_operator_adjoint_identity(sl, seed):
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(20, 300))
+    s, st = sl.sum_squareform(n)
+    w = rng.standard_normal(n * (n - 1) // 2)
+    d = rng.standard_normal(n)
+    assert np.isclose(d @ (s @ w), w @ (st @ d), rtol=1e-11)
+
+
+def test_laplacian_pair_golden(golden, ops):
+    g = golden("operators_n23")
+    assert rel(ops.laplacian_squareform_vec(g["w"]), g["lap_vec"]) < 1e-14
+    assert rel(ops.laplacian_squareform(g["w"][0]), g["lap_single"]) < 1e-14
+    assert rel(ops.laplacian_squareform_adj_vec(g["dual"]), g["adj_vec"]) < 1e-14
+    assert rel(ops.laplacian_squareform_adj(g["dual"][0]), g["adj_single"]) < 1e-14
+    assert np.array_equal(ops.square_to_vec(g["dual"]), g["sq2vec"])
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_laplacian_adjoint_identity(ops, seed):
+    """<L, Lap(w)> == <w, Lap*(L)>  (reference tests/test_operators.py:44-72)."""
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(20, 100))
+    k = 3
+    w = rng.standard_normal((k, n * (n - 1) // 2))
+    dual = rng.standard_normal((k, n, n))
+    lhs = np.sum(dual * ops.laplacian_squareform_vec(w))
+    rhs = np.sum(w * ops.laplacian_squareform_adj_vec(dual))
+    assert np.isclose(lhs, rhs, rtol=1e-10)
+
+
+# ---- layout ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [2, 5, 128, 129, 300])
+def test_layout_round_trip(sl, n):
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    lib = nat.lib()
+    rng = np.random.default_rng(n)
+    e = n * (n - 1) // 2
+    w = torch.as_tensor(rng.standard_normal((2, e)), device="cuda")
+    tiles = torch.full((2, lib.gl_tiled_elems(n)), float("nan"), dtype=torch.float64, device="cuda")
+    nt = lib.gl_num_tiles(n)
+    nat.check(lib.gl_pack_to_tiles(w.data_ptr(), tiles.data_ptr(), n, 2, nat.GL_F64, 0, nt, None))
+    assert not torch.isnan(tiles).any()          # invalid slots are zeroed
+    assert torch.isclose(tiles.sum(), w.sum())
+    back = torch.zeros_like(w)
+    nat.check(lib.gl_tiles_to_packed(tiles.data_ptr(), back.data_ptr(), n, 2, nat.GL_F64, 0, nt, None))
+    assert torch.equal(back, w)
+    sq = torch.full((n, n), float("nan"), dtype=torch.float64, device="cuda")
+    nat.check(lib.gl_tiles_to_square(tiles.data_ptr(), sq.data_ptr(), n, nat.GL_F64, float("-inf"), None))
+    assert np.array_equal(sq.cpu().numpy(), orc.to_square(w[0].cpu().numpy()))
+
+
+# ---- distances -----------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["n60", "n33"])
+def test_pdist_golden(golden, sl, tag):
+    g = golden(f"logmodel_{tag}")
+    z = sl.pdist_sq(g["x"]).cpu().numpy()
+    assert rel(z, g["pdist_sq"]) < 1e-13
+    z32 = sl.pdist_sq(g["x"], dtype="float32").cpu().numpy()
+    assert rel(z32, g["pdist_sq"]) < 2e-6
+
+
+@pytest.mark.parametrize("m,n", [(1, 2), (17, 130), (300, 257), (1000, 100)])
+def test_pdist_shapes_vs_oracle(sl, m, n):
+    rng = np.random.default_rng(m * 1000 + n)
+    x = rng.standard_normal((m, n))
+    assert rel(sl.pdist_sq(x).cpu().numpy(), orc.pdist_sq(x)) < 1e-13
+
+
+def test_pdist_weighted_centred(sl):
+    """GLMM M-step form (glmm.py:61-68): y = resp[:, None] * (x - mean)."""
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((200, 40))
+    resp = rng.uniform(0.1, 1.0, size=200)
+    mean = rng.standard_normal(40)
+    y = resp[:, None] * (x - mean)
+    z = sl.pdist_sq(x, row_scale=resp, col_shift=mean).cpu().numpy()
+    assert rel(z, orc.pdist_sq(y)) < 1e-13
+
+
+# ---- theta -----------------------------------------------------------------------------------------
+def test_theta_golden(golden, sl):
+    g = golden("theta_n40")
+    for k, ref in zip(g["ks"], g["thetas"]):
+        th = sl.get_theta(g["zsq"], int(k))
+        if np.isfinite(ref):
+            assert abs(th - ref) < 1e-12 * abs(ref), (k, th, ref)
+        else:
+            assert not np.isfinite(th) or np.isnan(ref)
+    assert rel(sl.get_theta(g["zsq"], 3, blocks=g["blocks"]), g["theta_blocks"]) < 1e-12
+    deg = {(0, 0): 2, (0, 1): 3, (0, 2): 2, (1, 1): 4, (1, 2): 2, (2, 2): 3}
+    assert rel(sl.get_theta(g["zsq"], deg, blocks=g["blocks"]), g["theta_blocks_dict"]) < 1e-12
+
+
+def test_theta_packed_and_tiled_layouts(golden, sl):
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    g = golden("theta_n40")
+    lib = nat.lib()
+    zp = torch.as_tensor(orc.to_packed(g["zsq"]), device="cuda")
+    tiles = torch.zeros(lib.gl_tiled_elems(40), dtype=torch.float64, device="cuda")
+    nat.check(lib.gl_pack_to_tiles(zp.data_ptr(), tiles.data_ptr(), 40, 1, nat.GL_F64, 0, 1, None))
+    for k, ref in zip(g["ks"][1:], g["thetas"][1:]):
+        for ptr, layout in ((zp, nat.LAYOUT_PACKED), (tiles, nat.LAYOUT_TILED)):
+            th = ctypes.c_double()
+            nat.check(lib.gl_theta(ptr.data_ptr(), layout, 40, int(k), nat.GL_F64, ctypes.byref(th), None))
+            assert abs(th.value - ref) < 1e-12 * abs(ref)
+
+
+# ---- LogModel end to end -------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["n60", "n33"])
+def test_logmodel_fit_golden(golden, sl, tag):
+    g = golden(f"logmodel_{tag}")
+    mdl = sl.LogModel(avg_degree=int(g["avg_degree"])).fit(g["x"])
+    assert abs(mdl.theta_ - float(g["theta"])) < 1e-12 * float(g["theta"])
+    assert mdl.weights_.shape == g["weights"].shape
+    assert rel(mdl.weights_, g["weights"]) < 1e-9
+    assert np.array_equal(mdl.weights_ > 0, g["weights"] > 0)
+    none = sl.LogModel(avg_degree=None, maxit=40).fit(g["x"])
+    assert none.theta_ == 1
+    assert rel(none.weights_, g["weights_none"]) < 1e-10
+    m32 = sl.LogModel(avg_degree=int(g["avg_degree"]), dtype="float32").fit(g["x"])
+    assert rel(m32.weights_, g["weights"]) < 1e-4
+
+
+def test_logmodel_sklearn_protocol(sl):
+    from sklearn.base import clone
+    mdl = sl.LogModel(avg_degree=4, maxit=10)
+    assert mdl.get_params()["avg_degree"] == 4
+    c = clone(mdl).set_params(tol=1e-3)
+    assert c.tol == 1e-3 and c.maxit == 10

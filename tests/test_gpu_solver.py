@@ -1,0 +1,184 @@
+"""GPU parity tests of the solver (K3/K4 kernels) through the C-ABI, against the golden vectors of
+the unmodified reference and against the CPU oracle.  Tolerances (BASELINE.json north_star):
+fp64 <= 1e-9 relative on the weights, same iteration count; fp32 <= 1e-4 relative with identical
+edge support above edge_tol.
+"""
+import numpy as np
+import pytest
+
+from oracle import logmodel_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def sl():
+    import graph_learning_b200.smooth_learning as m
+    return m
+
+
+@pytest.mark.parametrize("its", [1, 2, 3, 5, 50])
+def test_iterates_fp64(golden, sl, its):
+    g = golden("solver_n100")
+    w, info = sl.gsp_learn_graph_log_degrees(g["z"] * g["theta"], 1, 1, maxit=its, edge_tol=-np.inf,
+                                             return_info=True)
+    assert info.n_iter == its
+    assert w.shape == (100, 100)
+    assert rel(w, g[f"w_raw_it{its}"]) < 1e-12
+
+
+def test_converged_fp64(golden, sl):
+    g = golden("solver_n100")
+    z = g["z"] * g["theta"]
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, return_info=True)
+    _, oinfo = orc.solve_two_pass(z)
+    assert info.converged and info.n_iter == oinfo.n_iter
+    assert rel(w, g["w_final"]) < 1e-9
+    assert np.array_equal(w > 0, g["w_final"] > 0)
+    assert np.allclose(w, w.T) and np.all(np.diag(w) == 0)
+    assert abs(info.rel_primal - oinfo.rel_primal) < 1e-6 * oinfo.rel_primal
+    assert abs(info.rel_dual - oinfo.rel_dual) < 1e-6 * oinfo.rel_dual
+
+
+def test_converged_fp32(golden, sl):
+    g = golden("solver_n100")
+    z = g["z"] * g["theta"]
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, dtype="float32", return_info=True)
+    _, oinfo = orc.solve_two_pass(z)
+    assert w.dtype == np.float32
+    assert abs(info.n_iter - oinfo.n_iter) <= 2
+    assert rel(w, g["w_final"]) < 1e-4
+    # identical support away from the threshold band
+    ref = g["w_final"]
+    band = np.abs(ref - 1e-3) < 1e-5
+    assert np.array_equal((w > 0)[~band], (ref > 0)[~band])
+
+
+def test_alt_parameters_and_warm_start(golden, sl):
+    g = golden("solver_n100")
+    z = g["z"] * g["theta"]
+    w = sl.gsp_learn_graph_log_degrees(z, 0.7, 1.9, maxit=400, tol=1e-6, step_size=0.8, edge_tol=1e-4)
+    assert rel(w, g["w_alt"]) < 1e-9
+    w = sl.gsp_learn_graph_log_degrees(z, 1, 1, edge_init=g["edge_init"].copy(), maxit=30)
+    assert rel(w, g["w_warm"]) < 1e-11
+
+
+def test_batched_shared_stop(golden, sl):
+    g = golden("batched_n30")
+    z = g["z"] * g["theta"]
+    for its in (1, 2, 7, 40):
+        w = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=its, edge_tol=-np.inf)
+        assert w.shape == z.shape
+        assert rel(w, g[f"w_raw_it{its}"]) < 1e-12
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, return_info=True)
+    _, oinfo = orc.solve_two_pass(z)
+    assert info.n_iter == oinfo.n_iter
+    assert rel(w, g["w"]) < 1e-9
+    w = sl.gsp_learn_graph_log_degrees(z, 1, 1, edge_init=g["edge_init"].copy(), maxit=25)
+    assert rel(w, g["w_warm"]) < 1e-11
+
+
+def test_ndim_error(sl):
+    with pytest.raises(ValueError, match="vector or matrix"):
+        sl.gsp_learn_graph_log_degrees(np.zeros((2, 2, 3)), 1, 1)
+
+
+@pytest.mark.parametrize("n", [2, 3, 127, 128, 129, 257, 300])
+def test_ragged_sizes_vs_oracle(sl, n):
+    """Tile-boundary cases: n below / at / above multiples of the 128-node tile."""
+    rng = np.random.default_rng(n)
+    pts = rng.uniform(size=(n, 3))
+    z = orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1)) * 4.0
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=60, edge_tol=-np.inf, return_info=True)
+    wo, oinfo = orc.solve_one_pass(z, maxit=60, threshold=False)
+    assert info.n_iter == oinfo.n_iter
+    assert rel(w, orc.to_square(wo)) < 1e-11
+
+
+def test_n2000_fp64_vs_c_oracle(sl):
+    """Config 2 size (n=2,000, E=1,999,000), maxit-limited, against the C one-sweep oracle."""
+    from oracle import c_oracle
+    rng = np.random.default_rng(7)
+    n = 2000
+    pts = rng.uniform(size=(n, 2))
+    z = orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1)) * 300.0
+    wo, it_o, rp_o, rd_o = c_oracle.solve(z, maxit=40, threshold=False)
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=40, edge_tol=-np.inf, return_info=True)
+    assert info.n_iter == it_o == 40
+    assert rel(orc.to_packed(w), wo) < 1e-10
+    assert abs(info.rel_primal - rp_o) < 1e-8 * rp_o
+    w32 = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=40, edge_tol=-np.inf, dtype="float32")
+    assert rel(orc.to_packed(w32), wo) < 1e-4
+
+
+def test_solver_handle_steps_equal_run(golden, sl):
+    """edge_pass + node_tail stepped by hand (the sharded path's schedule) == gl_solver_run."""
+    g = golden("solver_n100")
+    z = torch.as_tensor(g["z"] * g["theta"], device="cuda")
+    s = sl.Solver(100, 1, torch.float64)
+    s.load(z)
+    s.begin(maxit=50)
+    for _ in range(50):
+        s.edge_pass()
+        s.node_tail()
+    assert s.status().n_iter == 50
+    w = s.square(-np.inf).cpu().numpy()
+    assert rel(w, g["w_raw_it50"]) < 1e-12
+    # more steps after maxit are no-ops
+    s.edge_pass()
+    s.node_tail()
+    assert s.status().n_iter == 50
+    assert np.array_equal(s.square(-np.inf).cpu().numpy(), w)
+    s.close()
+
+
+def test_two_shards_one_gpu(golden, sl):
+    """Two tile shards of the same problem, exchange buffers summed by hand: the multi-GPU
+    schedule emulated on one device."""
+    rng = np.random.default_rng(11)
+    n = 300
+    pts = rng.uniform(size=(n, 2))
+    z_np = orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1)) * 40.0
+    z = torch.as_tensor(z_np, device="cuda")
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    shards = []
+    for r in range(2):
+        b, e = ctypes.c_int(), ctypes.c_int()
+        nat.check(nat.lib().gl_shard_tiles(n, r, 2, ctypes.byref(b), ctypes.byref(e)))
+        s = sl.Solver(n, 1, torch.float64, tile_range=(b.value, e.value))
+        s.load(z)
+        shards.append(s)
+    assert shards[0].tile_end == shards[1].tile_begin
+
+    def allreduce():
+        tot = shards[0].exchange() + shards[1].exchange()
+        for s in shards:
+            s.exchange().copy_(tot)
+
+    for s in shards:
+        s.begin(maxit=30, finish=False)
+    allreduce()
+    for s in shards:
+        s.begin_finish()
+    for _ in range(30):
+        for s in shards:
+            s.edge_pass()
+        allreduce()
+        for s in shards:
+            s.node_tail()
+    out = torch.zeros((1, n * (n - 1) // 2), dtype=torch.float64, device="cuda")
+    for s in shards:
+        s.store(-np.inf, out)
+    wo, _ = orc.solve_one_pass(z_np, maxit=30, threshold=False)
+    assert rel(out[0].cpu().numpy(), wo) < 1e-11
+    assert torch.equal(shards[0].node_state(), shards[1].node_state())
+    for s in shards:
+        s.close()
