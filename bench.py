@@ -1,0 +1,446 @@
+#!/usr/bin/env python
+"""bench.py -- LogModel edges*iterations/s on B200 (BASELINE.json metric).
+
+    python bench.py --gpus 1 --steps K --warmup W            # our arm
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU algorithm
+
+Workload (config 3 of BASELINE.json): LogModel dense, n = 20,000 nodes (E = 199,990,000 edges),
+m = 50,000 synthetic smooth signals (random-geometric-graph low-pass filtered noise), fp32.
+One "step" = one solver call of ITERS iterations (reference default maxit = 1000, tol = 0 so the
+count is fixed) over all E edges.  value = E * ITERS * steps / device time, Z already resident in
+HBM; e2e = the same through the reference-facing call with HOST buffers (H2D of packed Z, solve,
+D2H of the dense (n,n) weights the reference returns).  At N > 1 the triangle tiles are sharded
+over the ranks (weak = false: total work fixed -> "strong").
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=3)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--n", type=int, default=20000, help="nodes (config 3: 20000)")
+    p.add_argument("--m", type=int, default=50000, help="signals (config 3: 50000)")
+    p.add_argument("--iters", type=int, default=1000, help="solver iterations per step (maxit)")
+    p.add_argument("--avg-degree", type=int, default=8)
+    p.add_argument("--dtype", default="float32", choices=["float32", "float64"])
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--cpu-n", type=int, default=3000, help="nodes of the bounded CPU sample")
+    p.add_argument("--cpu-iters", type=int, default=8, help="iterations per CPU step")
+    return p.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the reference's algorithm (NumPy/SciPy restatement, oracle/logmodel_oracle.py
+# solve_two_pass == graph_learn/smooth_learning.py:125-169 with four CSR mat-vecs per iteration)
+# ---------------------------------------------------------------------------------------------------
+def cpu_sample_inputs(n_s: int, seed: int = 0):
+    """Bounded sample of the workload: the same kind of synthetic smooth-signal distances on a
+    leading sub-graph of n_s nodes (CPU throughput in edges*iters/s does not depend on n once the
+    edge vectors leave the caches)."""
+    from oracle import logmodel_oracle as orc
+    rng = np.random.default_rng(seed)
+    pts = rng.uniform(size=(n_s, 2))
+    # smooth signals: low-pass kernel features of the point cloud (m_s = 64), cheap to build
+    centres = rng.uniform(size=(64, 2))
+    x = np.exp(-((pts[None, :, :] - centres[:, None, :]) ** 2).sum(-1) / 0.05) + 0.01 * rng.standard_normal((64, n_s))
+    z = orc.pdist_sq(x)
+    theta = orc.theta_for_degree(orc.to_square(z), 8)
+    return z * theta
+
+
+def cpu_time_steps(n_s: int, iters: int, steps: int, warmup: int):
+    from oracle import logmodel_oracle as orc
+    z = cpu_sample_inputs(n_s)
+    op = orc.sum_operator(n_s)
+    for _ in range(warmup):
+        orc.solve_two_pass(z, maxit=max(1, iters // 4), tol=0.0, operator=op)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        orc.solve_two_pass(z, maxit=iters, tol=0.0, operator=op)
+    dt = time.perf_counter() - t0
+    return z.size * iters * steps / dt, dt
+
+
+def c_oracle_rate(n_s: int, iters: int):
+    """The OpenMP C restatement (one sweep, all host threads) -- a stronger CPU baseline than the
+    reference's own schedule; reported next to it, not instead of it."""
+    try:
+        from oracle import c_oracle
+        z = cpu_sample_inputs(n_s)
+        c_oracle.solve(z, maxit=2, tol=0.0, threshold=False)
+        t0 = time.perf_counter()
+        c_oracle.solve(z, maxit=iters, tol=0.0, threshold=False)
+        return z.size * iters / (time.perf_counter() - t0), c_oracle.threads()
+    except Exception:  # noqa: BLE001
+        return None, 0
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    value, dt = cpu_time_steps(a.cpu_n, a.cpu_iters, a.steps, min(a.warmup, 1))
+    e_s = a.cpu_n * (a.cpu_n - 1) // 2
+    sample = (f"n={a.cpu_n} leading sub-graph (E={e_s}), {a.cpu_iters} iterations per step, operator "
+              f"construction excluded; NumPy/SciPy restatement of smooth_learning.py:146-167 (fp64, CSR S/S^T)")
+    line = {
+        "impl": "reference",
+        "metric": "LogModel edges*iters/sec",
+        "value": value,
+        "unit": "edge*iters/s",
+        "n_gpus": a.gpus,
+        "steps": a.steps,
+        "warmup": a.warmup,
+        "ms_per_step": 1e3 * dt / a.steps,
+        "higher_is_better": True,
+        "scaling": "strong",
+        "vs_baseline": None,
+        "dtype": "f64",
+        "data": "synthetic",
+        "config": workload_config(a, cpu=True),
+        "cpu_baseline": {"value": value, "unit": "edge*iters/s", "cores": 1, "kind": "port",
+                         "host_cores": os.cpu_count(), "sample": sample},
+        "e2e": {"value": value, "unit": "edge*iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(a, cpu=False):
+    return {
+        "workload": f"config3: LogModel dense n={a.n} (E={a.n * (a.n - 1) // 2}), m={a.m}, "
+                    f"{a.dtype}, maxit={a.iters}, tol=0 (fixed iteration count), avg_degree={a.avg_degree}",
+        "n_nodes": a.n, "n_edges": a.n * (a.n - 1) // 2, "n_signals": a.m, "iters_per_step": a.iters,
+        "l2": "inputs (w+z = 1.6 GB fp32) exceed the 126 MB L2; no flush needed",
+        "parallelism": f"tile-shard x{a.gpus}",
+        **({"cpu_sample_nodes": a.cpu_n, "cpu_sample_iters": a.cpu_iters} if cpu else {}),
+    }
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # noqa: BLE001
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {
+            "hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+            "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def run_ours(a):
+    import ctypes
+
+    import torch
+    import torch.distributed as dist
+
+    from graph_learning_b200 import _native as nat
+    from graph_learning_b200.sharded import ShardedLogModelSolver
+    from graph_learning_b200.smooth_learning import (Solver, _wrap_device_memory,
+                                                     gsp_learn_graph_log_degrees)
+    from graph_learning_b200.synthetic import rgg_signals_filtered
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus and world > 1:
+        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = nat.lib()
+    tdt = torch.float32 if a.dtype == "float32" else torch.float64
+    gdt = nat.GL_F32 if a.dtype == "float32" else nat.GL_F64
+    esz = 4 if a.dtype == "float32" else 8
+    n, m = a.n, a.m
+    E = n * (n - 1) // 2
+    ntiles = lib.gl_num_tiles(n)
+    tt = nat.TILE * nat.TILE
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- synthetic inputs (setup, untimed except for the reported Z build) ----------------------
+    x = rgg_signals_filtered(n, m, seed=0, device=dev, dtype=tdt)
+    z_full = torch.empty(ntiles * tt, dtype=tdt, device=dev)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    torch.cuda.synchronize()
+    ev[0].record()
+    nat.check(lib.gl_pdist_sq(x.data_ptr(), m, n, x.stride(0), None, None, z_full.data_ptr(),
+                              nat.LAYOUT_TILED, 0, ntiles, gdt, None))
+    ev[1].record()
+    torch.cuda.synchronize()
+    z_ms = ev[0].elapsed_time(ev[1])
+    del x
+    th = ctypes.c_double()
+    t0 = time.perf_counter()
+    nat.check(lib.gl_theta(z_full.data_ptr(), nat.LAYOUT_TILED, n, a.avg_degree, gdt, ctypes.byref(th), None))
+    theta_ms = 1e3 * (time.perf_counter() - t0)
+    theta = th.value
+    z_full.mul_(theta)
+
+    # ---- resident solver state ---------------------------------------------------------------------
+    if world == 1:
+        solver = Solver(n, 1, tdt)
+        zt = _wrap_device_memory(solver.z_tiles_ptr(0), ntiles * tt, tdt, dev, owner=solver)
+        zt.copy_(z_full)
+        sharded = None
+    else:
+        sharded = ShardedLogModelSolver(n, tdt)
+        sharded.load_tiles(z_full)
+        solver = sharded.solver
+
+    def one_step():
+        if sharded is None:
+            _wrap_device_memory(solver.w_tiles_ptr(0), ntiles * tt, tdt, dev, owner=solver).zero_()
+            solver.begin(1.0, 1.0, 0.5, a.iters, 0.0)
+            solver.run()
+        else:
+            b, e = sharded.tile_range
+            _wrap_device_memory(solver.w_tiles_ptr(0), (e - b) * tt, tdt, dev, owner=solver).zero_()
+            sharded.begin(1.0, 1.0, 0.5, a.iters, 0.0)
+            sharded.run(20)
+
+    for _ in range(a.warmup):
+        one_step()
+    assert solver.status().n_iter == a.iters, solver.status()
+    clocks = ClockSampler(local)
+    barrier()
+    l0 = nat.launch_count()
+    sh0 = getattr(sharded, "launches", 0) if sharded else 0
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        one_step()
+    e1.record()
+    barrier()
+    clk = clocks.stop()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    launches = (nat.launch_count() - l0) + ((sharded.launches - sh0) if sharded else 0)
+    value = E * a.iters * a.steps / (ms * 1e-3)
+
+    # ---- dominant kernel alone: average edge-pass launch duration, CUDA events on its stream -----
+    solver.begin(1.0, 1.0, 0.5, 10 ** 6, 0.0, finish=(world == 1))
+    if world > 1:
+        dist.all_reduce(solver.exchange())
+        solver.begin_finish()
+    reps = 30
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for i in range(reps + 3):
+        if i >= 3:
+            evs[i - 3][0].record()
+        solver.edge_pass()
+        if i >= 3:
+            evs[i - 3][1].record()
+        if world > 1:
+            dist.all_reduce(solver.exchange())
+        solver.node_tail()
+    torch.cuda.synchronize()
+    edge_ms = float(np.mean([s.elapsed_time(e) for s, e in evs]))
+    local_edges = E if world == 1 else (sharded.tile_range[1] - sharded.tile_range[0]) * tt
+    hbm_peak, peak_src = peaks()
+    achieved = 3 * esz * local_edges / (edge_ms * 1e-3) / 1e9
+
+    line = {
+        "metric": "LogModel edges*iters/sec",
+        "value": value,
+        "unit": "edge*iters/s",
+        "n_gpus": world,
+        "steps": a.steps,
+        "warmup": a.warmup,
+        "ms_per_step": ms / a.steps,
+        "ms_per_iteration": ms / a.steps / a.iters,
+        "higher_is_better": True,
+        "scaling": "strong",
+        "vs_baseline": None,
+        "dtype": "f32" if a.dtype == "float32" else "f64",
+        "data": "synthetic",
+        "config": workload_config(a),
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "roofline": {
+            "bound": "hbm", "kernel": "gl::edge_pass_kernel", "achieved": achieved, "peak": hbm_peak,
+            "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
+            "frac_of_nominal_8TBps": achieved / 8000.0,
+            "bytes_per_edge": 3 * esz, "edges_per_launch": int(local_edges), "kernel_ms": edge_ms,
+            "whole_iteration_frac": (3 * esz * E / world) / (ms * 1e-3 / a.steps / a.iters) / 1e9 / hbm_peak,
+            "traffic": read_traffic(),
+        },
+        "setup": {"z_build_ms": z_ms, "z_build_algorithmic_tflops": 2.0 * E * m / (z_ms * 1e-3) / 1e12,
+                  "z_kernel": "gl::pdist_kernel (direct differences, FP32 FMA pipe)", "theta_ms": theta_ms,
+                  "theta": theta},
+    }
+
+    # ---- end to end through the reference-facing call, host buffers ---------------------------------
+    if not a.no_e2e:
+        if world == 1:
+            z_packed = torch.empty(E, dtype=tdt, device=dev)
+            nat.check(lib.gl_tiles_to_packed(z_full.data_ptr(), z_packed.data_ptr(), n, 1, gdt, 0, ntiles, None))
+            del z_full
+            z_host = torch.empty(E, dtype=tdt, pin_memory=True)
+            z_host.copy_(z_packed)
+            del z_packed
+            w_host = torch.empty((n, n), dtype=tdt, pin_memory=True)
+            torch.cuda.synchronize()
+
+            def e2e_step():
+                return gsp_learn_graph_log_degrees(z_host, 1, 1, maxit=a.iters, tol=0.0, dtype=a.dtype,
+                                                   out=w_host, return_info=True)
+
+            for _ in range(min(a.warmup, 2)):
+                e2e_step()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(a.steps):
+                _, info = e2e_step()
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            assert info.n_iter == a.iters
+            line["e2e"] = {"value": E * a.iters * a.steps / dt, "unit": "edge*iters/s",
+                           "h2d_bytes_per_step": int(E * esz), "d2h_bytes_per_step": int(n * n * esz),
+                           "ms_per_step": 1e3 * dt / a.steps,
+                           "api": "gsp_learn_graph_log_degrees(pinned host (E,) -> pinned host (n,n))"}
+        else:
+            b, e = sharded.tile_range
+            z_host = torch.empty((e - b) * tt, dtype=tdt, pin_memory=True)
+            z_host.copy_(z_full[b * tt:e * tt])
+            del z_full
+            w_host = torch.empty((e - b) * tt, dtype=tdt, pin_memory=True)
+            zdev = _wrap_device_memory(solver.z_tiles_ptr(0), (e - b) * tt, tdt, dev, owner=solver)
+            wdev = _wrap_device_memory(solver.w_tiles_ptr(0), (e - b) * tt, tdt, dev, owner=solver)
+
+            def e2e_step():
+                zdev.copy_(z_host, non_blocking=True)
+                wdev.zero_()
+                sharded.begin(1.0, 1.0, 0.5, a.iters, 0.0)
+                sharded.run(20)
+                w_host.copy_(wdev, non_blocking=True)
+                torch.cuda.synchronize()
+
+            e2e_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(a.steps):
+                e2e_step()
+            barrier()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            dt = float(dt.item())
+            line["e2e"] = {"value": E * a.iters * a.steps / dt, "unit": "edge*iters/s",
+                           "h2d_bytes_per_step": int((e - b) * tt * esz), "d2h_bytes_per_step": int((e - b) * tt * esz),
+                           "ms_per_step": 1e3 * dt / a.steps,
+                           "api": "ShardedLogModelSolver: pinned host tile shard -> solve -> pinned host tile shard (per rank bytes)"}
+
+    # ---- CPU baseline: the reference's algorithm on this box's host cores (rank 0, N = 1) -----------
+    if world == 1 and rank == 0 and not a.no_cpu_baseline:
+        v, dt = cpu_time_steps(a.cpu_n, a.cpu_iters, 1, 1)
+        vc, nthr = c_oracle_rate(a.cpu_n, 4 * a.cpu_iters)
+        line["cpu_baseline"] = {
+            "value": v, "unit": "edge*iters/s", "cores": 1, "kind": "port", "host_cores": os.cpu_count(),
+            "sample": f"n={a.cpu_n} leading sub-graph (E={a.cpu_n * (a.cpu_n - 1) // 2}), {a.cpu_iters} iterations, "
+                      "operator construction excluded; NumPy/SciPy restatement of smooth_learning.py:146-167 "
+                      "(fp64, four CSR mat-vecs per iteration, single-threaded like the reference)",
+            "c_openmp_oracle": {"value": vc, "threads": nthr,
+                                "note": "one-sweep C restatement with OpenMP, all host threads (stronger than the reference schedule)"},
+        }
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def read_traffic():
+    """dram bytes per launch of the edge pass from the committed ncu capture, if any."""
+    path = os.path.join(ROOT, "profiles", "edge_pass_traffic.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return json.load(f).get("dram_bytes_per_launch")
+        except Exception:  # noqa: BLE001
+            return None
+    return None
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

@@ -67,7 +67,7 @@ def _gl_dtype(t: torch.dtype) -> int:
 def _to_device(a, dtype: torch.dtype) -> torch.Tensor:
     """NumPy / torch -> contiguous CUDA tensor of ``dtype`` (copy only when needed)."""
     if isinstance(a, torch.Tensor):
-        return a.to(device=_device(), dtype=dtype).contiguous()
+        return a.to(device=_device(), dtype=dtype, non_blocking=True).contiguous()
     arr = np.ascontiguousarray(a)
     t = torch.from_numpy(arr)
     if arr.dtype != (np.float32 if dtype == torch.float32 else np.float64):
@@ -334,6 +334,7 @@ def gsp_learn_graph_log_degrees(
     *,
     dtype=None,
     return_info: bool = False,
+    out=None,
 ):
     r"""Weighted adjacency from squared pairwise distances under the smoothness prior
     (Kalofolias 2016): minimise :math:`\sum_{ij} w_{ij} z_{ij} - \alpha \sum_i \log(\sum_j w_{ij})
@@ -347,8 +348,12 @@ def gsp_learn_graph_log_degrees(
 
     ``dtype`` (extra): arithmetic type of the edge arrays, default float64 (the reference's);
     float32 halves the memory traffic.  ``return_info`` (extra): also return a :class:`SolveInfo`.
+    ``out`` (extra): preallocated result (e.g. a pinned CPU tensor) to copy the result into.
+    A CPU torch tensor as input is treated like a NumPy array (host in, host out) and is copied
+    asynchronously when pinned.
     """
     is_np = not isinstance(distances, torch.Tensor)
+    is_host_tensor = isinstance(distances, torch.Tensor) and not distances.is_cuda
     n_dim = len(distances.shape)
     if n_dim > 2:
         raise ValueError("Distances must be vector or matrix")
@@ -376,12 +381,20 @@ def gsp_learn_graph_log_degrees(
         solver.begin(alpha, beta, step_size, maxit, tol)
         solver.run()
         info = solver.status()
-        out = solver.square(edge_tol) if n_dim == 1 else solver.store(edge_tol)
+        result = solver.square(edge_tol) if n_dim == 1 else solver.store(edge_tol)
     finally:
         solver.close()
-    if is_np:
-        out = out.cpu().numpy()
-    return (out, info) if return_info else out
+    res = result
+    if out is not None:
+        out_t = torch.from_numpy(out) if isinstance(out, np.ndarray) else out
+        out_t.copy_(result, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        res = out
+    elif is_np:
+        res = result.cpu().numpy()
+    elif is_host_tensor:
+        res = result.cpu()
+    return (res, info) if return_info else res
 
 
 # --------------------------------------------------------------------------------------------

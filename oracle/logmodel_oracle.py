@@ -179,13 +179,16 @@ def solve_two_pass(
     *,
     threshold=True,
     history=None,
+    operator=None,
 ):
     """FBF primal-dual iteration exactly as the reference schedules it
     (smooth_learning.py:125-174): two applications of S and two of S^T per iteration.
 
     distances: (E,) or (K, E).  Returns (w, info) with w shaped like ``distances``
     (NOT expanded to (n, n); callers use ``to_square``).  ``history`` (a list) receives
-    (w, d) copies after every iteration when given.
+    (w, d) copies after every iteration when given.  ``operator`` = a prebuilt (S, S^T) pair
+    (bench.py times the iterations without the operator construction, which the reference redoes
+    on every call with O(n^2) interpreter work, smooth_learning.py:133).
     """
     z = np.asarray(distances, dtype=np.float64)
     if z.ndim > 2:
@@ -193,7 +196,7 @@ def solve_two_pass(
     batched = z.ndim == 2
     zt = z.T if batched else z  # (E, K) internally, smooth_learning.py:128-129
     n = n_nodes_from_edges(zt.shape[0])
-    s_op, st_op = sum_operator(n)
+    s_op, st_op = operator if operator is not None else sum_operator(n)
     g = _gamma(n, beta, step_size)
     c = 1.0 - 2.0 * g * beta
 
