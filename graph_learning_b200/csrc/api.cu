@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256) store_packed_kernel(const F *tiled, int64
 void free_all(gl_solver *s) {
   if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
-                  s->xch, s->cta_partial, s->gprev, s->resid, s->eig_scratch, s->flags};
+                  s->xch, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -144,6 +144,7 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
   if (rc == GL_OK) rc = alloc_zero(&s->b, s->esz * nk);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->xch, 8 * (size_t)s->xch_len);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->cta_partial, 16 * (size_t)(s->ntl ? s->ntl : 1));
+  if (rc == GL_OK) rc = alloc_zero((void **)&s->node_partial, 16 * (nk / 256 + 2));
   if (rc == GL_OK) rc = alloc_zero((void **)&s->gprev, 8 * 2 * KK);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->resid, 16);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->eig_scratch, 8 * 10 * KK + 8 * K);

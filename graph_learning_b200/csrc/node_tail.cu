@@ -26,6 +26,7 @@ struct NodeArgs {
   double *gprev;   // [Gram(W) | Gram(D)] of the previous iterate
   double *resid;   // rel_primal, rel_dual
   double *eig;     // scratch 4 x 2 x K*K
+  double *node_partial;  // [gridDim.x][2] (K == 1)
   int *flags;
   int n, npad, K, f32, init, maxit;
   double gamma, four_ag, tol;
@@ -149,8 +150,10 @@ __device__ void node_gram2(const double *x0, const double *x1, int K, int n, int
 __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs A) {
   __shared__ int s_last;
   __shared__ double s_lam[4];
+  __shared__ double s_blk[NODE_THREADS / 32][2];
   if (!A.init && *reinterpret_cast<volatile int *>(A.flags + FLAG_DONE)) return;
   const int tid = threadIdx.x;
+  double my_rb2 = 0.0, my_d2 = 0.0;
   const int64_t total = (int64_t)A.K * A.npad;
   const int64_t idx = (int64_t)blockIdx.x * NODE_THREADS + tid;
   if (idx < total) {
@@ -171,6 +174,8 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
       ybn = dn + A.gamma * sw;                       //                      :148
       pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;  //                   :151
     }
+    my_rb2 = rbv * rbv;
+    my_d2 = dn * dn;
     A.d[idx] = dn;
     A.yb[idx] = ybn;
     A.pb[idx] = pbn;
@@ -181,6 +186,24 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     } else {
       static_cast<double *>(A.a)[idx] = A.gamma * dn;
       static_cast<double *>(A.b)[idx] = A.gamma * pbn;
+    }
+  }
+  if (A.K == 1) {  // single graph: per-CTA partial sums, combined in fixed order by the last CTA
+    my_rb2 = warp_sum(my_rb2);
+    my_d2 = warp_sum(my_d2);
+    if ((tid & 31) == 0) {
+      s_blk[tid >> 5][0] = my_rb2;
+      s_blk[tid >> 5][1] = my_d2;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double r2 = 0.0, d2 = 0.0;
+      for (int q = 0; q < NODE_THREADS / 32; ++q) {
+        r2 += s_blk[q][0];
+        d2 += s_blk[q][1];
+      }
+      A.node_partial[2 * blockIdx.x] = r2;
+      A.node_partial[2 * blockIdx.x + 1] = d2;
     }
   }
   // ---- last CTA: residual norms, stop rule --------------------------------------------------
@@ -197,7 +220,33 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   const int KK = A.K * A.K;
   double *g_r = A.xch + 2 * total, *g_w = g_r + KK;   // edge-side Grams (summed over shards)
   double *g_rb = A.eig + 8 * (int64_t)KK, *g_d = g_rb + KK;  // node-side Grams, computed here
-  node_gram2(A.rb, A.d, A.K, A.n, A.npad, g_rb, g_d);
+  if (A.K == 1) {
+    double r2 = 0.0, d2 = 0.0;
+    for (int i = tid; i < (int)gridDim.x; i += NODE_THREADS) {
+      r2 += __ldcg(A.node_partial + 2 * i);
+      d2 += __ldcg(A.node_partial + 2 * i + 1);
+    }
+    r2 = warp_sum(r2);
+    d2 = warp_sum(d2);
+    __syncthreads();
+    if ((tid & 31) == 0) {
+      s_blk[tid >> 5][0] = r2;
+      s_blk[tid >> 5][1] = d2;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      r2 = d2 = 0.0;
+      for (int q = 0; q < NODE_THREADS / 32; ++q) {
+        r2 += s_blk[q][0];
+        d2 += s_blk[q][1];
+      }
+      g_rb[0] = r2;
+      g_d[0] = d2;
+    }
+    __syncthreads();
+  } else {
+    node_gram2(A.rb, A.d, A.K, A.n, A.npad, g_rb, g_d);
+  }
 
   const int it = A.flags[FLAG_IT];
   if (!A.init && it >= 1) {
@@ -241,6 +290,7 @@ int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
   A.d = s->d; A.yb = s->yb; A.pb = s->pb; A.rb = s->rb;
   A.a = s->a; A.b = s->b;
   A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.eig = s->eig_scratch;
+  A.node_partial = s->node_partial;
   A.flags = s->flags;
   A.n = s->n; A.npad = s->npad; A.K = s->K; A.f32 = (s->dtype == GL_F32);
   A.init = init ? 1 : 0;

@@ -30,6 +30,7 @@ struct gl_solver {
   double *xch = nullptr;
   int64_t xch_len = 0;
   double *cta_partial = nullptr;  // [ntl][2] per-CTA residual sums of the edge pass (K == 1)
+  double *node_partial = nullptr; // [node CTAs][2] per-CTA dual residual sums of the node tail (K == 1)
   double *gprev = nullptr;        // [2][K*K]: Gram(W), Gram(D) of the previous iterate (denominators)
   double *resid = nullptr;        // [2]: rel_primal, rel_dual of the last checked iteration
   double *eig_scratch = nullptr;  // [4][2][K*K] repeated-squaring buffers
