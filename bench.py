@@ -341,7 +341,7 @@ def run_ours(a):
             "frac_of_nominal_8TBps": achieved / 8000.0,
             "bytes_per_edge": 3 * esz, "edges_per_launch": int(local_edges), "kernel_ms": edge_ms,
             "whole_iteration_frac": (3 * esz * E / world) / (ms * 1e-3 / a.steps / a.iters) / 1e9 / hbm_peak,
-            "traffic": read_traffic(),
+            "traffic": read_traffic(1.0 if world == 1 else local_edges / float(ntiles * tt)),
         },
         "setup": {"z_build_ms": z_ms, "z_build_algorithmic_tflops": 2.0 * E * m / (z_ms * 1e-3) / 1e12,
                   "z_kernel": "gl::pdist_kernel (direct differences, FP32 FMA pipe)", "theta_ms": theta_ms,
@@ -421,18 +421,28 @@ def run_ours(a):
                                 "note": "one-sweep C restatement with OpenMP, all host threads (stronger than the reference schedule)"},
         }
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # tear down in order: captured graphs (they hold NCCL work) -> sync -> barrier -> group;
+        # then leave without running interpreter finalisers that could wait on the communicator.
+        sharded.close()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
-def read_traffic():
-    """dram bytes per launch of the edge pass from the committed ncu capture, if any."""
+def read_traffic(fraction=1.0):
+    """dram bytes per launch of the edge pass from the committed ncu capture (taken at N = 1, all
+    tiles), scaled by the fraction of the tiles this rank's launch covers."""
     path = os.path.join(ROOT, "profiles", "edge_pass_traffic.json")
     if os.path.exists(path):
         try:
             with open(path) as f:
-                return json.load(f).get("dram_bytes_per_launch")
+                v = json.load(f).get("dram_bytes_per_launch")
+                return None if v is None else v * fraction
         except Exception:  # noqa: BLE001
             return None
     return None
