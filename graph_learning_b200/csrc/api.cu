@@ -53,8 +53,10 @@ __global__ void __launch_bounds__(256) store_packed_kernel(const F *tiled, int64
 
 void free_all(gl_solver *s) {
   if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+  for (void *p : s->ipc_opened)
+    if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
-                  s->xch, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags};
+                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -142,7 +144,9 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
   if (rc == GL_OK) rc = alloc_zero((void **)&s->rb, 8 * nk);
   if (rc == GL_OK) rc = alloc_zero(&s->a, s->esz * nk);
   if (rc == GL_OK) rc = alloc_zero(&s->b, s->esz * nk);
-  if (rc == GL_OK) rc = alloc_zero((void **)&s->xch, 8 * (size_t)s->xch_len);
+  s->xch_stride = (s->xch_len + 31) / 32 * 32;
+  if (rc == GL_OK) rc = alloc_zero((void **)&s->comm, 8 * (size_t)(COMM_HDR + 2 * s->xch_stride));
+  if (rc == GL_OK) s->xch = s->comm + COMM_HDR;
   if (rc == GL_OK) rc = alloc_zero((void **)&s->cta_partial, 16 * (size_t)(s->ntl ? s->ntl : 1));
   if (rc == GL_OK) rc = alloc_zero((void **)&s->node_partial, 16 * (nk / 256 + 2));
   if (rc == GL_OK) rc = alloc_zero((void **)&s->gprev, 8 * 2 * KK);
@@ -226,11 +230,14 @@ int gl_solver_begin(gl_solver *s, double alpha, double beta, double step_size, i
     cudaGraphExecDestroy(s->graph_exec);
     s->graph_exec = nullptr;
   }
-  GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
+  // peer mode: the buffer of the coming exchange was cleared by the previous node tail and the
+  // other one may still be read by a peer -- never touch them from the host side
+  if (s->world <= 1) GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
   GL_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
   if (s->K > 1 && s->ntl) GL_CUDA(cudaMemsetAsync(s->r, 0, (size_t)s->K * s->gstride * s->esz, st));
   GL_TRY(launch_edge_init(s, st));   // local partial of S w0 (and ||w0||^2 for K == 1)
   GL_TRY(launch_gram_edges(s, st));  // K > 1: Gram(W0)
+  GL_TRY(launch_signal(s, st));      // peer mode: publish the initial partials
   return GL_OK;
 }
 
@@ -251,6 +258,62 @@ int gl_solver_edge_pass(gl_solver *s, void *stream) {
 int gl_solver_node_tail(gl_solver *s, void *stream) {
   if (!s || !s->begun) return fail(GL_E_STATE, "gl_solver_begin/begin_finish must be called first");
   return launch_node_tail(s, false, as_stream(stream));
+}
+
+void *gl_solver_comm_ptr(gl_solver *s, int64_t *n_bytes) {
+  if (!s) return nullptr;
+  if (n_bytes) *n_bytes = 8 * (int64_t)(COMM_HDR + 2 * s->xch_stride);
+  return s->comm;
+}
+
+int gl_solver_comm_handle(gl_solver *s, void *handle64) {
+  if (!s || !handle64) return fail(GL_E_ARG, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  GL_CUDA(cudaIpcGetMemHandle(&h, s->comm));
+  std::memcpy(handle64, &h, sizeof(h));
+  return GL_OK;
+}
+
+int gl_solver_comm_connect_ptrs(gl_solver *s, int rank, int world, void *const *comm_ptrs) {
+  if (!s) return fail(GL_E_ARG, "null solver");
+  if (world < 1 || world > GL_MAX_PEERS || rank < 0 || rank >= world)
+    return fail(GL_E_ARG, "peer exchange supports 1..%d ranks (got rank %d of %d)", GL_MAX_PEERS, rank, world);
+  if (world > 1 && s->K != 1) return fail(GL_E_ARG, "peer exchange needs a single graph (K == 1)");
+  if (s->graph_exec) {
+    cudaGraphExecDestroy(s->graph_exec);
+    s->graph_exec = nullptr;
+  }
+  s->peers = PeerView{};
+  for (int r = 0; r < world; ++r) {
+    double *base = (r == rank) ? s->comm : static_cast<double *>(comm_ptrs[r]);
+    if (!base) return fail(GL_E_ARG, "null comm pointer for rank %d", r);
+    s->peers.hdr[r] = reinterpret_cast<int *>(base);
+    s->peers.xch[r] = base + COMM_HDR;
+  }
+  s->world = world;
+  s->rank = rank;
+  s->begun = false;
+  return GL_OK;
+}
+
+int gl_solver_comm_connect(gl_solver *s, int rank, int world, const void *handles) {
+  if (!s || !handles) return fail(GL_E_ARG, "null argument");
+  if (world < 1 || world > GL_MAX_PEERS || rank < 0 || rank >= world)
+    return fail(GL_E_ARG, "peer exchange supports 1..%d ranks (got rank %d of %d)", GL_MAX_PEERS, rank, world);
+  void *ptrs[GL_MAX_PEERS] = {};
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) continue;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, static_cast<const char *>(handles) + 64 * r, sizeof(h));
+    if (s->ipc_opened[r]) {
+      cudaIpcCloseMemHandle(s->ipc_opened[r]);
+      s->ipc_opened[r] = nullptr;
+    }
+    GL_CUDA(cudaIpcOpenMemHandle(&ptrs[r], h, cudaIpcMemLazyEnablePeerAccess));
+    s->ipc_opened[r] = ptrs[r];
+  }
+  return gl_solver_comm_connect_ptrs(s, rank, world, ptrs);
 }
 
 void *gl_solver_exchange_ptr(gl_solver *s, int64_t *n_doubles) {
@@ -358,6 +421,7 @@ int gl_solver_status(gl_solver *s, int *n_iter, double *rel_primal, double *rel_
   GL_CUDA(cudaMemcpyAsync(hf, s->flags, sizeof(hf), cudaMemcpyDeviceToHost, st));
   GL_CUDA(cudaMemcpyAsync(hr, s->resid, sizeof(hr), cudaMemcpyDeviceToHost, st));
   GL_CUDA(cudaStreamSynchronize(st));
+  if (hf[FLAG_ERROR]) return fail(GL_E_STATE, "peer exchange timed out waiting for another rank");
   if (n_iter) *n_iter = hf[FLAG_IT];
   if (converged) *converged = hf[FLAG_CONVERGED];
   if (rel_primal) *rel_primal = hr[0];

@@ -98,6 +98,22 @@ __device__ __forceinline__ double2 ld_stream(const double2 *p) { return __ldcs(p
 __device__ __forceinline__ void st_stream(float4 *p, const float4 &v) { __stcs(p, v); }
 __device__ __forceinline__ void st_stream(double2 *p, const double2 &v) { __stcs(p, v); }
 
+// ---- system-scope accesses for the peer (NVLink) exchange ------------------------------------------
+__device__ __forceinline__ void st_release_sys(int *p, int v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int *p) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double *p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int ld_volatile_int(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
+
 // ---- warp helpers ---------------------------------------------------------------------------------
 template <typename V> __device__ __forceinline__ V warp_sum(V v) {
 #pragma unroll

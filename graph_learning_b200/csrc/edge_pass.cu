@@ -26,9 +26,12 @@ template <typename F> struct EdgeArgs {
   F *r;  // batch mode: q - y
   int64_t gstride;
   const F *a, *b;          // gamma*d, gamma*pb   [K][npad]
-  double *sp, *sw;         // degree accumulators [K][npad]
+  double *xch;             // exchange buffer 0: [S p | S w' | G_r | G_w]; buffer 1 at +xch_stride
+  int64_t xch_stride;
   double *cta_partial;     // [ntl][2]
-  double *gsum;            // xch: G_r, G_w (K == 1: two scalars)
+  int *hdr;                // comm header (peer mode)
+  int world, rank;
+  PeerView peers;
   const int2 *tile_ij;
   int *flags;
   int n, npad, ntl;
@@ -169,6 +172,11 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
 
   const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
   const int t = blockIdx.x, k = blockIdx.y;
+  // peer mode: accumulate into the buffer of the current exchange parity
+  const int seq = A.world > 1 ? ld_volatile_int(A.hdr + HDR_SEQ) : 0;
+  double *const xb = A.xch + (seq & 1) * A.xch_stride;
+  double *const g_sp = xb, *const g_sw = xb + (int64_t)gridDim.y * A.npad;
+  double *const g_sum = xb + 2 * (int64_t)gridDim.y * A.npad;
   const int2 ij = A.tile_ij[t];
   const int I = ij.x, J = ij.y;
   const bool masked = (I == J) || ((J + 1) * T > A.n);
@@ -203,7 +211,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
     const int r = wp * ROWS_PER_WARP + (lane & 3) * 4 + ((lane >> 3) & 3);
     const int qty = (lane >> 2) & 1;
     const int gi = I * T + r;
-    if (gi < A.n) atomicAdd((qty ? A.sw : A.sp) + (int64_t)k * A.npad + gi, (double)rowfinal);
+    if (gi < A.n) atomicAdd((qty ? g_sw : g_sp) + (int64_t)k * A.npad + gi, (double)rowfinal);
   }
   // ---- column totals: 8 warps -> shared -> one atomic per (column, quantity) ------------------
 #pragma unroll
@@ -226,9 +234,13 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
 #pragma unroll
     for (int q = 0; q < EDGE_THREADS / 32; ++q) acc += (double)s_col[q][qty][col];
     const int gj = J * T + col;
-    if (gj < A.n) atomicAdd((qty ? A.sw : A.sp) + (int64_t)k * A.npad + gj, acc);
+    if (gj < A.n) atomicAdd((qty ? g_sw : g_sp) + (int64_t)k * A.npad + gj, acc);
   }
   if (BATCH) return;
+  if (A.world > 1) {  // the ticket below must be ordered after EVERY thread's atomics
+    __threadfence();
+    __syncthreads();
+  }
 
   // ---- residual sums: fixed-order two-stage reduction (deterministic) -------------------------
   if (tid == 0) {
@@ -266,9 +278,13 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
       r2 += s_red[q][0];
       w2 += s_red[q][1];
     }
-    A.gsum[0] += r2;  // xch slot is zeroed by the node tail; += keeps the sharded sum convention
-    A.gsum[1] += w2;
+    g_sum[0] += r2;  // xch slot is zeroed by the node tail; += keeps the sharded sum convention
+    g_sum[1] += w2;
     A.flags[FLAG_EDGE_TICKET] = 0;
+    if (A.world > 1) {  // publish: this rank's partials of exchange `seq` are complete
+      __threadfence_system();
+      for (int r = 0; r < A.world; ++r) st_release_sys(A.peers.hdr[r] + A.rank, seq + 1);
+    }
   }
 }
 
@@ -276,8 +292,12 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
 // Not on the per-iteration path; one warp per tile row, plain shuffles.
 template <typename F>
 __global__ void __launch_bounds__(EDGE_THREADS) edge_init_kernel(const F *w, int64_t gstride,
-                                                                 const int2 *tile_ij, double *sw,
-                                                                 double *gw, int n, int npad, int K) {
+                                                                 const int2 *tile_ij, double *xch,
+                                                                 int64_t xch_stride, const int *hdr, int world,
+                                                                 int n, int npad, int K) {
+  double *const xb = xch + (world > 1 ? (ld_volatile_int(hdr + HDR_SEQ) & 1) : 0) * xch_stride;
+  double *const sw = xb + (int64_t)K * npad;
+  double *const gw = xb + 2 * (int64_t)K * npad + (int64_t)K * K;
   __shared__ double s_col[T];
   __shared__ double s_sq;
   const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
@@ -321,10 +341,13 @@ template <typename F> static int edge_pass_t(gl_solver *s, cudaStream_t st) {
   A.gstride = s->gstride;
   A.a = static_cast<const F *>(s->a);
   A.b = static_cast<const F *>(s->b);
-  A.sp = s->xch;
-  A.sw = s->xch + (int64_t)s->K * s->npad;
+  A.xch = s->xch;
+  A.xch_stride = s->xch_stride;
   A.cta_partial = s->cta_partial;
-  A.gsum = s->xch + 2 * (int64_t)s->K * s->npad;
+  A.hdr = reinterpret_cast<int *>(s->comm);
+  A.world = s->world;
+  A.rank = s->rank;
+  A.peers = s->peers;
   A.tile_ij = s->tile_ij;
   A.flags = s->flags;
   A.n = s->n;
@@ -349,14 +372,30 @@ int launch_edge_pass(gl_solver *s, cudaStream_t st) {
 int launch_edge_init(gl_solver *s, cudaStream_t st) {
   if (s->ntl == 0) return GL_OK;
   dim3 grid(s->ntl, s->K);
-  double *sw = s->xch + (int64_t)s->K * s->npad;
-  double *gw = s->xch + 2 * (int64_t)s->K * s->npad + (int64_t)s->K * s->K;
+  const int *hdr = reinterpret_cast<const int *>(s->comm);
   if (s->dtype == GL_F32)
     edge_init_kernel<float><<<grid, EDGE_THREADS, 0, st>>>(static_cast<const float *>(s->w), s->gstride,
-                                                          s->tile_ij, sw, gw, s->n, s->npad, s->K);
+                                                          s->tile_ij, s->xch, s->xch_stride, hdr, s->world,
+                                                          s->n, s->npad, s->K);
   else
     edge_init_kernel<double><<<grid, EDGE_THREADS, 0, st>>>(static_cast<const double *>(s->w), s->gstride,
-                                                           s->tile_ij, sw, gw, s->n, s->npad, s->K);
+                                                           s->tile_ij, s->xch, s->xch_stride, hdr, s->world,
+                                                           s->n, s->npad, s->K);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+// peer mode: publish "my partials of the current exchange are complete" after a plain kernel
+// (the initial-degree pass); the iteration's edge pass does this from its last CTA instead.
+__global__ void signal_kernel(int *hdr, PeerView peers, int world, int rank) {
+  __threadfence_system();
+  const int seq = ld_volatile_int(hdr + HDR_SEQ);
+  for (int r = 0; r < world; ++r) st_release_sys(peers.hdr[r] + rank, seq + 1);
+}
+
+int launch_signal(gl_solver *s, cudaStream_t st) {
+  if (s->world <= 1) return GL_OK;
+  signal_kernel<<<1, 1, 0, st>>>(reinterpret_cast<int *>(s->comm), s->peers, s->world, s->rank);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }

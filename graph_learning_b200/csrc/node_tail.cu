@@ -27,6 +27,10 @@ struct NodeArgs {
   double *resid;   // rel_primal, rel_dual
   double *eig;     // scratch 4 x 2 x K*K
   double *node_partial;  // [gridDim.x][2] (K == 1)
+  int *hdr;              // comm header (peer mode)
+  int64_t xch_stride;
+  int world, rank;
+  PeerView peers;
   int *flags;
   int n, npad, K, f32, init, maxit;
   double gamma, four_ag, tol;
@@ -156,11 +160,44 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   double my_rb2 = 0.0, my_d2 = 0.0;
   const int64_t total = (int64_t)A.K * A.npad;
   const int64_t idx = (int64_t)blockIdx.x * NODE_THREADS + tid;
+  // ---- peer mode: wait until every rank has published its partials of this exchange, then read
+  //      them straight out of the peers' memory over NVLink (fixed rank order -> bit-identical
+  //      replicated state on all ranks).  Buffers alternate by exchange parity; the one NOT being
+  //      read is cleared here for the next edge pass (all peers are past reading it).
+  int seq = 0;
+  int64_t rd_off = 0, clr_off = 0;
+  if (A.world > 1) {
+    seq = ld_volatile_int(A.hdr + HDR_SEQ);
+    rd_off = (seq & 1) * A.xch_stride;
+    clr_off = ((seq + 1) & 1) * A.xch_stride;
+    if (tid < A.world) {
+      const long long t0 = clock64();
+      while (ld_acquire_sys(A.hdr + tid) < seq + 1) {
+        if (clock64() - t0 > 6000000000LL) {  // ~3 s: a peer died; fail instead of hanging the GPU
+          A.flags[FLAG_ERROR] = 1;
+          break;
+        }
+      }
+    }
+    __syncthreads();
+  }
   if (idx < total) {
     const int v = (int)(idx % A.npad);
-    const double sp = A.xch[idx], sw = A.xch[total + idx];
-    A.xch[idx] = 0.0;
-    A.xch[total + idx] = 0.0;
+    double sp, sw;
+    if (A.world > 1) {
+      sp = sw = 0.0;
+      for (int r = 0; r < A.world; ++r) {
+        sp += ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
+        sw += ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
+      }
+      A.xch[clr_off + idx] = 0.0;
+      A.xch[clr_off + total + idx] = 0.0;
+    } else {
+      sp = A.xch[idx];
+      sw = A.xch[total + idx];
+      A.xch[idx] = 0.0;
+      A.xch[total + idx] = 0.0;
+    }
     double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
     if (v < A.n) {
       if (A.init) {
@@ -220,6 +257,22 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   const int KK = A.K * A.K;
   double *g_r = A.xch + 2 * total, *g_w = g_r + KK;   // edge-side Grams (summed over shards)
   double *g_rb = A.eig + 8 * (int64_t)KK, *g_d = g_rb + KK;  // node-side Grams, computed here
+  double *g_clear = g_r;
+  if (A.world > 1) {  // K == 1: sum the two edge-side scalars over the ranks into local scratch
+    g_clear = A.xch + clr_off + 2 * total;
+    g_r = A.node_partial + 2 * (int64_t)gridDim.x;
+    g_w = g_r + 1;
+    if (tid == 0) {
+      double r2 = 0.0, w2 = 0.0;
+      for (int r = 0; r < A.world; ++r) {
+        r2 += ld_relaxed_sys(A.peers.xch[r] + rd_off + 2 * total);
+        w2 += ld_relaxed_sys(A.peers.xch[r] + rd_off + 2 * total + 1);
+      }
+      g_r[0] = r2;
+      g_w[0] = w2;
+    }
+    __syncthreads();
+  }
   if (A.K == 1) {
     double r2 = 0.0, d2 = 0.0;
     for (int i = tid; i < (int)gridDim.x; i += NODE_THREADS) {
@@ -260,9 +313,13 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     A.gprev[KK + e] = g_d[e];
   }
   __syncthreads();
-  for (int e = tid; e < 2 * KK; e += NODE_THREADS) g_r[e] = 0.0;
+  for (int e = tid; e < 2 * KK; e += NODE_THREADS) g_clear[e] = 0.0;
   if (tid == 0) {
     A.flags[FLAG_NODE_TICKET] = 0;
+    if (A.world > 1) {
+      if (ld_volatile_int(A.flags + FLAG_ERROR)) A.flags[FLAG_DONE] = 1;
+      A.hdr[HDR_SEQ] = seq + 1;  // this exchange is consumed
+    }
     if (A.init) {
       A.flags[FLAG_IT] = 0;
       A.flags[FLAG_CONVERGED] = 0;
@@ -291,6 +348,11 @@ int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
   A.a = s->a; A.b = s->b;
   A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.eig = s->eig_scratch;
   A.node_partial = s->node_partial;
+  A.hdr = reinterpret_cast<int *>(s->comm);
+  A.xch_stride = s->xch_stride;
+  A.world = s->world;
+  A.rank = s->rank;
+  A.peers = s->peers;
   A.flags = s->flags;
   A.n = s->n; A.npad = s->npad; A.K = s->K; A.f32 = (s->dtype == GL_F32);
   A.init = init ? 1 : 0;

@@ -9,7 +9,19 @@ enum {
   FLAG_CONVERGED = 2,   // stop rule (smooth_learning.py:166) fired
   FLAG_EDGE_TICKET = 3, // last-CTA-done counter of the edge pass
   FLAG_NODE_TICKET = 4, // last-CTA-done counter of the node tail
+  FLAG_ERROR = 5,       // peer exchange timed out
   FLAG_COUNT = 8
+};
+
+// Peer (NVLink) exchange: every rank owns one "comm block" = [header | xch buffer 0 | xch buffer 1].
+// Header ints: sig[r] (r < 8) = last exchange sequence number rank r has published to this rank;
+// HDR_SEQ = number of exchanges this rank has consumed (buffer parity = seq & 1).
+constexpr int GL_MAX_PEERS = 8;
+constexpr int COMM_HDR = 64;  // doubles (512 B)
+constexpr int HDR_SEQ = 16;
+struct PeerView {
+  double *xch[GL_MAX_PEERS];  // base of every rank's xch buffer 0 (peer-mapped)
+  int *hdr[GL_MAX_PEERS];     // base of every rank's header
 };
 
 struct gl_solver {
@@ -27,8 +39,12 @@ struct gl_solver {
   double *d = nullptr, *yb = nullptr, *pb = nullptr, *rb = nullptr;  // [K][npad]
   void *a = nullptr, *b = nullptr;  // [K][npad] edge dtype: gamma*d, gamma*pb
   // exchange buffer (float64): [sp K*npad | sw K*npad | G_r K*K | G_w K*K]
+  double *comm = nullptr;  // the comm block; xch = comm + COMM_HDR
   double *xch = nullptr;
-  int64_t xch_len = 0;
+  int64_t xch_len = 0, xch_stride = 0;
+  int world = 1, rank = 0;  // > 1 ranks: peer mode (exchange over mapped peer memory, K == 1)
+  PeerView peers = {};
+  void *ipc_opened[GL_MAX_PEERS] = {};
   double *cta_partial = nullptr;  // [ntl][2] per-CTA residual sums of the edge pass (K == 1)
   double *node_partial = nullptr; // [node CTAs][2] per-CTA dual residual sums of the node tail (K == 1)
   double *gprev = nullptr;        // [2][K*K]: Gram(W), Gram(D) of the previous iterate (denominators)
@@ -50,6 +66,7 @@ struct gl_solver {
 namespace gl {
 int launch_edge_pass(gl_solver *s, cudaStream_t st);
 int launch_edge_init(gl_solver *s, cudaStream_t st);
+int launch_signal(gl_solver *s, cudaStream_t st);
 int launch_gram_edges(gl_solver *s, cudaStream_t st);
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
 int fill_tile_table(gl_solver *s);

@@ -57,7 +57,10 @@ class ShardedLogModelSolver:
     """CUDA backend: one :class:`~graph_learning_b200.smooth_learning.Solver` per rank over its tile
     shard, iterations captured in a CUDA graph together with the NCCL all-reduce."""
 
-    def __init__(self, n: int, dtype=torch.float32, n_graphs: int = 1, group=None):
+    def __init__(self, n: int, dtype=torch.float32, n_graphs: int = 1, group=None, exchange: str = "auto"):
+        """``exchange``: "peer" = the node tail reads all ranks' partials over NVLink from
+        peer-mapped memory (no collective call; single graph only), "nccl" = ncclAllReduce inside
+        the captured graph, "auto" = peer when possible."""
         from .smooth_learning import Solver
 
         self.group = group
@@ -67,6 +70,15 @@ class ShardedLogModelSolver:
         self.tile_range = shard_tiles(n, self.rank, self.world)
         self.solver = Solver(n, n_graphs, dtype, tile_range=self.tile_range)
         self._xch = self.solver.exchange()
+        if exchange == "auto":
+            exchange = "peer" if (self.world > 1 and n_graphs == 1 and self.world <= 8) else "nccl"
+        self.exchange = exchange if self.world > 1 else "none"
+        if self.exchange == "peer":
+            handles = [None] * self.world
+            dist.all_gather_object(handles, self.solver.comm_handle(), group=group)
+            self.solver.comm_connect(self.rank, self.world, b"".join(handles))
+            dist.barrier(group=group)
+        self.launches = 0
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_iters = 0
         self.maxit = 0
@@ -90,7 +102,7 @@ class ShardedLogModelSolver:
 
     # -- schedule -------------------------------------------------------------------------------------
     def _allreduce(self):
-        if self.world > 1:
+        if self.exchange == "nccl":
             dist.all_reduce(self._xch, group=self.group)
 
     def begin(self, alpha=1.0, beta=1.0, step_size=0.5, maxit=1000, tol=1e-5):
@@ -116,6 +128,12 @@ class ShardedLogModelSolver:
         since every rank evaluates the same all-reduced sums)."""
         if self.maxit <= 0:
             return
+        if self.exchange != "nccl":
+            # no collective call in the loop: the library's own graph + pipelined polling drives it
+            before = nat.launch_count()
+            self.solver.run(poll_every)
+            self.launches += nat.launch_count() - before
+            return
         if poll_every <= 0:
             poll_every = 10
         poll_every = min(poll_every, self.maxit)
@@ -125,9 +143,8 @@ class ShardedLogModelSolver:
         done_it = 0
         while done_it < self.maxit:
             self._graph.replay()
-            nat.lib()  # (launch accounting below is informational)
             done_it += poll_every
-            self.launches = getattr(self, "launches", 0) + per_iter * poll_every
+            self.launches += per_iter * poll_every
             st = self.solver.status()
             if st.n_iter >= self.maxit or st.converged:
                 break
@@ -144,4 +161,7 @@ class ShardedLogModelSolver:
 
     def close(self):
         self._graph = None
+        if self.exchange == "peer":
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)  # nobody unmaps memory a peer may still read
         self.solver.close()

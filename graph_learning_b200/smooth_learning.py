@@ -170,6 +170,24 @@ class Solver:
     def run(self, poll_every: int = 0):
         nat.check(self.lib.gl_solver_run(self._h, int(poll_every), _stream()))
 
+    # -- peer (NVLink) exchange ---------------------------------------------------------------------
+    def comm_handle(self) -> bytes:
+        """64-byte CUDA IPC handle of this rank's comm block (to be all-gathered by the caller)."""
+        buf = ctypes.create_string_buffer(64)
+        nat.check(self.lib.gl_solver_comm_handle(self._h, buf))
+        return buf.raw
+
+    def comm_connect(self, rank: int, world: int, handles: bytes):
+        assert len(handles) == 64 * world
+        nat.check(self.lib.gl_solver_comm_connect(self._h, int(rank), int(world), handles))
+
+    def comm_ptr(self) -> int:
+        return self.lib.gl_solver_comm_ptr(self._h, None)
+
+    def comm_connect_ptrs(self, rank: int, world: int, ptrs):
+        arr = (ctypes.c_void_p * world)(*[ctypes.c_void_p(int(p)) for p in ptrs])
+        nat.check(self.lib.gl_solver_comm_connect_ptrs(self._h, int(rank), int(world), arr))
+
     def status(self) -> SolveInfo:
         it, conv = ctypes.c_int(), ctypes.c_int()
         rp, rd = ctypes.c_double(), ctypes.c_double()

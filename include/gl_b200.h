@@ -142,6 +142,17 @@ int gl_solver_node_tail(gl_solver *s, void *stream);
 /* Exchange buffer: float64 [K*2*npad degrees partials | K*2 residual sums], to be summed over
  * shards between edge pass and node tail.  *n_doubles receives its length. */
 void *gl_solver_exchange_ptr(gl_solver *s, int64_t *n_doubles);
+/* Peer (NVLink) exchange, single graph: instead of an all-reduce by the caller, the node tail of
+ * every rank reads all ranks' exchange buffers directly from peer-mapped memory, synchronised by
+ * sequence flags the edge pass's last CTA publishes.  Each rank exports the
+ * 64-byte CUDA IPC handle of its comm block, the caller all-gathers them (any transport) and
+ * connects; or passes already-mapped device pointers (same process / symmetric memory).  After
+ * connecting with world > 1 the caller performs NO collective between edge pass and node tail,
+ * and begin_finish directly follows begin.  world == 1 restores the plain mode. */
+int gl_solver_comm_handle(gl_solver *s, void *handle64_out);
+int gl_solver_comm_connect(gl_solver *s, int rank, int world, const void *handles /* world x 64 B */);
+void *gl_solver_comm_ptr(gl_solver *s, int64_t *n_bytes);
+int gl_solver_comm_connect_ptrs(gl_solver *s, int rank, int world, void *const *comm_ptrs);
 /* Single-GPU driver: runs iterations from an internally captured CUDA graph until the device
  * stop flag is set; polls every `poll_every` iterations (<=0: default).  Synchronises. */
 int gl_solver_run(gl_solver *s, int poll_every, void *stream);

@@ -182,3 +182,49 @@ def test_two_shards_one_gpu(golden, sl):
     assert torch.equal(shards[0].node_state(), shards[1].node_state())
     for s in shards:
         s.close()
+
+
+def test_peer_exchange_two_shards_one_gpu(sl):
+    """Peer-memory exchange (node tail reads every rank's partials through mapped pointers, flags
+    published by the edge pass) with two shards in ONE process on one GPU.  Launch order
+    [edge A, edge B, node A, node B] on one stream means no kernel ever waits on a later one."""
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    rng = np.random.default_rng(21)
+    n = 300
+    pts = rng.uniform(size=(n, 2))
+    z_np = orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1)) * 40.0
+    z = torch.as_tensor(z_np, device="cuda")
+    shards = []
+    for r in range(2):
+        b, e = ctypes.c_int(), ctypes.c_int()
+        nat.check(nat.lib().gl_shard_tiles(n, r, 2, ctypes.byref(b), ctypes.byref(e)))
+        s = sl.Solver(n, 1, torch.float64, tile_range=(b.value, e.value))
+        s.load(z)
+        shards.append(s)
+    ptrs = [s.comm_ptr() for s in shards]
+    for r, s in enumerate(shards):
+        s.comm_connect_ptrs(r, 2, ptrs)
+    for solve in range(2):  # two solves back to back: sequence numbers keep running
+        maxit = 30 if solve == 0 else 45
+        if solve == 1:
+            for s in shards:
+                s.load(z)
+        for s in shards:
+            s.begin(maxit=maxit, finish=False)
+        for s in shards:
+            s.begin_finish()
+        for _ in range(maxit + 3):  # extra steps are no-ops
+            for s in shards:
+                s.edge_pass()
+            for s in shards:
+                s.node_tail()
+        out = torch.zeros((1, n * (n - 1) // 2), dtype=torch.float64, device="cuda")
+        for s in shards:
+            assert s.status().n_iter == maxit
+            s.store(-np.inf, out)
+        wo, _ = orc.solve_one_pass(z_np, maxit=maxit, threshold=False)
+        assert rel(out[0].cpu().numpy(), wo) < 1e-11
+        assert torch.equal(shards[0].node_state(), shards[1].node_state())
+    for s in shards:
+        s.close()
