@@ -59,6 +59,7 @@ SIGNATURES = {
     "gl_solver_comm_connect": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "gl_solver_comm_ptr": (c_void_p, [c_void_p, POINTER(c_int64)]),
     "gl_solver_comm_connect_ptrs": (c_int, [c_void_p, c_int, c_int, POINTER(c_void_p)]),
+    "gl_solver_comm_publish": (c_int, [c_void_p, c_void_p]),
     "gl_solver_exchange_ptr": (c_void_p, [c_void_p, POINTER(c_int64)]),
     "gl_solver_run": (c_int, [c_void_p, c_int, c_void_p]),
     "gl_solver_status": (c_int, [c_void_p, _pi, _pd, _pd, _pi, c_void_p]),

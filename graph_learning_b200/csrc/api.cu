@@ -237,7 +237,6 @@ int gl_solver_begin(gl_solver *s, double alpha, double beta, double step_size, i
   if (s->K > 1 && s->ntl) GL_CUDA(cudaMemsetAsync(s->r, 0, (size_t)s->K * s->gstride * s->esz, st));
   GL_TRY(launch_edge_init(s, st));   // local partial of S w0 (and ||w0||^2 for K == 1)
   GL_TRY(launch_gram_edges(s, st));  // K > 1: Gram(W0)
-  GL_TRY(launch_signal(s, st));      // peer mode: publish the initial partials
   return GL_OK;
 }
 
@@ -314,6 +313,11 @@ int gl_solver_comm_connect(gl_solver *s, int rank, int world, const void *handle
     s->ipc_opened[r] = ptrs[r];
   }
   return gl_solver_comm_connect_ptrs(s, rank, world, ptrs);
+}
+
+int gl_solver_comm_publish(gl_solver *s, void *stream) {
+  if (!s) return fail(GL_E_ARG, "null solver");
+  return launch_signal(s, as_stream(stream));
 }
 
 void *gl_solver_exchange_ptr(gl_solver *s, int64_t *n_doubles) {

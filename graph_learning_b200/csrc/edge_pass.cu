@@ -237,10 +237,6 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
     if (gj < A.n) atomicAdd((qty ? g_sw : g_sp) + (int64_t)k * A.npad + gj, acc);
   }
   if (BATCH) return;
-  if (A.world > 1) {  // the ticket below must be ordered after EVERY thread's atomics
-    __threadfence();
-    __syncthreads();
-  }
 
   // ---- residual sums: fixed-order two-stage reduction (deterministic) -------------------------
   if (tid == 0) {
@@ -281,10 +277,6 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
     g_sum[0] += r2;  // xch slot is zeroed by the node tail; += keeps the sharded sum convention
     g_sum[1] += w2;
     A.flags[FLAG_EDGE_TICKET] = 0;
-    if (A.world > 1) {  // publish: this rank's partials of exchange `seq` are complete
-      __threadfence_system();
-      for (int r = 0; r < A.world; ++r) st_release_sys(A.peers.hdr[r] + A.rank, seq + 1);
-    }
   }
 }
 
@@ -385,9 +377,11 @@ int launch_edge_init(gl_solver *s, cudaStream_t st) {
   return GL_OK;
 }
 
-// peer mode: publish "my partials of the current exchange are complete" after a plain kernel
-// (the initial-degree pass); the iteration's edge pass does this from its last CTA instead.
-__global__ void signal_kernel(int *hdr, PeerView peers, int world, int rank) {
+// peer mode: publish "my partials of the current exchange are complete" as a stand-alone launch.
+// The node tail does the same on entry; this entry point exists for single-process emulation of
+// several ranks on one stream, where every rank must have published before any node tail starts.
+__global__ void signal_kernel(int *hdr, PeerView peers, int world, int rank, const int *flags) {
+  if (ld_volatile_int(flags + FLAG_DONE)) return;  // nothing was produced: never publish early
   __threadfence_system();
   const int seq = ld_volatile_int(hdr + HDR_SEQ);
   for (int r = 0; r < world; ++r) st_release_sys(peers.hdr[r] + rank, seq + 1);
@@ -395,7 +389,7 @@ __global__ void signal_kernel(int *hdr, PeerView peers, int world, int rank) {
 
 int launch_signal(gl_solver *s, cudaStream_t st) {
   if (s->world <= 1) return GL_OK;
-  signal_kernel<<<1, 1, 0, st>>>(reinterpret_cast<int *>(s->comm), s->peers, s->world, s->rank);
+  signal_kernel<<<1, 1, 0, st>>>(reinterpret_cast<int *>(s->comm), s->peers, s->world, s->rank, s->flags);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }

@@ -170,6 +170,12 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     seq = ld_volatile_int(A.hdr + HDR_SEQ);
     rd_off = (seq & 1) * A.xch_stride;
     clr_off = ((seq + 1) & 1) * A.xch_stride;
+    // publish first: this kernel runs after the rank's edge pass has completed (stream order), so
+    // its partials of exchange `seq` are final.  No fence or flag work inside the edge pass.
+    if (blockIdx.x == 0 && tid == 0) {
+      __threadfence_system();
+      for (int r = 0; r < A.world; ++r) st_release_sys(A.peers.hdr[r] + A.rank, seq + 1);
+    }
     if (tid < A.world) {
       const long long t0 = clock64();
       while (ld_acquire_sys(A.hdr + tid) < seq + 1) {

@@ -181,6 +181,9 @@ class Solver:
         assert len(handles) == 64 * world
         nat.check(self.lib.gl_solver_comm_connect(self._h, int(rank), int(world), handles))
 
+    def comm_publish(self):
+        nat.check(self.lib.gl_solver_comm_publish(self._h, _stream()))
+
     def comm_ptr(self) -> int:
         return self.lib.gl_solver_comm_ptr(self._h, None)
 

@@ -186,8 +186,9 @@ def test_two_shards_one_gpu(golden, sl):
 
 def test_peer_exchange_two_shards_one_gpu(sl):
     """Peer-memory exchange (node tail reads every rank's partials through mapped pointers, flags
-    published by the edge pass) with two shards in ONE process on one GPU.  Launch order
-    [edge A, edge B, node A, node B] on one stream means no kernel ever waits on a later one."""
+    published per exchange) with two shards in ONE process on one GPU.  Launch order
+    [edge A, edge B, publish A, publish B, node A, node B] on one stream means no kernel ever
+    waits on a later one."""
     import ctypes
     from graph_learning_b200 import _native as nat
     rng = np.random.default_rng(21)
@@ -213,10 +214,14 @@ def test_peer_exchange_two_shards_one_gpu(sl):
         for s in shards:
             s.begin(maxit=maxit, finish=False)
         for s in shards:
+            s.comm_publish()
+        for s in shards:
             s.begin_finish()
         for _ in range(maxit + 3):  # extra steps are no-ops
             for s in shards:
                 s.edge_pass()
+            for s in shards:
+                s.comm_publish()
             for s in shards:
                 s.node_tail()
         out = torch.zeros((1, n * (n - 1) // 2), dtype=torch.float64, device="cuda")
