@@ -215,6 +215,11 @@ def run_ours(a):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: everything libraries print (e.g. NCCL's version banner)
+    # is routed to stderr, the line itself is written to the saved descriptor at the end.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world != a.gpus and world > 1:
         raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
@@ -423,7 +428,7 @@ def run_ours(a):
                                 "note": "one-sweep C restatement with OpenMP, all host threads (stronger than the reference schedule)"},
         }
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
         # tear down in order: captured graphs (they hold NCCL work) -> sync -> barrier -> group;
         # then leave without running interpreter finalisers that could wait on the communicator.
