@@ -6,6 +6,7 @@
 //   edge_pass + node_tail (per iteration) <- :146-167
 //   store        <- :169-174 (threshold, output layout)
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -56,7 +57,7 @@ void free_all(gl_solver *s) {
   for (void *p : s->ipc_opened)
     if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
-                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags};
+                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -147,12 +148,13 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
   s->xch_stride = (s->xch_len + 31) / 32 * 32;
   if (rc == GL_OK) rc = alloc_zero((void **)&s->comm, 8 * (size_t)(COMM_HDR + 2 * s->xch_stride));
   if (rc == GL_OK) s->xch = s->comm + COMM_HDR;
-  if (rc == GL_OK) rc = alloc_zero((void **)&s->cta_partial, 16 * (size_t)(s->ntl ? s->ntl : 1));
+  if (rc == GL_OK) rc = alloc_zero((void **)&s->cta_partial, 16 * (size_t)((s->ntl > 1024 ? s->ntl : 1024) + s->npad / 256 + 8));
   if (rc == GL_OK) rc = alloc_zero((void **)&s->node_partial, 16 * (nk / 256 + 2));
   if (rc == GL_OK) rc = alloc_zero((void **)&s->gprev, 8 * 2 * KK);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->resid, 16);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->eig_scratch, 8 * 10 * KK + 8 * K);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->flags, sizeof(int) * FLAG_COUNT);
+  if (rc == GL_OK) rc = alloc_zero((void **)&s->grid_bar, 64);
   if (rc == GL_OK) rc = fill_tile_table(s);
   if (rc != GL_OK) {
     free_all(s);
@@ -329,7 +331,9 @@ void *gl_solver_exchange_ptr(gl_solver *s, int64_t *n_doubles) {
 int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   if (!s || !s->begun) return fail(GL_E_STATE, "gl_solver_begin/begin_finish must be called first");
   cudaStream_t user = as_stream(stream);
-  if (poll_every <= 0) poll_every = ((int64_t)s->ntl * s->K >= 4096) ? 8 : 32;
+  const char *env = std::getenv("GL_B200_PERSISTENT");
+  const bool persistent = s->K == 1 && s->ntl > 0 && !(env && env[0] == '0');
+  if (poll_every <= 0) poll_every = persistent ? 50 : (((int64_t)s->ntl * s->K >= 4096) ? 8 : 32);
   if (poll_every > s->maxit) poll_every = s->maxit > 0 ? s->maxit : 1;
 
   // private stream: the caller's stream may be the legacy default stream, which cannot be captured
@@ -364,7 +368,7 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   RUN_CUDA(cudaEventCreateWithFlags(&evs[1], cudaEventDisableTiming));
 
   const int per_iter = (s->ntl ? 1 : 0) + ((s->K > 1 && s->ntl) ? 1 : 0) + 1;
-  if (!s->graph_exec || s->graph_iters != poll_every) {
+  if (!persistent && (!s->graph_exec || s->graph_iters != poll_every)) {
     if (s->graph_exec) {
       cudaGraphExecDestroy(s->graph_exec);
       s->graph_exec = nullptr;
@@ -390,15 +394,23 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
     RUN_CUDA(ce);
     s->graph_iters = poll_every;
   }
-  // pipelined replay: graph g+1 is enqueued before the flags of graph g are inspected; iterations
+  // pipelined replay: chunk g+1 is enqueued before the flags of chunk g are inspected; iterations
   // past the stop are device-side no-ops, so over-enqueueing costs only empty launches.
   const int max_graphs = (s->maxit + poll_every - 1) / poll_every;
   int launched = 0, checked = 0;
   bool done = s->maxit <= 0;
   while (!done) {
     while (launched < max_graphs && launched - checked < 2) {
-      RUN_CUDA(cudaGraphLaunch(s->graph_exec, st));
-      g_launches.fetch_add((long long)per_iter * poll_every);
+      if (persistent) {
+        rc = launch_persistent(s, poll_every, st);  // one resident kernel runs the whole chunk
+        if (rc != GL_OK) {
+          cleanup();
+          return rc;
+        }
+      } else {
+        RUN_CUDA(cudaGraphLaunch(s->graph_exec, st));
+        g_launches.fetch_add((long long)per_iter * poll_every);
+      }
       RUN_CUDA(cudaMemcpyAsync(h_flags + (launched & 1) * FLAG_COUNT, s->flags, sizeof(int) * FLAG_COUNT,
                                cudaMemcpyDeviceToHost, st));
       RUN_CUDA(cudaEventRecord(evs[launched & 1], st));

@@ -1,0 +1,291 @@
+// persistent.cu -- whole iterations in ONE resident kernel (single graph, K == 1).
+//
+// Same arithmetic as edge_pass.cu + node_tail.cu (graph_learn/smooth_learning.py:146-167), but the
+// CTAs stay resident (cooperative launch, one or two per SM) and loop over
+//   E phase : each CTA sweeps its tiles (static stride assignment), atomics into the exchange buffer
+//   barrier
+//   N phase : block 0 folds the CTAs' residual partials and (peer mode) publishes this rank's flag;
+//             node chunks of 256 nodes are updated by the first CTAs, reading every rank's partials
+//             straight from peer memory once all flags have arrived
+//   barrier
+//   decide  : every CTA evaluates the stop rule from the same partial sums (bit-identical), so no
+//             third barrier and no broadcast is needed
+// This removes the two kernel boundaries per iteration (launch gap + ramp-up/drain), which is what
+// bounds the sharded case: at 8 GPUs the per-rank edge sweep is ~50 us.
+#include <math_constants.h>
+
+#include "edge_tile.cuh"
+
+namespace gl {
+
+template <typename F> struct PersistArgs {
+  EdgeArgs<F> E;
+  double *d, *yb, *pb, *rb;
+  F *a, *b;
+  double *node_partial;  // [nchunks][2] dual residual / ||d'||^2 partials, then [2] rank-summed edge sums
+  double *gprev, *resid;
+  unsigned int *bar;
+  double gamma, four_ag, tol;
+  int maxit, iters, nchunks;
+};
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void grid_barrier(unsigned *bar, unsigned &gen) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    gen += gridDim.x;
+    __threadfence();
+    atomicAdd(bar, 1u);
+    while (ld_acquire_gpu(bar) < gen) {
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// fixed-order block sum of two values per thread; result valid in thread 0 (and broadcast via smem)
+__device__ __forceinline__ void block_sum2(double &x, double &y, double (*s_red)[2]) {
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  x = warp_sum(x);
+  y = warp_sum(y);
+  __syncthreads();
+  if (lane == 0) {
+    s_red[wp][0] = x;
+    s_red[wp][1] = y;
+  }
+  __syncthreads();
+  x = y = 0.0;
+#pragma unroll
+  for (int q = 0; q < EDGE_THREADS / 32; ++q) {
+    x += s_red[q][0];
+    y += s_red[q][1];
+  }
+  __syncthreads();
+}
+
+template <typename F>
+__global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persistent_kernel(const PersistArgs<F> P) {
+  __shared__ EdgeSmem<F> sm;
+  const EdgeArgs<F> &A = P.E;
+  const int tid = threadIdx.x;
+  int *flags = A.flags;
+  if (ld_volatile_int(flags + FLAG_DONE)) return;  // set only by earlier launches: uniform
+  int it = ld_volatile_int(flags + FLAG_IT);
+  double gw_prev = __ldcg(P.gprev), gd_prev = __ldcg(P.gprev + 1);
+  int seq = A.world > 1 ? ld_volatile_int(A.hdr + HDR_SEQ) : 0;
+  unsigned gen = 0;
+  const int64_t total = A.npad;  // K == 1
+
+  for (int step = 0; step < P.iters; ++step) {
+    const int64_t rd_off = (A.world > 1 ? (seq & 1) : 0) * A.xch_stride;
+    const int64_t clr_off = (A.world > 1 ? ((seq + 1) & 1) : 0) * A.xch_stride;
+    double *const xb = A.xch + rd_off;
+    // ---------------- E phase --------------------------------------------------------------------
+    double r2acc = 0.0, w2acc = 0.0;
+    for (int t = blockIdx.x; t < A.ntl; t += gridDim.x) {
+      double r2 = 0.0, w2 = 0.0;
+      edge_cta_tile<F, false, true>(A, sm, t, 0, xb, xb + total, r2, w2);
+      if (tid == 0) {
+        r2acc += r2;
+        w2acc += w2;
+      }
+      __syncthreads();
+    }
+    if (tid == 0) {
+      A.cta_partial[2 * blockIdx.x] = r2acc;
+      A.cta_partial[2 * blockIdx.x + 1] = w2acc;
+    }
+    grid_barrier(P.bar, gen);
+    // ---------------- N phase --------------------------------------------------------------------
+    if (blockIdx.x == 0) {
+      double r2 = 0.0, w2 = 0.0;
+      for (int i = tid; i < (int)gridDim.x; i += EDGE_THREADS) {
+        r2 += __ldcg(A.cta_partial + 2 * i);
+        w2 += __ldcg(A.cta_partial + 2 * i + 1);
+      }
+      block_sum2(r2, w2, sm.red);
+      if (tid == 0) {
+        xb[2 * total] += r2;      // slot was cleared; += keeps the classic kernels' convention
+        xb[2 * total + 1] += w2;
+        if (A.world > 1) {
+          __threadfence_system();
+          for (int r = 0; r < A.world; ++r) st_release_sys(A.peers.hdr[r] + A.rank, seq + 1);
+        }
+      }
+      __syncthreads();
+    }
+    for (int c = blockIdx.x; c < P.nchunks; c += gridDim.x) {
+      if (A.world > 1) {
+        if (tid < A.world) {
+          const long long t0 = clock64();
+          while (ld_acquire_sys(A.hdr + tid) < seq + 1) {
+            if (clock64() - t0 > 6000000000LL) {
+              flags[FLAG_ERROR] = 1;
+              break;
+            }
+          }
+        }
+        __syncthreads();
+      }
+      const int64_t idx = (int64_t)c * EDGE_THREADS + tid;
+      double my_rb2 = 0.0, my_d2 = 0.0;
+      if (idx < total) {
+        double sp = 0.0, sw = 0.0;
+        if (A.world > 1) {
+          for (int r = 0; r < A.world; ++r) {
+            sp += ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
+            sw += ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
+          }
+        } else {
+          sp = __ldcg(xb + idx);
+          sw = __ldcg(xb + total + idx);
+        }
+        A.xch[clr_off + idx] = 0.0;
+        A.xch[clr_off + total + idx] = 0.0;
+        double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
+        if (idx < A.n) {
+          const double dv = __ldcg(P.d + idx), ybv = __ldcg(P.yb + idx);
+          const double qb = __ldcg(P.pb + idx) + P.gamma * sp;   // :154
+          rbv = qb - ybv;
+          dn = (dv - ybv) + qb;                                  // :164
+          ybn = dn + P.gamma * sw;                               // :148
+          pbn = (ybn - sqrt(ybn * ybn + P.four_ag)) / 2.0;       // :151
+        }
+        my_rb2 = rbv * rbv;
+        my_d2 = dn * dn;
+        P.d[idx] = dn;
+        P.yb[idx] = ybn;
+        P.pb[idx] = pbn;
+        P.rb[idx] = rbv;
+        P.a[idx] = (F)(P.gamma * dn);
+        P.b[idx] = (F)(P.gamma * pbn);
+      }
+      block_sum2(my_rb2, my_d2, sm.red);
+      if (tid == 0) {
+        P.node_partial[2 * c] = my_rb2;
+        P.node_partial[2 * c + 1] = my_d2;
+        if (c == 0) {  // edge-side sums over the ranks, then clear the slots of the next exchange
+          double r2 = 0.0, w2 = 0.0;
+          if (A.world > 1) {
+            for (int r = 0; r < A.world; ++r) {
+              r2 += ld_relaxed_sys(A.peers.xch[r] + rd_off + 2 * total);
+              w2 += ld_relaxed_sys(A.peers.xch[r] + rd_off + 2 * total + 1);
+            }
+          } else {
+            r2 = xb[2 * total];
+            w2 = xb[2 * total + 1];
+          }
+          P.node_partial[2 * P.nchunks] = r2;
+          P.node_partial[2 * P.nchunks + 1] = w2;
+          A.xch[clr_off + 2 * total] = 0.0;
+          A.xch[clr_off + 2 * total + 1] = 0.0;
+        }
+      }
+    }
+    grid_barrier(P.bar, gen);
+    // ---------------- decision: identical on every CTA -----------------------------------------------
+    double rb2 = 0.0, d2 = 0.0;
+    for (int i = tid; i < P.nchunks; i += EDGE_THREADS) {
+      rb2 += __ldcg(P.node_partial + 2 * i);
+      d2 += __ldcg(P.node_partial + 2 * i + 1);
+    }
+    block_sum2(rb2, d2, sm.red);
+    const double g_r = __ldcg(P.node_partial + 2 * P.nchunks), g_w = __ldcg(P.node_partial + 2 * P.nchunks + 1);
+    bool conv = false;
+    double rp = CUDART_INF, rdl = CUDART_INF;
+    if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+      rp = sqrt(g_r) / sqrt(gw_prev);
+      rdl = sqrt(rb2) / sqrt(gd_prev);
+      conv = (rp < P.tol) && (rdl < P.tol);
+    }
+    gw_prev = g_w;
+    gd_prev = d2;
+    const bool had_check = it >= 1;
+    ++it;
+    if (A.world > 1) ++seq;
+    bool done = conv || it >= P.maxit;
+    if (ld_volatile_int(flags + FLAG_ERROR)) done = true;  // written before the barrier above
+    if (blockIdx.x == 0 && tid == 0) {
+      flags[FLAG_IT] = it;
+      if (had_check) {
+        P.resid[0] = rp;
+        P.resid[1] = rdl;
+      }
+      P.gprev[0] = gw_prev;
+      P.gprev[1] = gd_prev;
+      if (conv) flags[FLAG_CONVERGED] = 1;
+      if (A.world > 1) A.hdr[HDR_SEQ] = seq;
+      if (done) {
+        __threadfence();
+        flags[FLAG_DONE] = 1;
+      }
+    }
+    if (done) break;
+  }
+}
+
+template <typename F> static int persistent_launch_t(gl_solver *s, int iters, cudaStream_t st) {
+  PersistArgs<F> P;
+  EdgeArgs<F> &A = P.E;
+  A.w = static_cast<F *>(s->w);
+  A.z = static_cast<const F *>(s->z);
+  A.r = nullptr;
+  A.gstride = s->gstride;
+  A.a = static_cast<const F *>(s->a);
+  A.b = static_cast<const F *>(s->b);
+  A.xch = s->xch;
+  A.xch_stride = s->xch_stride;
+  A.cta_partial = s->cta_partial;
+  A.hdr = reinterpret_cast<int *>(s->comm);
+  A.world = s->world;
+  A.rank = s->rank;
+  A.peers = s->peers;
+  A.tile_ij = s->tile_ij;
+  A.flags = s->flags;
+  A.n = s->n;
+  A.npad = s->npad;
+  A.ntl = s->ntl;
+  A.c = (F)s->c;
+  A.tgz = (F)(2.0 * s->gamma);
+  P.d = s->d; P.yb = s->yb; P.pb = s->pb; P.rb = s->rb;
+  P.a = static_cast<F *>(s->a);
+  P.b = static_cast<F *>(s->b);
+  P.node_partial = s->node_partial;
+  P.gprev = s->gprev;
+  P.resid = s->resid;
+  P.bar = s->grid_bar;
+  P.gamma = s->gamma;
+  P.four_ag = 4.0 * s->alpha * s->gamma;
+  P.tol = s->tol;
+  P.maxit = s->maxit;
+  P.iters = iters;
+  P.nchunks = (s->npad + EDGE_THREADS - 1) / EDGE_THREADS;
+  if (s->persist_grid == 0) {
+    int per_sm = 0, sms = 0;
+    GL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, persistent_kernel<F>, EDGE_THREADS, 0));
+    GL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
+    int grid = per_sm * sms;
+    if (grid < 1) return fail(GL_E_CUDA, "persistent kernel does not fit on the device");
+    const int want = s->ntl > P.nchunks ? s->ntl : P.nchunks;
+    if (grid > want) grid = want;
+    s->persist_grid = grid;
+  }
+  GL_CUDA(cudaMemsetAsync(s->grid_bar, 0, sizeof(unsigned int), st));
+  void *args[] = {&P};
+  GL_CUDA(cudaLaunchCooperativeKernel((void *)persistent_kernel<F>, dim3(s->persist_grid), dim3(EDGE_THREADS), args, 0, st));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return GL_OK;
+}
+
+// `iters` iterations (or fewer if the stop rule fires) in one cooperative launch.
+int launch_persistent(gl_solver *s, int iters, cudaStream_t st) {
+  if (s->K != 1 || s->ntl == 0) return fail(GL_E_STATE, "persistent kernel needs a single graph with local tiles");
+  return s->dtype == GL_F32 ? persistent_launch_t<float>(s, iters, st) : persistent_launch_t<double>(s, iters, st);
+}
+
+}  // namespace gl

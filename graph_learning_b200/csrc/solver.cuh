@@ -51,6 +51,8 @@ struct gl_solver {
   double *resid = nullptr;        // [2]: rel_primal, rel_dual of the last checked iteration
   double *eig_scratch = nullptr;  // [4][2][K*K] repeated-squaring buffers
   int *flags = nullptr;           // [FLAG_COUNT]
+  unsigned int *grid_bar = nullptr;  // grid barrier counter of the persistent kernel
+  int persist_grid = 0;           // resident CTAs of the persistent kernel (0 = not sized yet)
 
   // parameters of the current solve
   double alpha = 1, beta = 1, step = 0.5, gamma = 0, c = 0, tol = 1e-5;
@@ -69,5 +71,6 @@ int launch_edge_init(gl_solver *s, cudaStream_t st);
 int launch_signal(gl_solver *s, cudaStream_t st);
 int launch_gram_edges(gl_solver *s, cudaStream_t st);
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
+int launch_persistent(gl_solver *s, int iters, cudaStream_t st);
 int fill_tile_table(gl_solver *s);
 }  // namespace gl
