@@ -303,27 +303,47 @@ def run_ours(a):
     launches = (nat.launch_count() - l0) + ((sharded.launches - sh0) if sharded else 0)
     value = E * a.iters * a.steps / (ms * 1e-3)
 
-    # ---- dominant kernel alone: average edge-pass launch duration, CUDA events on its stream -----
-    if world == 1:
-        solver.begin(1.0, 1.0, 0.5, 10 ** 6, 0.0)
-    else:
-        sharded.begin(1.0, 1.0, 0.5, 10 ** 6, 0.0)
-    reps = 30
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
-    for i in range(reps + 3):
-        if i >= 3:
-            evs[i - 3][0].record()
-        solver.edge_pass()
-        if i >= 3:
-            evs[i - 3][1].record()
-        if world > 1:
-            sharded._allreduce()
-        solver.node_tail()
-    torch.cuda.synchronize()
-    edge_ms = float(np.mean([s.elapsed_time(e) for s, e in evs]))
+    # ---- dominant kernel alone, CUDA events on its stream ------------------------------------------
     local_edges = E if world == 1 else (sharded.tile_range[1] - sharded.tile_range[0]) * tt
     hbm_peak, peak_src = peaks()
-    achieved = 3 * esz * local_edges / (edge_ms * 1e-3) / 1e9
+    persistent = (world == 1 or sharded.exchange == "peer") and os.environ.get("GL_B200_PERSISTENT", "1") != "0"
+    if persistent:
+        # gl::persistent_kernel: one cooperative launch runs a chunk of whole iterations
+        kname = "gl::persistent_kernel"
+        if world == 1:
+            solver.begin(1.0, 1.0, 0.5, a.iters, 0.0)
+        else:
+            sharded.begin(1.0, 1.0, 0.5, a.iters, 0.0)
+        barrier()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        lk = nat.launch_count()
+        k0.record()
+        solver.run()
+        k1.record()
+        torch.cuda.synchronize()
+        n_launch = max(1, nat.launch_count() - lk)
+        kernel_ms = k0.elapsed_time(k1) / n_launch
+        bytes_per_launch = 3 * esz * local_edges * a.iters / n_launch
+        iters_per_launch = a.iters / n_launch
+    else:
+        kname = "gl::edge_pass_kernel"
+        sharded.begin(1.0, 1.0, 0.5, 10 ** 6, 0.0) if world > 1 else solver.begin(1.0, 1.0, 0.5, 10 ** 6, 0.0)
+        reps = 30
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        for i in range(reps + 3):
+            if i >= 3:
+                evs[i - 3][0].record()
+            solver.edge_pass()
+            if i >= 3:
+                evs[i - 3][1].record()
+            if world > 1:
+                sharded._allreduce()
+            solver.node_tail()
+        torch.cuda.synchronize()
+        kernel_ms = float(np.mean([s.elapsed_time(e) for s, e in evs]))
+        bytes_per_launch = 3 * esz * local_edges
+        iters_per_launch = 1
+    achieved = bytes_per_launch / (kernel_ms * 1e-3) / 1e9
 
     line = {
         "metric": "LogModel edges*iters/sec",
@@ -343,12 +363,13 @@ def run_ours(a):
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {
-            "bound": "hbm", "kernel": "gl::edge_pass_kernel", "achieved": achieved, "peak": hbm_peak,
+            "bound": "hbm", "kernel": kname, "achieved": achieved, "peak": hbm_peak,
             "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
             "frac_of_nominal_8TBps": achieved / 8000.0,
-            "bytes_per_edge": 3 * esz, "edges_per_launch": int(local_edges), "kernel_ms": edge_ms,
+            "bytes_per_edge_per_iteration": 3 * esz, "edges_per_launch": int(local_edges),
+            "iterations_per_launch": iters_per_launch, "bytes_per_launch": bytes_per_launch, "kernel_ms": kernel_ms,
             "whole_iteration_frac": (3 * esz * E / world) / (ms * 1e-3 / a.steps / a.iters) / 1e9 / hbm_peak,
-            "traffic": read_traffic(1.0 if world == 1 else local_edges / float(ntiles * tt)),
+            "traffic": read_traffic((1.0 if world == 1 else local_edges / float(ntiles * tt)) * iters_per_launch),
         },
         "setup": {"z_build_ms": z_ms, "z_build_algorithmic_tflops": 2.0 * E * m / (z_ms * 1e-3) / 1e12,
                   "z_kernel": "gl::pdist_kernel (direct differences, FP32 FMA pipe)", "theta_ms": theta_ms,
