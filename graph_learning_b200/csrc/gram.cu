@@ -1,0 +1,627 @@
+// gram.cu -- K1 (tensor-core form): pairwise squared distances between the COLUMNS of X as a
+// tcgen05 / TMA Gram GEMM with the norm epilogue fused, written straight into tiled or packed
+// edge order (BASELINE north_star (1)).
+//
+//   y[t,i] = row_scale[t] * (X[t,i] - col_shift[i])         (GLMM form, clustering/glmm.py:61-68)
+//   Z_ij   = |y_i|^2 + |y_j|^2 - 2 <y_i, y_j>               (= pdist(x.T)**2, smooth_learning.py:278)
+//
+// Precision (SURVEY 7.2 "Z precision"): the Gram form cancels on smooth signals, so <y_i,y_j> must
+// carry (nearly) full fp32 accuracy.  Two measures:
+//   * error-compensated operands: y = y0 + y1 (+ y2), each term bf16 (8 significant bits), so the
+//     sum carries 16 (24) bits; the product is expanded into the cross terms whose weight is
+//     >= 2^-16 (2^-24): 3 (6) bf16 MMAs per k-step, all accumulating into the same fp32 TMEM tile;
+//   * chunked accumulation: the tensor core's fp32 accumulator is only trusted over `chunk`
+//     samples; the epilogue warps fold every chunk out of TMEM into fp32 registers (round to
+//     nearest) while the MMA pipe fills the other TMEM buffer.
+// Norms |y_i|^2 are summed in float64 by the split pre-pass from the same fp32 y values.
+//
+// Stage 1  gram_split_kernel: X (m,n) fp32 -> TERMS bf16 planes, TRANSPOSED to (n_pad, m_pad) so
+//          both GEMM operands are K-major (sample index contiguous), zero padded; partial norms.
+// Stage 2  gram_kernel: persistent, one CTA per SM, warp-specialised:
+//            warp 0     TMA producer   (cp.async.bulk.tensor.3d: one box = all planes of a k-block)
+//            warp 1     MMA issuer     (one thread; tcgen05.mma.cta_group::1.kind::f16, M=128, N=BN)
+//            warp 2     TMEM allocator
+//            warps 4..  epilogue       (tcgen05.ld chunk folds; final norm epilogue + stores)
+//          Work unit = tile row I x BN/128 adjacent column tiles; units are ordered so that the
+//          ~148 units in flight cover a compact block of the triangle (operand panels are shared
+//          through the 126 MB L2).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <vector>
+
+#include "solver.cuh"
+
+namespace gl {
+
+constexpr int GR_BM = 128;          // rows of a unit = one solver tile row
+constexpr int GR_UMMA_K = 16;       // bf16 MMA depth
+constexpr int GR_CTRL_WARPS = 4;    // producer, MMA, TMEM allocator, (spare: keeps epilogue warp%4 aligned)
+constexpr int GR_SPLIT_TILE = 64;   // split pre-pass: 64 samples x 64 nodes per step
+constexpr int GR_GROUP_ROWS = 8;    // tile rows per L2 rasterisation group
+
+// ------------------------------------------------------------------------------------------------
+// PTX wrappers (sm_100a)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+// Bounded wait: a protocol bug must trap (and fail the launch) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (clock64() - t0 > 8000000000LL) {  // ~4 s: far beyond any legitimate wait
+      printf("gram_kernel: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void tma_load_3d(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int c0,
+                                            int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot_in_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_in_smem)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], bf16 x bf16 -> fp32, issued by ONE thread for the CTA.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrives once all MMAs issued so far by this thread have completed.
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// 32 lanes x 16 consecutive fp32 columns: thread t of the warp reads lane (lane_base + t).
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp): rows of
+// ROW_BYTES (= swizzle span) bytes, 8-row groups SBO = 8*ROW_BYTES apart, sm_100 version bit.
+template <int ROW_BYTES>
+__device__ __forceinline__ uint64_t smem_desc_kmajor(uint32_t saddr) {
+  static_assert(ROW_BYTES == 64 || ROW_BYTES == 128, "swizzle span");
+  constexpr uint64_t layout = ROW_BYTES == 128 ? 2 /*SWIZZLE_128B*/ : 4 /*SWIZZLE_64B*/;
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);                 // start address, bits [0,14)
+  d |= (uint64_t)1 << 16;                                  // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)((8 * ROW_BYTES) >> 4) << 32;             // stride byte offset, bits [32,46)
+  d |= (uint64_t)1 << 46;                                  // descriptor version (Blackwell)
+  d |= layout << 61;                                       // layout type, bits [61,64)
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D=F32, A=B=BF16, both K-major, M=128, N.
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int n_dim) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_dim >> 3) << 17) | ((uint32_t)(GR_BM >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Stage 1: split + transpose + norms
+// ------------------------------------------------------------------------------------------------
+// grid (n_pad/64, S); block 256.  planes[p][node][sample] bf16, leading dimension m_pad.
+template <int TERMS>
+__global__ void __launch_bounds__(256)
+gram_split_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, const float *__restrict__ row_scale,
+                  const float *__restrict__ col_shift, __nv_bfloat16 *__restrict__ planes, int64_t m_pad, int n_pad,
+                  double *__restrict__ norm_part, int64_t seg_len) {
+  __shared__ float tile[GR_SPLIT_TILE][GR_SPLIT_TILE + 1];
+  __shared__ double s_norm[4][GR_SPLIT_TILE];
+  const int tid = threadIdx.x;
+  const int node0 = blockIdx.x * GR_SPLIT_TILE;
+  const int64_t t_begin = (int64_t)blockIdx.y * seg_len;
+  const int64_t t_end = min(t_begin + seg_len, m_pad);
+  // loader mapping: column lx (node), rows ly, ly+4, ...
+  const int lx = tid & 63, ly = tid >> 6;
+  const int gnode = node0 + lx;
+  const float sh = (col_shift && gnode < n) ? col_shift[gnode] : 0.f;
+  // writer mapping: node wx, 16 consecutive samples starting at wy*16
+  const int wx = tid >> 2, wy = tid & 3;
+  const int64_t plane_stride = (int64_t)n_pad * m_pad;
+  double nsum = 0.0;
+
+  for (int64_t t0 = t_begin; t0 < t_end; t0 += GR_SPLIT_TILE) {
+#pragma unroll
+    for (int r = 0; r < GR_SPLIT_TILE / 4; ++r) {
+      const int row = ly + 4 * r;
+      const int64_t tt = t0 + row;
+      float y = 0.f;
+      if (tt < m && gnode < n) {
+        const float sc = row_scale ? row_scale[tt] : 1.f;
+        y = sc * (X[tt * ldx + gnode] - sh);
+      }
+      tile[row][lx] = y;
+      nsum += (double)y * (double)y;
+    }
+    __syncthreads();
+    float v[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) v[e] = tile[wy * 16 + e][wx];
+#pragma unroll
+    for (int p = 0; p < TERMS; ++p) {
+      uint32_t packed[8];
+#pragma unroll
+      for (int e = 0; e < 16; e += 2) {
+        const __nv_bfloat16 b0 = __float2bfloat16_rn(v[e]);
+        const __nv_bfloat16 b1 = __float2bfloat16_rn(v[e + 1]);
+        v[e] -= __bfloat162float(b0);        // exact: the residual fits fp32
+        v[e + 1] -= __bfloat162float(b1);
+        packed[e >> 1] = (uint32_t)__bfloat16_as_ushort(b0) | ((uint32_t)__bfloat16_as_ushort(b1) << 16);
+      }
+      uint4 *dst = reinterpret_cast<uint4 *>(planes + p * plane_stride + (int64_t)(node0 + wx) * m_pad + t0 + wy * 16);
+      dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    }
+    __syncthreads();
+  }
+  s_norm[ly][lx] = nsum;
+  __syncthreads();
+  if (tid < GR_SPLIT_TILE)
+    norm_part[(int64_t)blockIdx.y * n_pad + node0 + tid] =
+        ((s_norm[0][tid] + s_norm[1][tid]) + s_norm[2][tid]) + s_norm[3][tid];
+}
+
+// norms[i] = sum over segments, fixed order (deterministic)
+__global__ void gram_norm_reduce_kernel(const double *__restrict__ norm_part, int n_pad, int segs,
+                                        double *__restrict__ norms) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pad) return;
+  double s = 0.0;
+  for (int g = 0; g < segs; ++g) s += norm_part[(int64_t)g * n_pad + i];
+  norms[i] = s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Stage 2: the GEMM
+// ------------------------------------------------------------------------------------------------
+template <int TERMS, int BN, int BK>
+struct GramCfg {
+  static constexpr int ROW_BYTES = BK * 2;                             // bf16
+  static constexpr int A_PLANE = GR_BM * ROW_BYTES;                    // bytes
+  static constexpr int B_PLANE = BN * ROW_BYTES;
+  static constexpr int STAGE_BYTES = TERMS * (A_PLANE + B_PLANE);
+  static constexpr int SMEM_BUDGET = 227 * 1024 - 2048;                // barriers + alignment slack
+  static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int EPI_WARPS = BN / 16;                            // 32 lanes x 64 columns each
+  static constexpr int THREADS = 32 * (GR_CTRL_WARPS + EPI_WARPS);
+  static constexpr int TMEM_COLS = 2 * BN;                             // double-buffered accumulator
+  static constexpr int PAIRS = TERMS == 2 ? 3 : 6;
+  static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static_assert(STAGES >= 2, "need at least a double-buffered operand pipeline");
+  static_assert(TMEM_COLS <= 512, "TMEM has 512 columns");
+};
+
+struct GramArgs {
+  const int2 *units;      // (I, Jp) work list
+  int n_units;
+  int num_kb;             // k-blocks (m_pad / BK)
+  int kb_per_chunk;       // k-blocks accumulated in TMEM before the fold
+  const double *norms;    // (n_pad,)
+  float *Z;
+  int layout, n, nt, tile_begin, tile_end;
+};
+
+template <int TERMS, int BN, int BK>
+__global__ void __launch_bounds__(GramCfg<TERMS, BN, BK>::THREADS, 1)
+gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+            const GramArgs args) {
+  using C = GramCfg<TERMS, BN, BK>;
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)C::STAGES * C::STAGE_BYTES);
+  uint64_t *full = bars, *empty = bars + C::STAGES, *acc_full = bars + 2 * C::STAGES,
+           *acc_empty = bars + 2 * C::STAGES + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * C::STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], C::EPI_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, C::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_kb = args.num_kb, kb_per_chunk = args.kb_per_chunk;
+  const int num_chunks = (num_kb + kb_per_chunk - 1) / kb_per_chunk;
+
+  if (warp == 0) {
+    // ===== TMA producer ===========================================================================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int u = blockIdx.x; u < args.n_units; u += gridDim.x) {
+        const int2 unit = args.units[u];
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          unsigned char *sa = smem + (size_t)s * C::STAGE_BYTES;
+          unsigned char *sb = sa + TERMS * C::A_PLANE;
+          mbar_expect_tx(&full[s], C::STAGE_BYTES);
+          tma_load_3d(sa, &map_a, &full[s], kb * BK, unit.x * GR_BM, 0);
+          tma_load_3d(sb, &map_b, &full[s], kb * BK, unit.y * BN, 0);
+          if (++s == C::STAGES) {
+            s = 0;
+            ph ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) ==================================================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BN);
+      // cross terms in decreasing weight: (a-plane, b-plane)
+      constexpr int pa[6] = {0, 0, 1, 1, 0, 2};
+      constexpr int pb[6] = {0, 1, 0, 1, 2, 0};
+      int s = 0;
+      uint32_t ph = 0;
+      int ab = 0;
+      uint32_t aph = 0;
+      for (int u = blockIdx.x; u < args.n_units; u += gridDim.x) {
+        for (int c = 0; c < num_chunks; ++c) {
+          mbar_wait(&acc_empty[ab], aph ^ 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)(ab * BN);
+          const int kb_end = min(num_kb, (c + 1) * kb_per_chunk);
+          for (int kb = c * kb_per_chunk; kb < kb_end; ++kb) {
+            mbar_wait(&full[s], ph);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + (size_t)s * C::STAGE_BYTES);
+            const uint32_t sb = sa + TERMS * C::A_PLANE;
+            uint32_t accumulate = kb > c * kb_per_chunk;
+#pragma unroll
+            for (int p = 0; p < C::PAIRS; ++p) {
+              const uint64_t da = smem_desc_kmajor<C::ROW_BYTES>(sa + pa[p] * C::A_PLANE);
+              const uint64_t db = smem_desc_kmajor<C::ROW_BYTES>(sb + pb[p] * C::B_PLANE);
+#pragma unroll
+              for (int k = 0; k < BK / GR_UMMA_K; ++k) {
+                // advance along K inside the swizzle span: +32 B per k-step (encoded >> 4)
+                umma_bf16(tmem_d, da + (uint64_t)(k * GR_UMMA_K * 2 / 16), db + (uint64_t)(k * GR_UMMA_K * 2 / 16),
+                          idesc, accumulate);
+                accumulate = 1;
+              }
+            }
+            umma_commit(&empty[s]);   // frees the operand stage once these MMAs have read it
+            if (++s == C::STAGES) {
+              s = 0;
+              ph ^= 1;
+            }
+          }
+          umma_commit(&acc_full[ab]);  // chunk accumulated: hand the TMEM buffer to the epilogue
+          if ((ab ^= 1) == 0) aph ^= 1;
+        }
+      }
+    }
+  } else if (warp >= GR_CTRL_WARPS) {
+    // ===== epilogue warps ===========================================================================
+    const int e = warp - GR_CTRL_WARPS;
+    const int q = warp & 3;                  // TMEM lane quarter this warp may access
+    const int cb = e >> 2;                   // 64-column block of the unit
+    const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
+    int ab = 0;
+    uint32_t aph = 0;
+    for (int u = blockIdx.x; u < args.n_units; u += gridDim.x) {
+      const int2 unit = args.units[u];
+      float acc[64];
+#pragma unroll
+      for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+      for (int c = 0; c < num_chunks; ++c) {
+        mbar_wait(&acc_full[ab], aph);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + lane_sel + (uint32_t)(ab * BN + cb * 64);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float v[16];
+          tmem_ld16(taddr + g * 16, v);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc[g * 16 + i] += v[i];
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[ab]);
+        if ((ab ^= 1) == 0) aph ^= 1;
+      }
+      // ---- norm epilogue: Z = n_i + n_j - 2 G_ij, clamped at 0, masked to the strict upper triangle
+      const int I = unit.x;
+      const int col0 = unit.y * BN + cb * 64;          // first global column of this warp's block
+      const int J = col0 / GR_BM;                       // the solver tile this block falls into
+      if (J < I || J >= args.nt) continue;
+      const int tile = tile_index(I, J, args.nt);
+      if (tile < args.tile_begin || tile >= args.tile_end) continue;
+      const int r = q * 32 + lane;                      // row inside the tile
+      const int gi = I * GR_BM + r;
+      const int c0 = col0 - J * GR_BM;                  // 0 or 64
+      const double ni = args.norms[gi];
+      if (args.layout == GL_LAYOUT_TILED) {
+        float *dst = args.Z + (int64_t)(tile - args.tile_begin) * TT + r * T + c0;
+#pragma unroll
+        for (int g = 0; g < 16; ++g) {
+          float o[4];
+#pragma unroll
+          for (int x = 0; x < 4; ++x) {
+            const int gj = col0 + g * 4 + x;
+            const double z = (ni + args.norms[gj]) - 2.0 * (double)acc[g * 4 + x];
+            o[x] = (gj > gi && gj < args.n) ? fmaxf((float)z, 0.f) : 0.f;
+          }
+          *reinterpret_cast<float4 *>(dst + g * 4) = make_float4(o[0], o[1], o[2], o[3]);
+        }
+      } else if (gi < args.n) {
+#pragma unroll
+        for (int x = 0; x < 64; ++x) {
+          const int gj = col0 + x;
+          if (gj > gi && gj < args.n) {
+            const double z = (ni + args.norms[gj]) - 2.0 * (double)acc[x];
+            args.Z[packed_index(gi, gj, args.n)] = fmaxf((float)z, 0.f);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int get_encode_fn(EncodeTiledFn *out) {
+  static EncodeTiledFn cached = nullptr;
+  if (!cached) {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    GL_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || !fn) return fail(GL_E_CUDA, "cuTensorMapEncodeTiled unavailable");
+    cached = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  *out = cached;
+  return GL_OK;
+}
+
+struct GramLayout {
+  int64_t m_pad;
+  int n_pad, segs;
+  int64_t seg_len;
+  size_t off_planes, off_norm_part, off_norms, off_units, total;
+  int max_units;
+};
+
+static GramLayout gram_layout(int64_t m, int n, int terms) {
+  GramLayout L;
+  L.m_pad = ((m + 63) / 64) * 64;
+  if (L.m_pad == 0) L.m_pad = 64;
+  L.n_pad = tiles_per_side(n) * T;
+  const int node_blocks = L.n_pad / GR_SPLIT_TILE;
+  const int64_t steps = L.m_pad / GR_SPLIT_TILE;
+  int64_t segs = (1184 + node_blocks - 1) / node_blocks;   // ~8 blocks per SM overall
+  if (segs > steps) segs = steps;
+  if (segs < 1) segs = 1;
+  L.seg_len = ((steps + segs - 1) / segs) * GR_SPLIT_TILE;
+  L.segs = (int)((L.m_pad + L.seg_len - 1) / L.seg_len);
+  auto align = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
+  size_t off = 0;
+  L.off_planes = off;
+  off = align(off + (size_t)terms * L.n_pad * L.m_pad * sizeof(__nv_bfloat16));
+  L.off_norm_part = off;
+  off = align(off + (size_t)L.segs * L.n_pad * sizeof(double));
+  L.off_norms = off;
+  off = align(off + (size_t)(L.n_pad + 256) * sizeof(double));   // + slack: B box may overhang by one tile
+  L.off_units = off;
+  const int nt = L.n_pad / T;
+  L.max_units = nt * (nt + 1) / 2 + nt;
+  off = align(off + (size_t)L.max_units * sizeof(int2));
+  L.total = off;
+  return L;
+}
+
+// Units (I, Jp) covering tiles [tile_begin, tile_end), rasterised in groups of GR_GROUP_ROWS tile
+// rows, column-major inside a group, so that concurrently running CTAs share operand panels in L2.
+static void build_units(int nt, int nb /*tiles per unit*/, int tile_begin, int tile_end, std::vector<int2> &units) {
+  units.clear();
+  const int njp = (nt + nb - 1) / nb;
+  for (int I0 = 0; I0 < nt; I0 += GR_GROUP_ROWS) {
+    const int I1 = std::min(nt, I0 + GR_GROUP_ROWS);
+    for (int jp = I0 / nb; jp < njp; ++jp)
+      for (int I = I0; I < I1; ++I) {
+        bool any = false;
+        for (int b = 0; b < nb; ++b) {
+          const int J = jp * nb + b;
+          if (J < I || J >= nt) continue;
+          const int t = tile_index(I, J, nt);
+          any |= (t >= tile_begin && t < tile_end);
+        }
+        if (any) units.push_back(make_int2(I, jp));
+      }
+  }
+}
+
+template <int TERMS, int BN, int BK>
+static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &base, int n_sms, cudaStream_t st) {
+  using C = GramCfg<TERMS, BN, BK>;
+  EncodeTiledFn encode;
+  GL_TRY(get_encode_fn(&encode));
+  CUtensorMap map_a, map_b;
+  const cuuint64_t gdim[3] = {(cuuint64_t)L.m_pad, (cuuint64_t)L.n_pad, (cuuint64_t)TERMS};
+  const cuuint64_t gstride[2] = {(cuuint64_t)L.m_pad * 2, (cuuint64_t)L.n_pad * (cuuint64_t)L.m_pad * 2};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  const CUtensorMapSwizzle sw = BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  const cuuint32_t box_a[3] = {BK, GR_BM, TERMS};
+  const cuuint32_t box_b[3] = {BK, BN, TERMS};
+  CUresult r1 = encode(&map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_a, estride,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r2 = encode(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_b, estride,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS)
+    return fail(GL_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d)", (int)r1, (int)r2);
+  GramArgs a = base;
+  a.num_kb = (int)(L.m_pad / BK);
+  a.kb_per_chunk = std::max(1, a.kb_per_chunk / BK);   // caller passed samples per chunk
+  auto kern = gram_kernel<TERMS, BN, BK>;
+  GL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+  const int grid = std::min(n_sms, a.n_units);
+  kern<<<grid, C::THREADS, C::SMEM_BYTES, st>>>(map_a, map_b, a);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+}  // namespace gl
+using namespace gl;
+
+extern "C" int64_t gl_gram_workspace_bytes(int64_t m, int n, int terms) {
+  if (m < 0 || n < 2 || (terms != 2 && terms != 3)) return -1;
+  return (int64_t)gram_layout(m, n, terms).total;
+}
+
+extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, const void *row_scale,
+                                const void *col_shift, void *Z, int layout, int tile_begin, int tile_end,
+                                int terms, int chunk, int variant, void *workspace, int64_t workspace_bytes,
+                                void *stream) {
+  if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
+  if (m < 0 || ldx < n) return fail(GL_E_SHAPE, "bad signal matrix shape (m=%lld, ldx=%lld, n=%d)",
+                                    (long long)m, (long long)ldx, n);
+  if (layout != GL_LAYOUT_PACKED && layout != GL_LAYOUT_TILED) return fail(GL_E_ARG, "bad layout");
+  if (terms != 2 && terms != 3) return fail(GL_E_ARG, "terms must be 2 or 3");
+  if (variant < 0 || variant > 3) return fail(GL_E_ARG, "variant must be 0..3");
+  if (layout == GL_LAYOUT_PACKED) {
+    tile_begin = 0;
+    tile_end = num_tiles(n);
+  }
+  if (tile_begin < 0 || tile_end > num_tiles(n) || tile_end < tile_begin)
+    return fail(GL_E_ARG, "bad tile range [%d,%d)", tile_begin, tile_end);
+  if (tile_end == tile_begin) return GL_OK;
+  const GramLayout L = gram_layout(m, n, terms);
+  if (!workspace || workspace_bytes < (int64_t)L.total)
+    return fail(GL_E_ARG, "workspace too small: need %lld bytes (gl_gram_workspace_bytes)", (long long)L.total);
+  if (reinterpret_cast<uintptr_t>(workspace) & 1023) return fail(GL_E_ARG, "workspace must be 1024-byte aligned");
+  if (chunk <= 0) chunk = 256;
+  cudaStream_t st = as_stream(stream);
+  unsigned char *ws = static_cast<unsigned char *>(workspace);
+  int dev = 0, n_sms = 0, cc_major = 0;
+  GL_CUDA(cudaGetDevice(&dev));
+  GL_CUDA(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
+  GL_CUDA(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (cc_major != 10) return fail(GL_E_CUDA, "the tcgen05 Gram kernel needs an sm_100 device (got sm_%d)", cc_major * 10);
+
+  // ---- stage 1: split / transpose / norms ----------------------------------------------------------
+  __nv_bfloat16 *planes = reinterpret_cast<__nv_bfloat16 *>(ws + L.off_planes);
+  double *norm_part = reinterpret_cast<double *>(ws + L.off_norm_part);
+  double *norms = reinterpret_cast<double *>(ws + L.off_norms);
+  GL_CUDA(cudaMemsetAsync(norms, 0, (size_t)(L.n_pad + 256) * sizeof(double), st));
+  const dim3 sgrid(L.n_pad / GR_SPLIT_TILE, L.segs);
+  if (terms == 2)
+    gram_split_kernel<2><<<sgrid, 256, 0, st>>>((const float *)X, m, n, ldx, (const float *)row_scale,
+                                                (const float *)col_shift, planes, L.m_pad, L.n_pad, norm_part, L.seg_len);
+  else
+    gram_split_kernel<3><<<sgrid, 256, 0, st>>>((const float *)X, m, n, ldx, (const float *)row_scale,
+                                                (const float *)col_shift, planes, L.m_pad, L.n_pad, norm_part, L.seg_len);
+  GL_LAUNCH_CHECK();
+  gram_norm_reduce_kernel<<<(L.n_pad + 255) / 256, 256, 0, st>>>(norm_part, L.n_pad, L.segs, norms);
+  GL_LAUNCH_CHECK();
+
+  // ---- stage 2: work list + GEMM -------------------------------------------------------------------
+  const int bn = (variant & 1) ? 128 : 256;
+  const int nt = tiles_per_side(n);
+  std::vector<int2> units;
+  build_units(nt, bn / T, tile_begin, tile_end, units);
+  if ((int)units.size() > L.max_units) return fail(GL_E_STATE, "unit list overflow");
+  int2 *units_dev = reinterpret_cast<int2 *>(ws + L.off_units);
+  // pageable source: the runtime stages it before returning, so the vector may die afterwards
+  GL_CUDA(cudaMemcpyAsync(units_dev, units.data(), units.size() * sizeof(int2), cudaMemcpyHostToDevice, st));
+  GramArgs a;
+  a.units = units_dev;
+  a.n_units = (int)units.size();
+  a.num_kb = 0;
+  a.kb_per_chunk = chunk;
+  a.norms = norms;
+  a.Z = static_cast<float *>(Z);
+  a.layout = layout;
+  a.n = n;
+  a.nt = nt;
+  a.tile_begin = tile_begin;
+  a.tile_end = tile_end;
+  // variant bit 0: BN (0 = 256, 1 = 128); bit 1: BK (0 = 32 / SWIZZLE_64B, 1 = 64 / SWIZZLE_128B)
+  const bool bk64 = (variant & 2) != 0;
+  if (terms == 3) {
+    if (bn == 256) {
+      if (bk64) return fail(GL_E_ARG, "terms=3, BN=256, BK=64 does not fit shared memory");
+      return launch_gram<3, 256, 32>(L, ws, a, n_sms, st);
+    }
+    return bk64 ? launch_gram<3, 128, 64>(L, ws, a, n_sms, st) : launch_gram<3, 128, 32>(L, ws, a, n_sms, st);
+  }
+  if (bn == 256) return bk64 ? launch_gram<2, 256, 64>(L, ws, a, n_sms, st) : launch_gram<2, 256, 32>(L, ws, a, n_sms, st);
+  return bk64 ? launch_gram<2, 128, 64>(L, ws, a, n_sms, st) : launch_gram<2, 128, 32>(L, ws, a, n_sms, st);
+}

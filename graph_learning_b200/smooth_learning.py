@@ -33,6 +33,7 @@ __all__ = [
     "LogModel",
     "Solver",
     "pdist_sq",
+    "pdist_sq_tiles",
     "SolveInfo",
 ]
 
@@ -277,11 +278,63 @@ def sum_squareform(n: int):
 # --------------------------------------------------------------------------------------------
 # pairwise squared distances (reference :278) and theta (reference :177-235)
 # --------------------------------------------------------------------------------------------
-def pdist_sq(x, row_scale=None, col_shift=None, dtype=None) -> torch.Tensor:
+# tensor-core Gram form: used by "auto" for float32 when there are enough samples to pay for the
+# split pre-pass; the exact direct-difference kernel stays the float64 path and the parity anchor.
+GRAM_MIN_SAMPLES = 256
+_gram_ws = {}
+
+
+def _gram_workspace(m: int, n: int, terms: int, device) -> torch.Tensor:
+    """Scratch for the split operand planes; one cached buffer per device, grown on demand."""
+    need = int(nat.lib().gl_gram_workspace_bytes(m, n, terms))
+    if need < 0:
+        raise ValueError(f"bad Gram problem size (m={m}, n={n}, terms={terms})")
+    key = (device.type, device.index)
+    buf = _gram_ws.get(key)
+    if buf is None or buf.numel() < need:
+        _gram_ws.pop(key, None)
+        buf = torch.empty((need,), dtype=torch.uint8, device=device)
+        _gram_ws[key] = buf
+    return buf
+
+
+def release_gram_workspace() -> None:
+    """Drop the cached Gram workspace (6 GB at n=20,000, m=50,000)."""
+    _gram_ws.clear()
+
+
+def _resolve_method(method: str, dt: torch.dtype, m: int) -> str:
+    if method not in ("auto", "direct", "gram", "gram2"):
+        raise ValueError(f"method must be auto, direct, gram or gram2, got {method!r}")
+    if method == "auto":
+        return "gram" if (dt == torch.float32 and m >= GRAM_MIN_SAMPLES) else "direct"
+    if method != "direct" and dt != torch.float32:
+        raise ValueError("the tensor-core Gram form is float32 only; use method='direct' for float64")
+    return method
+
+
+def _pdist_into(xd, rs, cs, out, layout, tile_begin, tile_end, method, chunk=0, variant=0) -> None:
+    """Launch the chosen distance kernel writing ``out`` (packed (E,) or a tile range)."""
+    m, n = xd.shape
+    if method == "direct":
+        nat.check(nat.lib().gl_pdist_sq(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
+                                        layout, tile_begin, tile_end, _gl_dtype(xd.dtype), _stream()))
+        return
+    terms = 2 if method == "gram2" else 3
+    ws = _gram_workspace(m, n, terms, xd.device)
+    nat.check(nat.lib().gl_pdist_sq_gram(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
+                                         layout, tile_begin, tile_end, terms, int(chunk), int(variant),
+                                         _ptr(ws), ws.numel(), _stream()))
+
+
+def pdist_sq(x, row_scale=None, col_shift=None, dtype=None, method="auto", chunk=0, variant=0) -> torch.Tensor:
     """Packed squared distances between the COLUMNS of x (m, n): ``pdist(x.T) ** 2``.
 
     With ``row_scale`` (m,) / ``col_shift`` (n,) the signals are first mapped to
     ``row_scale[:, None] * (x - col_shift)`` -- the GLMM M-step form (glmm.py:61-68).
+    ``method``: "direct" = exact differences on the FMA pipe (float32/float64); "gram" = tcgen05
+    Gram GEMM on 3-term bf16 splits (float32, ~fp32 accuracy); "gram2" = 2-term splits (faster,
+    ~16 bits); "auto" = gram for float32 with >= 256 samples, direct otherwise.
     Returns a CUDA tensor of shape (E,).
     """
     dt = _torch_dtype(dtype if dtype is not None else (x.dtype if getattr(x, "dtype", None) in (np.float32, torch.float32) else None))
@@ -292,8 +345,21 @@ def pdist_sq(x, row_scale=None, col_shift=None, dtype=None) -> torch.Tensor:
     rs = None if row_scale is None else _to_device(row_scale, dt)
     cs = None if col_shift is None else _to_device(col_shift, dt)
     out = torch.empty((n * (n - 1) // 2,), dtype=dt, device=xd.device)
-    nat.check(nat.lib().gl_pdist_sq(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
-                                    nat.LAYOUT_PACKED, 0, 0, _gl_dtype(dt), _stream()))
+    _pdist_into(xd, rs, cs, out, nat.LAYOUT_PACKED, 0, 0, _resolve_method(method, dt, m), chunk, variant)
+    return out
+
+
+def pdist_sq_tiles(x, tile_begin: int, tile_end: int, out=None, dtype=None, method="auto", chunk=0,
+                   variant=0) -> torch.Tensor:
+    """Same quantity written in the solver's resident tiled layout for tiles
+    [tile_begin, tile_end) -- what a GPU shard builds for itself."""
+    dt = _torch_dtype(dtype if dtype is not None else (x.dtype if getattr(x, "dtype", None) in (np.float32, torch.float32) else None))
+    xd = _to_device(x, dt)
+    m, n = xd.shape
+    if out is None:
+        out = torch.empty(((tile_end - tile_begin) * nat.TILE * nat.TILE,), dtype=dt, device=xd.device)
+    _pdist_into(xd, None, None, out, nat.LAYOUT_TILED, tile_begin, tile_end, _resolve_method(method, dt, m),
+                chunk, variant)
     return out
 
 
