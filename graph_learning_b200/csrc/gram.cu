@@ -5,14 +5,21 @@
 //   y[t,i] = row_scale[t] * (X[t,i] - col_shift[i])         (GLMM form, clustering/glmm.py:61-68)
 //   Z_ij   = |y_i|^2 + |y_j|^2 - 2 <y_i, y_j>               (= pdist(x.T)**2, smooth_learning.py:278)
 //
-// Precision (SURVEY 7.2 "Z precision"): the Gram form cancels on smooth signals, so <y_i,y_j> must
-// carry (nearly) full fp32 accuracy.  Two measures:
-//   * error-compensated operands: y = y0 + y1 (+ y2), each term bf16 (8 significant bits), so the
-//     sum carries 16 (24) bits; the product is expanded into the cross terms whose weight is
-//     >= 2^-16 (2^-24): 3 (6) bf16 MMAs per k-step, all accumulating into the same fp32 TMEM tile;
-//   * chunked accumulation: the tensor core's fp32 accumulator is only trusted over `chunk`
-//     samples; the epilogue warps fold every chunk out of TMEM into fp32 registers (round to
-//     nearest) while the MMA pipe fills the other TMEM buffer.
+// Precision (SURVEY 7.2 "Z precision"): the Gram form cancels on smooth signals (neighbours have
+// Z_ij << |y_i|^2), and the tensor core adds into its fp32 accumulator with truncation, which biases
+// same-sign sums by ~1 ulp per MMA (measured on B200: theta off by 3e-4 with a plain accumulator).
+// Four measures, all measured in tools/gram_weights_probe.py:
+//   * error-compensated operands: y = y0 + y1 (+ y2), each slice bf16, products expanded into the
+//     cross terms of weight >= 2^-16 (2^-24): 3 (6) bf16 MMAs per k-step;
+//   * exact leading slice (3-term form): y0 is a multiple of a per-node power-of-two quantum with
+//     |y0 / quantum| <= 256, so the products y0_i * y0_j are integers <= 2^16 and up to 256 samples
+//     accumulate EXACTLY in fp32 whatever the rounding mode (an Ozaki-style slice);
+//   * separate TMEM accumulators for the leading term and for the small cross terms, so the small
+//     terms are truncated at the ulp of a 2^-8 smaller sum;
+//   * chunked accumulation: every `chunk` (<= 256) samples the epilogue warps fold both TMEM tiles
+//     into float64 registers while the MMA pipe fills the other TMEM buffer pair.
+// Result on B200 (n=5,000, m=20,000 smooth signals): |dZ| <= 5e-7 |y|^2 (the exact fp32 kernel:
+// 1.4e-6), theta within 3e-8, learned weights within 2.6e-6 of the float64 solve.
 // Norms |y_i|^2 are summed in float64 by the split pre-pass from the same fp32 y values.
 //
 // Stage 1  gram_split_kernel: X (m,n) fp32 -> TERMS bf16 planes, TRANSPOSED to (n_pad, m_pad) so
@@ -22,12 +29,15 @@
 //            warp 1     MMA issuer     (one thread; tcgen05.mma.cta_group::1.kind::f16, M=128, N=BN)
 //            warp 2     TMEM allocator
 //            warps 4..  epilogue       (tcgen05.ld chunk folds; final norm epilogue + stores)
+//          Variants: split accumulators + float64 folds on 128-wide units (default, precise), or one
+//          fp32 accumulator on 128/256-wide units (faster, ~1e-5 |y|^2 bias).
 //          Work unit = tile row I x BN/128 adjacent column tiles; units are ordered so that the
 //          ~148 units in flight cover a compact block of the triangle (operand panels are shared
 //          through the 126 MB L2).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <type_traits>
 #include <vector>
 
 #include "solver.cuh"
@@ -125,6 +135,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// Same for 8 columns (keeps the staging registers of the two-tile fold small).
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float *v) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+
 // K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp): rows of
 // ROW_BYTES (= swizzle span) bytes, 8-row groups SBO = 8*ROW_BYTES apart, sm_100 version bit.
 template <int ROW_BYTES>
@@ -147,12 +169,43 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int n_dim) {
 // ------------------------------------------------------------------------------------------------
 // Stage 1: split + transpose + norms
 // ------------------------------------------------------------------------------------------------
+// Column maxima max_t |y[t,i]| (as float bit patterns: non-negative floats order like ints), for the
+// exact leading slice.  grid (n_pad/64, S); block 256; colmax zero-initialised by the caller.
+__global__ void __launch_bounds__(256)
+gram_colmax_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, const float *__restrict__ row_scale,
+                   const float *__restrict__ col_shift, int *__restrict__ colmax, int64_t seg_len) {
+  __shared__ float s_max[4][GR_SPLIT_TILE];
+  const int tid = threadIdx.x, lx = tid & 63, ly = tid >> 6;
+  const int gnode = blockIdx.x * GR_SPLIT_TILE + lx;
+  const int64_t t_begin = (int64_t)blockIdx.y * seg_len;
+  const int64_t t_end = min(t_begin + seg_len, m);
+  float mx = 0.f;
+  if (gnode < n) {
+    const float sh = col_shift ? col_shift[gnode] : 0.f;
+    for (int64_t tt = t_begin + ly; tt < t_end; tt += 4) {
+      const float sc = row_scale ? row_scale[tt] : 1.f;
+      mx = fmaxf(mx, fabsf(sc * (X[tt * ldx + gnode] - sh)));
+    }
+  }
+  s_max[ly][lx] = mx;
+  __syncthreads();
+  if (tid < GR_SPLIT_TILE && gnode < n) {
+    mx = fmaxf(fmaxf(s_max[0][tid], s_max[1][tid]), fmaxf(s_max[2][tid], s_max[3][tid]));
+    if (mx == mx && mx > 0.f) atomicMax(colmax + gnode, __float_as_int(fminf(mx, 3.0e38f)));
+  }
+}
+
 // grid (n_pad/64, S); block 256.  planes[p][node][sample] bf16, leading dimension m_pad.
-template <int TERMS>
+// EXACT0: the leading slice y0 is rounded to a multiple of the per-node quantum 2^(e_i - 8)
+// (2^e_i > max_t |y_ti|), so y0 = k * quantum with |k| <= 256: products of leading slices are
+// integers <= 2^16 in units of quantum_i * quantum_j and up to 256 of them sum EXACTLY in the fp32
+// TMEM accumulator, whatever its rounding mode (Ozaki-style slice).  The residual goes to the
+// ordinary bf16 slices y1 (, y2), whose accumulator is 2^-8 smaller.
+template <int TERMS, bool EXACT0>
 __global__ void __launch_bounds__(256)
 gram_split_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, const float *__restrict__ row_scale,
                   const float *__restrict__ col_shift, __nv_bfloat16 *__restrict__ planes, int64_t m_pad, int n_pad,
-                  double *__restrict__ norm_part, int64_t seg_len) {
+                  double *__restrict__ norm_part, int64_t seg_len, const int *__restrict__ colmax) {
   __shared__ float tile[GR_SPLIT_TILE][GR_SPLIT_TILE + 1];
   __shared__ double s_norm[4][GR_SPLIT_TILE];
   const int tid = threadIdx.x;
@@ -167,6 +220,15 @@ gram_split_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, co
   const int wx = tid >> 2, wy = tid & 3;
   const int64_t plane_stride = (int64_t)n_pad * m_pad;
   double nsum = 0.0;
+  float q_up = 1.f, q_down = 1.f;   // 1/quantum, quantum (powers of two) of the writer's node
+  if (EXACT0) {
+    const float mx = __int_as_float(colmax[node0 + wx]);
+    int e = 0;
+    if (mx > 0.f) frexpf(mx, &e);   // mx = f * 2^e, f in [0.5, 1)
+    e = max(-100, min(e, 127));
+    q_up = ldexpf(1.f, 8 - e);
+    q_down = ldexpf(1.f, e - 8);
+  }
 
   for (int64_t t0 = t_begin; t0 < t_end; t0 += GR_SPLIT_TILE) {
 #pragma unroll
@@ -190,8 +252,9 @@ gram_split_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, co
       uint32_t packed[8];
 #pragma unroll
       for (int e = 0; e < 16; e += 2) {
-        const __nv_bfloat16 b0 = __float2bfloat16_rn(v[e]);
-        const __nv_bfloat16 b1 = __float2bfloat16_rn(v[e + 1]);
+        const bool quant = EXACT0 && p == 0;
+        const __nv_bfloat16 b0 = __float2bfloat16_rn(quant ? rintf(v[e] * q_up) * q_down : v[e]);
+        const __nv_bfloat16 b1 = __float2bfloat16_rn(quant ? rintf(v[e + 1] * q_up) * q_down : v[e + 1]);
         v[e] -= __bfloat162float(b0);        // exact: the residual fits fp32
         v[e + 1] -= __bfloat162float(b1);
         packed[e >> 1] = (uint32_t)__bfloat16_as_ushort(b0) | ((uint32_t)__bfloat16_as_ushort(b1) << 16);
@@ -222,7 +285,7 @@ __global__ void gram_norm_reduce_kernel(const double *__restrict__ norm_part, in
 // ------------------------------------------------------------------------------------------------
 // Stage 2: the GEMM
 // ------------------------------------------------------------------------------------------------
-template <int TERMS, int BN, int BK>
+template <int TERMS, int BN, int BK, bool SPLIT>
 struct GramCfg {
   static constexpr int ROW_BYTES = BK * 2;                             // bf16
   static constexpr int A_PLANE = GR_BM * ROW_BYTES;                    // bytes
@@ -231,13 +294,19 @@ struct GramCfg {
   static constexpr int SMEM_BUDGET = 227 * 1024 - 2048;                // barriers + alignment slack
   static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
-  static constexpr int EPI_WARPS = BN / 16;                            // 32 lanes x 64 columns each
+  // SPLIT: the leading term y0*y0 and the small cross terms accumulate in separate TMEM tiles and
+  // are folded into float64 registers, 32 columns per epilogue warp; otherwise one TMEM tile,
+  // fp32 registers, 64 columns per warp.
+  static constexpr int COLS_PER_WARP = SPLIT ? 32 : 64;
+  static constexpr int EPI_WARPS = 4 * (BN / COLS_PER_WARP);
   static constexpr int THREADS = 32 * (GR_CTRL_WARPS + EPI_WARPS);
-  static constexpr int TMEM_COLS = 2 * BN;                             // double-buffered accumulator
+  static constexpr int TMEM_COLS = (SPLIT ? 4 : 2) * BN;               // double-buffered accumulator(s)
+  static constexpr int SMALL_OFF = 2 * BN;                             // first column of the small-term tiles
   static constexpr int PAIRS = TERMS == 2 ? 3 : 6;
   static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
   static_assert(STAGES >= 2, "need at least a double-buffered operand pipeline");
   static_assert(TMEM_COLS <= 512, "TMEM has 512 columns");
+  static_assert(THREADS <= 1024, "block size");
 };
 
 struct GramArgs {
@@ -250,11 +319,11 @@ struct GramArgs {
   int layout, n, nt, tile_begin, tile_end;
 };
 
-template <int TERMS, int BN, int BK>
-__global__ void __launch_bounds__(GramCfg<TERMS, BN, BK>::THREADS, 1)
+template <int TERMS, int BN, int BK, bool SPLIT>
+__global__ void __launch_bounds__(GramCfg<TERMS, BN, BK, SPLIT>::THREADS, 1)
 gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
             const GramArgs args) {
-  using C = GramCfg<TERMS, BN, BK>;
+  using C = GramCfg<TERMS, BN, BK, SPLIT>;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)C::STAGES * C::STAGE_BYTES);
@@ -332,17 +401,24 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             tc_fence_after();
             const uint32_t sa = smem_u32(smem + (size_t)s * C::STAGE_BYTES);
             const uint32_t sb = sa + TERMS * C::A_PLANE;
-            uint32_t accumulate = kb > c * kb_per_chunk;
+            // accumulate flags: the first MMA into each TMEM tile of a chunk overwrites it
+            uint32_t acc_main = kb > c * kb_per_chunk, acc_small = acc_main;
 #pragma unroll
             for (int p = 0; p < C::PAIRS; ++p) {
               const uint64_t da = smem_desc_kmajor<C::ROW_BYTES>(sa + pa[p] * C::A_PLANE);
               const uint64_t db = smem_desc_kmajor<C::ROW_BYTES>(sb + pb[p] * C::B_PLANE);
+              const bool to_small = SPLIT && p > 0;
 #pragma unroll
               for (int k = 0; k < BK / GR_UMMA_K; ++k) {
                 // advance along K inside the swizzle span: +32 B per k-step (encoded >> 4)
-                umma_bf16(tmem_d, da + (uint64_t)(k * GR_UMMA_K * 2 / 16), db + (uint64_t)(k * GR_UMMA_K * 2 / 16),
-                          idesc, accumulate);
-                accumulate = 1;
+                const uint64_t adv = (uint64_t)(k * GR_UMMA_K * 2 / 16);
+                if (to_small) {
+                  umma_bf16(tmem_d + C::SMALL_OFF, da + adv, db + adv, idesc, acc_small);
+                  acc_small = 1;
+                } else {
+                  umma_bf16(tmem_d, da + adv, db + adv, idesc, acc_main);
+                  acc_main = 1;
+                }
               }
             }
             umma_commit(&empty[s]);   // frees the operand stage once these MMAs have read it
@@ -358,27 +434,40 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     }
   } else if (warp >= GR_CTRL_WARPS) {
     // ===== epilogue warps ===========================================================================
+    using AccT = typename std::conditional<SPLIT, double, float>::type;
+    constexpr int CPW = C::COLS_PER_WARP;
     const int e = warp - GR_CTRL_WARPS;
     const int q = warp & 3;                  // TMEM lane quarter this warp may access
-    const int cb = e >> 2;                   // 64-column block of the unit
+    const int cb = e >> 2;                   // column block of the unit
     const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
     int ab = 0;
     uint32_t aph = 0;
     for (int u = blockIdx.x; u < args.n_units; u += gridDim.x) {
       const int2 unit = args.units[u];
-      float acc[64];
+      AccT acc[CPW];
 #pragma unroll
-      for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+      for (int i = 0; i < CPW; ++i) acc[i] = AccT(0);
       for (int c = 0; c < num_chunks; ++c) {
         mbar_wait(&acc_full[ab], aph);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + lane_sel + (uint32_t)(ab * BN + cb * 64);
+        const uint32_t taddr = tmem_base + lane_sel + (uint32_t)(ab * BN + cb * CPW);
+        if (SPLIT) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float v[16];
-          tmem_ld16(taddr + g * 16, v);
+          for (int g = 0; g < CPW / 8; ++g) {
+            float v[8], vs[8];
+            tmem_ld8(taddr + g * 8, v);
+            tmem_ld8(taddr + C::SMALL_OFF + g * 8, vs);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) acc[g * 16 + i] += v[i];
+            for (int i = 0; i < 8; ++i) acc[g * 8 + i] += (AccT)(v[i] + vs[i]);
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < CPW / 16; ++g) {
+            float v[16];
+            tmem_ld16(taddr + g * 16, v);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) acc[g * 16 + i] += (AccT)v[i];
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -387,19 +476,19 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
       // ---- norm epilogue: Z = n_i + n_j - 2 G_ij, clamped at 0, masked to the strict upper triangle
       const int I = unit.x;
-      const int col0 = unit.y * BN + cb * 64;          // first global column of this warp's block
+      const int col0 = unit.y * BN + cb * CPW;         // first global column of this warp's block
       const int J = col0 / GR_BM;                       // the solver tile this block falls into
       if (J < I || J >= args.nt) continue;
       const int tile = tile_index(I, J, args.nt);
       if (tile < args.tile_begin || tile >= args.tile_end) continue;
       const int r = q * 32 + lane;                      // row inside the tile
       const int gi = I * GR_BM + r;
-      const int c0 = col0 - J * GR_BM;                  // 0 or 64
+      const int c0 = col0 - J * GR_BM;
       const double ni = args.norms[gi];
       if (args.layout == GL_LAYOUT_TILED) {
         float *dst = args.Z + (int64_t)(tile - args.tile_begin) * TT + r * T + c0;
 #pragma unroll
-        for (int g = 0; g < 16; ++g) {
+        for (int g = 0; g < CPW / 4; ++g) {
           float o[4];
 #pragma unroll
           for (int x = 0; x < 4; ++x) {
@@ -411,7 +500,7 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
       } else if (gi < args.n) {
 #pragma unroll
-        for (int x = 0; x < 64; ++x) {
+        for (int x = 0; x < CPW; ++x) {
           const int gj = col0 + x;
           if (gj > gi && gj < args.n) {
             const double z = (ni + args.norms[gj]) - 2.0 * (double)acc[x];
@@ -454,7 +543,7 @@ struct GramLayout {
   int64_t m_pad;
   int n_pad, segs;
   int64_t seg_len;
-  size_t off_planes, off_norm_part, off_norms, off_units, total;
+  size_t off_planes, off_norm_part, off_norms, off_colmax, off_units, total;
   int max_units;
 };
 
@@ -478,6 +567,8 @@ static GramLayout gram_layout(int64_t m, int n, int terms) {
   off = align(off + (size_t)L.segs * L.n_pad * sizeof(double));
   L.off_norms = off;
   off = align(off + (size_t)(L.n_pad + 256) * sizeof(double));   // + slack: B box may overhang by one tile
+  L.off_colmax = off;
+  off = align(off + (size_t)L.n_pad * sizeof(int));
   L.off_units = off;
   const int nt = L.n_pad / T;
   L.max_units = nt * (nt + 1) / 2 + nt;
@@ -507,9 +598,9 @@ static void build_units(int nt, int nb /*tiles per unit*/, int tile_begin, int t
   }
 }
 
-template <int TERMS, int BN, int BK>
+template <int TERMS, int BN, int BK, bool SPLIT>
 static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &base, int n_sms, cudaStream_t st) {
-  using C = GramCfg<TERMS, BN, BK>;
+  using C = GramCfg<TERMS, BN, BK, SPLIT>;
   EncodeTiledFn encode;
   GL_TRY(get_encode_fn(&encode));
   CUtensorMap map_a, map_b;
@@ -530,7 +621,7 @@ static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &b
   GramArgs a = base;
   a.num_kb = (int)(L.m_pad / BK);
   a.kb_per_chunk = std::max(1, a.kb_per_chunk / BK);   // caller passed samples per chunk
-  auto kern = gram_kernel<TERMS, BN, BK>;
+  auto kern = gram_kernel<TERMS, BN, BK, SPLIT>;
   GL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
   const int grid = std::min(n_sms, a.n_units);
   kern<<<grid, C::THREADS, C::SMEM_BYTES, st>>>(map_a, map_b, a);
@@ -543,7 +634,7 @@ using namespace gl;
 
 extern "C" int64_t gl_gram_workspace_bytes(int64_t m, int n, int terms) {
   if (m < 0 || n < 2 || (terms != 2 && terms != 3)) return -1;
-  return (int64_t)gram_layout(m, n, terms).total;
+  return (int64_t)gram_layout(m, n, terms).total + 1024;   // + slack: the base is aligned up internally
 }
 
 extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, const void *row_scale,
@@ -555,7 +646,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
                                     (long long)m, (long long)ldx, n);
   if (layout != GL_LAYOUT_PACKED && layout != GL_LAYOUT_TILED) return fail(GL_E_ARG, "bad layout");
   if (terms != 2 && terms != 3) return fail(GL_E_ARG, "terms must be 2 or 3");
-  if (variant < 0 || variant > 3) return fail(GL_E_ARG, "variant must be 0..3");
+  if (variant < 0 || variant > 5) return fail(GL_E_ARG, "variant must be 0..5");
   if (layout == GL_LAYOUT_PACKED) {
     tile_begin = 0;
     tile_end = num_tiles(n);
@@ -564,12 +655,15 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
     return fail(GL_E_ARG, "bad tile range [%d,%d)", tile_begin, tile_end);
   if (tile_end == tile_begin) return GL_OK;
   const GramLayout L = gram_layout(m, n, terms);
-  if (!workspace || workspace_bytes < (int64_t)L.total)
-    return fail(GL_E_ARG, "workspace too small: need %lld bytes (gl_gram_workspace_bytes)", (long long)L.total);
-  if (reinterpret_cast<uintptr_t>(workspace) & 1023) return fail(GL_E_ARG, "workspace must be 1024-byte aligned");
+  // TMA and the swizzled operand planes want a 1024-byte aligned base: align up inside the buffer
+  const uintptr_t ws_raw = reinterpret_cast<uintptr_t>(workspace);
+  const uintptr_t ws_al = (ws_raw + 1023) & ~(uintptr_t)1023;
+  if (!workspace || workspace_bytes < (int64_t)(L.total + (ws_al - ws_raw)))
+    return fail(GL_E_ARG, "workspace too small: need %lld bytes (gl_gram_workspace_bytes)",
+                (long long)L.total + 1024);
   if (chunk <= 0) chunk = 256;
   cudaStream_t st = as_stream(stream);
-  unsigned char *ws = static_cast<unsigned char *>(workspace);
+  unsigned char *ws = reinterpret_cast<unsigned char *>(ws_al);
   int dev = 0, n_sms = 0, cc_major = 0;
   GL_CUDA(cudaGetDevice(&dev));
   GL_CUDA(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
@@ -582,18 +676,32 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   double *norms = reinterpret_cast<double *>(ws + L.off_norms);
   GL_CUDA(cudaMemsetAsync(norms, 0, (size_t)(L.n_pad + 256) * sizeof(double), st));
   const dim3 sgrid(L.n_pad / GR_SPLIT_TILE, L.segs);
-  if (terms == 2)
-    gram_split_kernel<2><<<sgrid, 256, 0, st>>>((const float *)X, m, n, ldx, (const float *)row_scale,
-                                                (const float *)col_shift, planes, L.m_pad, L.n_pad, norm_part, L.seg_len);
-  else
-    gram_split_kernel<3><<<sgrid, 256, 0, st>>>((const float *)X, m, n, ldx, (const float *)row_scale,
-                                                (const float *)col_shift, planes, L.m_pad, L.n_pad, norm_part, L.seg_len);
+  // The split-accumulator variants of the 3-term form carry the exact leading slice.  With 2 terms
+  // the residual slice alone cannot hold the bits the quantisation pushes into it, so the 2-term
+  // form keeps plain round-to-nearest bf16 slices (still with separate accumulators).
+  const bool exact0 = variant <= 1 && terms == 3;
+  int *colmax = reinterpret_cast<int *>(ws + L.off_colmax);
+  const float *Xf = (const float *)X, *rsf = (const float *)row_scale, *csf = (const float *)col_shift;
+  if (exact0) {
+    GL_CUDA(cudaMemsetAsync(colmax, 0, (size_t)L.n_pad * sizeof(int), st));
+    gram_colmax_kernel<<<sgrid, 256, 0, st>>>(Xf, m, n, ldx, rsf, csf, colmax, L.seg_len);
+    GL_LAUNCH_CHECK();
+  }
+#define GL_SPLIT(TERMS_, EX_)                                                                                \
+  gram_split_kernel<TERMS_, EX_><<<sgrid, 256, 0, st>>>(Xf, m, n, ldx, rsf, csf, planes, L.m_pad, L.n_pad, \
+                                                        norm_part, L.seg_len, colmax)
+  if (terms == 2) {
+    GL_SPLIT(2, false);
+  } else {
+    if (exact0) GL_SPLIT(3, true); else GL_SPLIT(3, false);
+  }
+#undef GL_SPLIT
   GL_LAUNCH_CHECK();
   gram_norm_reduce_kernel<<<(L.n_pad + 255) / 256, 256, 0, st>>>(norm_part, L.n_pad, L.segs, norms);
   GL_LAUNCH_CHECK();
 
   // ---- stage 2: work list + GEMM -------------------------------------------------------------------
-  const int bn = (variant & 1) ? 128 : 256;
+  const int bn = (variant == 2 || variant == 4) ? 256 : 128;
   const int nt = tiles_per_side(n);
   std::vector<int2> units;
   build_units(nt, bn / T, tile_begin, tile_end, units);
@@ -613,15 +721,26 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   a.nt = nt;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
-  // variant bit 0: BN (0 = 256, 1 = 128); bit 1: BK (0 = 32 / SWIZZLE_64B, 1 = 64 / SWIZZLE_128B)
-  const bool bk64 = (variant & 2) != 0;
+  // variant: 0 = split accumulators (precise, default), 128-wide units, 32-sample k-blocks (SWIZZLE_64B)
+  //          1 = same with 64-sample k-blocks (SWIZZLE_128B)
+  //          2 / 3 = single accumulator, 256- / 128-wide units, 32-sample k-blocks
+  //          4 / 5 = single accumulator, 256- / 128-wide units, 64-sample k-blocks
   if (terms == 3) {
-    if (bn == 256) {
-      if (bk64) return fail(GL_E_ARG, "terms=3, BN=256, BK=64 does not fit shared memory");
-      return launch_gram<3, 256, 32>(L, ws, a, n_sms, st);
+    switch (variant) {
+      case 0: return launch_gram<3, 128, 32, true>(L, ws, a, n_sms, st);
+      case 1: return launch_gram<3, 128, 64, true>(L, ws, a, n_sms, st);
+      case 2: return launch_gram<3, 256, 32, false>(L, ws, a, n_sms, st);
+      case 3: return launch_gram<3, 128, 32, false>(L, ws, a, n_sms, st);
+      case 4: return fail(GL_E_ARG, "terms=3 with 256-wide units and 64-sample k-blocks does not fit shared memory");
+      default: return launch_gram<3, 128, 64, false>(L, ws, a, n_sms, st);
     }
-    return bk64 ? launch_gram<3, 128, 64>(L, ws, a, n_sms, st) : launch_gram<3, 128, 32>(L, ws, a, n_sms, st);
   }
-  if (bn == 256) return bk64 ? launch_gram<2, 256, 64>(L, ws, a, n_sms, st) : launch_gram<2, 256, 32>(L, ws, a, n_sms, st);
-  return bk64 ? launch_gram<2, 128, 64>(L, ws, a, n_sms, st) : launch_gram<2, 128, 32>(L, ws, a, n_sms, st);
+  switch (variant) {
+    case 0: return launch_gram<2, 128, 32, true>(L, ws, a, n_sms, st);
+    case 1: return launch_gram<2, 128, 64, true>(L, ws, a, n_sms, st);
+    case 2: return launch_gram<2, 256, 32, false>(L, ws, a, n_sms, st);
+    case 3: return launch_gram<2, 128, 32, false>(L, ws, a, n_sms, st);
+    case 4: return launch_gram<2, 256, 64, false>(L, ws, a, n_sms, st);
+    default: return launch_gram<2, 128, 64, false>(L, ws, a, n_sms, st);
+  }
 }

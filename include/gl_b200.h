@@ -103,15 +103,20 @@ int gl_pdist_sq(const void *X_dev, int64_t m, int n, int64_t ldx, const void *ro
                 int dtype, void *stream);
 
 /* Tensor-core form of the same quantity, float32 only (north_star (1)): the Gram
- * matrix <y_i, y_j> runs as a tcgen05 / TMA GEMM on error-compensated bf16 operands
- * (`terms` = 2: y0+y1, 3 MMAs per k-step, ~16 significant bits; 3: y0+y1+y2, 6 MMAs, ~24 bits),
- * accumulated in TMEM over `chunk` samples at a time and folded into fp32 registers by the
- * epilogue warps (chunk <= 0: default 256); the norm epilogue |y_i|^2 + |y_j|^2 - 2<y_i,y_j>
- * (norms in float64, result clamped at 0 like a distance) is fused and writes either layout
- * directly.  `variant` selects the tile shape: bit 0 = 128-wide units (default 256), bit 1 =
- * 64-sample k-blocks / SWIZZLE_128B (default 32 / SWIZZLE_64B).  `workspace_dev` (1024-byte
- * aligned, gl_gram_workspace_bytes(m, n, terms) bytes) receives the split, transposed operand
- * planes.  Needs an sm_100 device. */
+ * matrix <y_i, y_j> runs as a tcgen05 / TMA GEMM on error-compensated bf16 slices of y
+ * (`terms` = 3: y0+y1+y2, 6 MMAs per k-step, float32-grade; 2: y0+y1, 3 MMAs, ~16 bits),
+ * accumulated in TMEM over `chunk` samples at a time (<= 0: default 256) and folded into registers
+ * by the epilogue warps; the norm epilogue |y_i|^2 + |y_j|^2 - 2<y_i,y_j> (norms in float64,
+ * result clamped at 0 like a distance) is fused and writes either layout directly.
+ * `variant`: 0 = precise (default): exact power-of-two-quantised leading slice (terms = 3),
+ *                separate TMEM accumulators for the leading and the small cross terms, float64
+ *                folds, 128-wide units, 32-sample k-blocks (SWIZZLE_64B);
+ *            1 = same with 64-sample k-blocks (SWIZZLE_128B);
+ *            2 / 3 = one fp32 accumulator, 256- / 128-wide units, 32-sample k-blocks (faster; the
+ *                tensor core's truncating accumulation leaves a bias of ~1e-5 |y|^2);
+ *            4 / 5 = same with 64-sample k-blocks (4 needs terms = 2).
+ * `workspace_dev` (any alignment, gl_gram_workspace_bytes(m, n, terms) bytes) receives the split,
+ * transposed operand planes.  Needs an sm_100 device. */
 int64_t gl_gram_workspace_bytes(int64_t m, int n, int terms);
 int gl_pdist_sq_gram(const void *X_dev, int64_t m, int n, int64_t ldx, const void *row_scale_dev,
                      const void *col_shift_dev, void *Z_dev, int layout, int tile_begin, int tile_end,

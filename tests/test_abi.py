@@ -45,6 +45,11 @@ def test_sizes(nat):
         assert lib.gl_num_tiles(n) == nt * (nt + 1) // 2
         assert lib.gl_tiled_elems(n) == nt * (nt + 1) // 2 * 128 * 128
     assert lib.gl_nodes_from_edges(7) == -1
+    # Gram workspace (host-only arithmetic): 3 bf16 planes of (n_pad, m_pad) dominate
+    need = lib.gl_gram_workspace_bytes(50000, 20000, 3)
+    assert 3 * 20096 * 50048 * 2 < need < 3 * 20096 * 50048 * 2 + (64 << 20)
+    assert lib.gl_gram_workspace_bytes(50000, 20000, 2) < need
+    assert lib.gl_gram_workspace_bytes(10, 1, 3) == -1 and lib.gl_gram_workspace_bytes(10, 5, 4) == -1
 
 
 @pytest.mark.parametrize("n,world", [(100, 2), (2000, 2), (20000, 8), (20000, 3), (300, 8)])
