@@ -510,16 +510,21 @@ def z_setup(a, z_ms, use_gram, terms, E, m, n, theta_ms, theta):
 
 
 def read_traffic(fraction=1.0):
-    """dram bytes per launch of the edge pass from the committed ncu capture (taken at N = 1, all
-    tiles), scaled by the fraction of the tiles this rank's launch covers."""
-    path = os.path.join(ROOT, "profiles", "edge_pass_traffic.json")
-    if os.path.exists(path):
-        try:
-            with open(path) as f:
-                v = json.load(f).get("dram_bytes_per_launch")
-                return None if v is None else v * fraction
-        except Exception:  # noqa: BLE001
-            return None
+    """dram bytes per launch of the dominant kernel from the committed ncu captures (taken at N = 1,
+    all tiles): per-iteration traffic x `fraction` (= share of the tiles this rank owns x iterations
+    per launch).  profiles/persistent_traffic.json (persistent kernel, 50 iterations per launch) is
+    preferred, profiles/edge_pass_traffic.json (one edge pass) is the older capture."""
+    for name, key in (("persistent_traffic.json", "dram_bytes_per_iteration"),
+                      ("edge_pass_traffic.json", "dram_bytes_per_launch")):
+        path = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(path):
+            try:
+                with open(path) as f:
+                    v = json.load(f).get(key)
+                if v is not None:
+                    return v * fraction
+            except Exception:  # noqa: BLE001
+                continue
     return None
 
 

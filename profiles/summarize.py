@@ -27,7 +27,14 @@ METRICS = [
     "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
     "sm__cycles_elapsed.max",
+    "sm__inst_executed_pipe_tensor.sum", "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+    "lts__t_bytes.sum", "lts__t_sectors_srcunit_tex_op_read.sum", "l1tex__m_xbar2l1tex_read_bytes.sum",
+    "lts__throughput.avg.pct_of_peak_sustained_elapsed", "launch__shared_mem_per_block_dynamic",
+    "smsp__cycles_active.avg", "sm__cycles_active.avg",
 ]
+OURS = ("persistent_kernel", "gram_kernel", "gram_split_kernel", "gram_colmax_kernel", "gram_norm_reduce_kernel",
+        "edge_pass_kernel", "node_tail_kernel", "edge_init_kernel", "theta_rows_kernel", "theta_mean_kernel",
+        "pdist_kernel", "knn_", "pack_to_tiles", "tiles_to_", "store_packed", "gram_edges_kernel")
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}
 
 
@@ -40,14 +47,15 @@ def launches(src, dst):
         agg[x["Kernel Name"][:90]][0] += 1
         agg[x["Kernel Name"][:90]][1] += v
     tot = sum(v[1] for v in agg.values())
-    ours = sum(v[1] for k, v in agg.items() if "gl::" in k)
+    is_ours = lambda k: "gl::" in k or any(t in k for t in OURS)  # noqa: E731  (newer ncu drops the namespace)
+    ours = sum(v[1] for k, v in agg.items() if is_ours(k))
     with open(dst, "w") as f:
         f.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none: {len(recs)} launches, "
                 f"{tot / 1e3:.3f} ms total, {ours / 1e3:.3f} ms in libgl_b200 kernels (gl::)\n")
         f.write("# per-launch times are cold-cache and serialised: compare SHARES\n")
         f.write(f"{'kernel':92s} {'count':>6s} {'total_ms':>10s} {'avg_us':>10s} {'share':>7s} {'share_of_gl':>11s}\n")
         for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-            sg = f"{v[1] / ours:11.3f}" if "gl::" in k else " " * 11
+            sg = f"{v[1] / ours:11.3f}" if is_ours(k) else " " * 11
             f.write(f"{k:92s} {v[0]:6d} {v[1] / 1e3:10.3f} {v[1] / v[0]:10.1f} {v[1] / tot:7.3f} {sg}\n")
 
 
