@@ -66,6 +66,8 @@ SIGNATURES = {
     "gl_solver_exchange_ptr": (c_void_p, [c_void_p, POINTER(c_int64)]),
     "gl_solver_run": (c_int, [c_void_p, c_int, c_void_p]),
     "gl_solver_status": (c_int, [c_void_p, _pi, _pd, _pd, _pi, c_void_p]),
+    "gl_solver_trace_enable": (c_int, [c_void_p]),
+    "gl_solver_trace_read": (c_int, [c_void_p, POINTER(c_int64), c_int]),
     "gl_solver_store": (c_int, [c_void_p, c_void_p, c_double, c_void_p]),
     "gl_solver_node_state": (c_int, [c_void_p, c_void_p, c_void_p]),
     "gl_logmodel_solve": (c_int, [c_void_p, _pd, c_int, c_int, c_int, c_double, c_double, c_void_p, c_int,

@@ -57,7 +57,7 @@ void free_all(gl_solver *s) {
   for (void *p : s->ipc_opened)
     if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
-                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar};
+                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -457,6 +457,20 @@ int gl_solver_store(gl_solver *s, void *w_packed, double edge_tol, void *stream)
     store_packed_kernel<double><<<grid, 256, 0, st>>>((const double *)s->w, s->gstride, (double *)w_packed,
                                                      s->tile_ij, s->n, edge_tol);
   GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+int gl_solver_trace_enable(gl_solver *s) {
+  if (!s) return fail(GL_E_ARG, "null solver");
+  if (!s->trace) GL_TRY(alloc_zero((void **)&s->trace, sizeof(long long) * TRACE_CAP * TRACE_STAMPS));
+  return GL_OK;
+}
+
+int gl_solver_trace_read(gl_solver *s, int64_t *stamps_host, int max_iters) {
+  if (!s || !s->trace) return fail(GL_E_STATE, "tracing is not enabled on this solver");
+  if (max_iters > TRACE_CAP) max_iters = TRACE_CAP;
+  if (max_iters <= 0) return GL_OK;
+  GL_CUDA(cudaMemcpy(stamps_host, s->trace, sizeof(long long) * TRACE_STAMPS * max_iters, cudaMemcpyDeviceToHost));
   return GL_OK;
 }
 

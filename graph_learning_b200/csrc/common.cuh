@@ -102,6 +102,13 @@ __device__ __forceinline__ void st_stream(double2 *p, const double2 &v) { __stcs
 __device__ __forceinline__ void st_release_sys(int *p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
+// Flag publication to all peers: ONE system-scope fence (orders everything this thread has observed,
+// i.e. the rank's partials made visible by the preceding grid barrier / kernel boundary), then
+// relaxed stores that do not wait for one another.  A st.release per peer costs a full NVLink
+// round trip each (measured: 16.6 us for 8 peers against ~2 us this way).
+__device__ __forceinline__ void st_relaxed_sys(int *p, int v) {
+  asm volatile("st.relaxed.sys.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ int ld_acquire_sys(const int *p) {
   int v;
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

@@ -178,7 +178,7 @@ __global__ void signal_kernel(int *hdr, PeerView peers, int world, int rank, con
   if (ld_volatile_int(flags + FLAG_DONE)) return;  // nothing was produced: never publish early
   __threadfence_system();
   const int seq = ld_volatile_int(hdr + HDR_SEQ);
-  for (int r = 0; r < world; ++r) st_release_sys(peers.hdr[r] + rank, seq + 1);
+  for (int r = 0; r < world; ++r) st_relaxed_sys(peers.hdr[r] + rank, seq + 1);
 }
 
 int launch_signal(gl_solver *s, cudaStream_t st) {

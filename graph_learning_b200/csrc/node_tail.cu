@@ -172,9 +172,9 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     clr_off = ((seq + 1) & 1) * A.xch_stride;
     // publish first: this kernel runs after the rank's edge pass has completed (stream order), so
     // its partials of exchange `seq` are final.  No fence or flag work inside the edge pass.
-    if (blockIdx.x == 0 && tid == 0) {
+    if (blockIdx.x == 0 && tid < A.world) {
       __threadfence_system();
-      for (int r = 0; r < A.world; ++r) st_release_sys(A.peers.hdr[r] + A.rank, seq + 1);
+      st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
     }
     if (tid < A.world) {
       const long long t0 = clock64();
@@ -192,9 +192,19 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     double sp, sw;
     if (A.world > 1) {
       sp = sw = 0.0;
-      for (int r = 0; r < A.world; ++r) {
-        sp += ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
-        sw += ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
+      double vp[GL_MAX_PEERS], vw[GL_MAX_PEERS];
+#pragma unroll
+      for (int r = 0; r < GL_MAX_PEERS; ++r) {
+        vp[r] = vw[r] = 0.0;
+        if (r < A.world) {
+          vp[r] = ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
+          vw[r] = ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < GL_MAX_PEERS; ++r) {
+        sp += vp[r];
+        sw += vw[r];
       }
       A.xch[clr_off + idx] = 0.0;
       A.xch[clr_off + total + idx] = 0.0;

@@ -25,6 +25,7 @@ template <typename F> struct PersistArgs {
   double *node_partial;  // [nchunks][2] dual residual / ||d'||^2 partials, then [2] rank-summed edge sums
   double *gprev, *resid;
   unsigned int *bar;
+  long long *trace;   // nullable: [TRACE_CAP][TRACE_STAMPS] globaltimer stamps of CTA 0
   double gamma, four_ag, tol;
   int maxit, iters, nchunks;
 };
@@ -34,6 +35,17 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+
+__device__ __forceinline__ long long global_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// CTA 0 / thread 0 stamps the phase boundaries of iteration `it` (tracing only)
+#define GL_STAMP(k)                                                                              \
+  do {                                                                                           \
+    if (P.trace && blockIdx.x == 0 && tid == 0) P.trace[(it % TRACE_CAP) * TRACE_STAMPS + (k)] = global_ns(); \
+  } while (0)
 
 __device__ __forceinline__ void grid_barrier(unsigned *bar, unsigned &gen) {
   __syncthreads();
@@ -86,6 +98,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
     const int64_t clr_off = (A.world > 1 ? ((seq + 1) & 1) : 0) * A.xch_stride;
     double *const xb = A.xch + rd_off;
     // ---------------- E phase --------------------------------------------------------------------
+    GL_STAMP(0);
     double r2acc = 0.0, w2acc = 0.0;
     for (int t = blockIdx.x; t < A.ntl; t += gridDim.x) {
       double r2 = 0.0, w2 = 0.0;
@@ -100,7 +113,9 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
       A.cta_partial[2 * blockIdx.x] = r2acc;
       A.cta_partial[2 * blockIdx.x + 1] = w2acc;
     }
+    GL_STAMP(1);
     grid_barrier(P.bar, gen);
+    GL_STAMP(2);
     // ---------------- N phase --------------------------------------------------------------------
     if (blockIdx.x == 0) {
       double r2 = 0.0, w2 = 0.0;
@@ -112,13 +127,14 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
       if (tid == 0) {
         xb[2 * total] += r2;      // slot was cleared; += keeps the classic kernels' convention
         xb[2 * total + 1] += w2;
-        if (A.world > 1) {
-          __threadfence_system();
-          for (int r = 0; r < A.world; ++r) st_release_sys(A.peers.hdr[r] + A.rank, seq + 1);
-        }
       }
       __syncthreads();
+      if (A.world > 1 && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
+        __threadfence_system();
+        st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
+      }
     }
+    GL_STAMP(3);
     for (int c = blockIdx.x; c < P.nchunks; c += gridDim.x) {
       if (A.world > 1) {
         if (tid < A.world) {
@@ -132,14 +148,26 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
         }
         __syncthreads();
       }
+      if (c == 0) GL_STAMP(4);
       const int64_t idx = (int64_t)c * EDGE_THREADS + tid;
       double my_rb2 = 0.0, my_d2 = 0.0;
       if (idx < total) {
         double sp = 0.0, sw = 0.0;
         if (A.world > 1) {
-          for (int r = 0; r < A.world; ++r) {
-            sp += ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
-            sw += ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
+          // all peer loads in flight together (one NVLink round trip), summed in rank order
+          double vp[GL_MAX_PEERS], vw[GL_MAX_PEERS];
+#pragma unroll
+          for (int r = 0; r < GL_MAX_PEERS; ++r) {
+            vp[r] = vw[r] = 0.0;
+            if (r < A.world) {
+              vp[r] = ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
+              vw[r] = ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
+            }
+          }
+#pragma unroll
+          for (int r = 0; r < GL_MAX_PEERS; ++r) {
+            sp += vp[r];
+            sw += vw[r];
           }
         } else {
           sp = __ldcg(xb + idx);
@@ -187,7 +215,9 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
         }
       }
     }
+    GL_STAMP(5);
     grid_barrier(P.bar, gen);
+    GL_STAMP(6);
     // ---------------- decision: identical on every CTA -----------------------------------------------
     double rb2 = 0.0, d2 = 0.0;
     for (int i = tid; i < P.nchunks; i += EDGE_THREADS) {
@@ -205,6 +235,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
     }
     gw_prev = g_w;
     gd_prev = d2;
+    GL_STAMP(7);
     const bool had_check = it >= 1;
     ++it;
     if (A.world > 1) ++seq;
@@ -259,6 +290,7 @@ template <typename F> static int persistent_launch_t(gl_solver *s, int iters, cu
   P.gprev = s->gprev;
   P.resid = s->resid;
   P.bar = s->grid_bar;
+  P.trace = s->trace;
   P.gamma = s->gamma;
   P.four_ag = 4.0 * s->alpha * s->gamma;
   P.tol = s->tol;

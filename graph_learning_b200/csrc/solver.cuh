@@ -17,6 +17,7 @@ enum {
 // Header ints: sig[r] (r < 8) = last exchange sequence number rank r has published to this rank;
 // HDR_SEQ = number of exchanges this rank has consumed (buffer parity = seq & 1).
 constexpr int GL_MAX_PEERS = 8;
+constexpr int TRACE_CAP = 4096, TRACE_STAMPS = 8;
 constexpr int COMM_HDR = 64;  // doubles (512 B)
 constexpr int HDR_SEQ = 16;
 struct PeerView {
@@ -53,6 +54,7 @@ struct gl_solver {
   int *flags = nullptr;           // [FLAG_COUNT]
   unsigned int *grid_bar = nullptr;  // grid barrier counter of the persistent kernel
   int persist_grid = 0;           // resident CTAs of the persistent kernel (0 = not sized yet)
+  long long *trace = nullptr;     // optional phase timestamps of the persistent kernel: [TRACE_CAP][TRACE_STAMPS] ns
 
   // parameters of the current solve
   double alpha = 1, beta = 1, step = 0.5, gamma = 0, c = 0, tol = 1e-5;

@@ -129,6 +129,17 @@ class Solver:
 
     __del__ = close
 
+    # -- optional phase tracing of the persistent kernel (profiling aid, K == 1) -----------------------
+    def trace_enable(self) -> None:
+        nat.check(self.lib.gl_solver_trace_enable(self._h))
+
+    def trace_read(self, n_iters: int) -> np.ndarray:
+        """(n_iters, 8) int64 %globaltimer stamps (ns) of CTA 0, see ``gl_solver_trace_read``."""
+        n_iters = min(int(n_iters), 4096)
+        out = np.zeros((n_iters, 8), dtype=np.int64)
+        nat.check(self.lib.gl_solver_trace_read(self._h, out.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)), n_iters))
+        return out
+
     def load(self, z_packed: torch.Tensor, z_scale=None, w_packed: Optional[torch.Tensor] = None):
         assert z_packed.is_cuda and z_packed.dtype == self.dtype and z_packed.is_contiguous()
         assert z_packed.numel() == self.K * self.n_edges

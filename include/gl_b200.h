@@ -183,6 +183,12 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream);
 /* Read back iteration count and the last relative residuals (synchronises the stream). */
 int gl_solver_status(gl_solver *s, int *n_iter, double *rel_primal, double *rel_dual,
                      int *converged, void *stream);
+/* Optional phase tracing of the persistent iteration kernel (K == 1): after enabling, CTA 0 stamps
+ * %globaltimer (ns) at 8 phase boundaries of every iteration: [E start, E done, after barrier 1,
+ * after fold+publish, after peer-flag wait, node chunk done, after barrier 2, after decision].
+ * gl_solver_trace_read copies the first max_iters x 8 stamps (iteration index modulo 4096). */
+int gl_solver_trace_enable(gl_solver *s);
+int gl_solver_trace_read(gl_solver *s, int64_t *stamps_host, int max_iters);
 /* Results: packed (K,E) with the edge_tol threshold applied (smooth_learning.py:169); or the
  * raw node state for tests. */
 int gl_solver_store(gl_solver *s, void *w_packed_dev, double edge_tol, void *stream);
