@@ -74,6 +74,7 @@ SIGNATURES = {
                                   c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p]),
     "gl_logmodel_solve_host": (c_int, [c_void_p, _pd, c_int, c_int, c_int, c_double, c_double, c_void_p, c_int,
                                        c_double, c_double, c_double, c_void_p, _pi, _pd, _pd]),
+    "gl_knn_build": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "gl_knn_logmodel_solve": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_double, c_double,
                                       c_int, c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p]),
 }

@@ -5,8 +5,20 @@
 // columns of the support, and step size gamma = step / (2 beta + sqrt(2 d_max)) (signless-Laplacian
 // bound on ||S_mask||_2; equals smooth_learning.py:135-137 on the complete graph).  Parity is
 // pinned against oracle/logmodel_oracle.py::solve_knn and, with the complete edge list, against the
-// dense solver.  Algorithmic traffic: 20 B per stored edge per iteration in fp32 (i, j, w, z, w').
-// The node tail is the dense solver's (node_tail.cu) on a workspace that owns no tiles.
+// dense solver.
+//
+// Layout: every undirected edge (i, j) is stored TWICE, as directed slots i->j and j->i, sorted by
+// source node, each slot carrying its own copy of w and z.  Both copies apply the same update
+// (a_i + a_j is commutative, so they stay bit-identical), and each slot contributes only to the
+// degree sums of its SOURCE node: consecutive slots share the source, a warp reduces its 32 slots by
+// segments with shuffles and issues one float64 atomic per (warp, source node) instead of four per
+// edge, and nothing is scattered to the far end of an edge.  Traffic: 20 B per slot = 40 B per
+// undirected edge per iteration in fp32 (src, dst, w, z, w'); SURVEY 8(d)'s algorithmic figure of
+// 20 B per stored edge is what roofline.achieved is quoted on.  The node vectors (a, b: 4 B x n) are
+// L2-resident gathers.  The node tail is the dense solver's (node_tail.cu) on a workspace that owns
+// no tiles.
+#include <cub/device/device_radix_sort.cuh>
+
 #include "solver.cuh"
 
 namespace gl {
@@ -32,45 +44,99 @@ __global__ void knn_max_kernel(const int *cnt, int n, int *out) {
   if (threadIdx.x == 0) *out = s[0];
 }
 
-// MODE 0: iteration.  MODE 1: initial degrees S w0 and ||w0||^2.
+// undirected list -> unsorted directed slots (key = source node, value = undirected edge id)
+__global__ void knn_expand_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, int32_t *key, int32_t *val) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
+    key[2 * e] = ei[e];
+    val[2 * e] = (int32_t)e;
+    key[2 * e + 1] = ej[e];
+    val[2 * e + 1] = (int32_t)e;
+  }
+}
+// sorted slots: fill in the far end and this slot's copies of z and w
+template <typename F>
+__global__ void knn_fill_kernel(const int32_t *ei, const int32_t *ej, const F *z, const F *w, int64_t nslots,
+                                const int32_t *src, const int32_t *eid, int32_t *dst, F *zs, F *ws) {
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t e = eid[s], i = ei[e], j = ej[e];
+    dst[s] = src[s] == i ? j : i;
+    zs[s] = z[e];
+    ws[s] = w[e];
+  }
+}
+// result back in the caller's edge order, from the slot whose source is the edge's first end; the
+// edge_tol threshold of smooth_learning.py:169 applied on the way
+template <typename F>
+__global__ void knn_writeback_kernel(const int32_t *ei, const int32_t *src, const int32_t *eid, const F *ws,
+                                     int64_t nslots, double edge_tol, F *w) {
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t e = eid[s];
+    if (src[s] == ei[e]) {
+      const F v = ws[s];
+      w[e] = (double)v < edge_tol ? F(0) : v;
+    }
+  }
+}
+
+// MODE 0: iteration.  MODE 1: initial degrees S w0 and ||w0||^2.  One thread per directed slot,
+// warps own 32 consecutive slots; gsum receives HALF the slot sums (every edge appears twice).
 template <typename F, int MODE>
-__global__ void __launch_bounds__(KNN_THREADS) knn_edge_kernel(const int32_t *__restrict__ ei,
-                                                               const int32_t *__restrict__ ej,
+__global__ void __launch_bounds__(KNN_THREADS) knn_slot_kernel(const int32_t *__restrict__ src,
+                                                               const int32_t *__restrict__ dst,
                                                                const F *__restrict__ z, F *__restrict__ w,
-                                                               int64_t nnz, const F *__restrict__ a,
+                                                               int64_t nslots, const F *__restrict__ a,
                                                                const F *__restrict__ b, double *sp, double *sw,
                                                                double *gsum, const int *flags, F c, F tgz) {
   if (MODE == 0 && *reinterpret_cast<const volatile int *>(flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][2];
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   double res = 0.0, wsq = 0.0;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
-    const int i = ei[e], j = ej[e];
-    const F wo = w[e];
-    if (MODE == 1) {
-      atomicAdd(sw + i, (double)wo);
-      atomicAdd(sw + j, (double)wo);
-      wsq += (double)wo * (double)wo;
-    } else {
-      const F y = c * wo - (a[i] + a[j]);
-      F p = y - tgz * z[e];
-      p = p > F(0) ? p : F(0);
-      const F q = c * p - (b[i] + b[j]);
-      const F r = q - y;
-      const F wn = (wo - y) + q;
-      w[e] = wn;
-      if (p != F(0)) {
-        atomicAdd(sp + i, (double)p);
-        atomicAdd(sp + j, (double)p);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t s0 = (int64_t)blockIdx.x * blockDim.x + wp * 32; s0 < nslots; s0 += stride) {
+    const int64_t s = s0 + lane;
+    const bool valid = s < nslots;
+    int i = -1;
+    double vp = 0.0, vw = 0.0;
+    if (valid) {
+      i = src[s];
+      const F wo = w[s];
+      if (MODE == 1) {
+        vw = (double)wo;
+        wsq += vw * vw;
+      } else {
+        const int j = dst[s];
+        const F y = c * wo - (a[i] + a[j]);
+        F p = y - tgz * z[s];
+        p = p > F(0) ? p : F(0);
+        const F q = c * p - (b[i] + b[j]);
+        const F r = q - y;
+        const F wn = (wo - y) + q;
+        w[s] = wn;
+        vp = (double)p;
+        vw = (double)wn;
+        res += (double)r * (double)r;
+        wsq += vw * vw;
       }
-      atomicAdd(sw + i, (double)wn);
-      atomicAdd(sw + j, (double)wn);
-      res += (double)r * (double)r;
-      wsq += (double)wn * (double)wn;
+    }
+    // segmented suffix sums over runs of equal source (slots are sorted by source)
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int io = __shfl_down_sync(0xffffffffu, i, off);
+      const double po = __shfl_down_sync(0xffffffffu, vp, off);
+      const double wo2 = __shfl_down_sync(0xffffffffu, vw, off);
+      if (lane + off < 32 && io == i) {
+        vp += po;
+        vw += wo2;
+      }
+    }
+    const int iprev = __shfl_up_sync(0xffffffffu, i, 1);
+    if (valid && (lane == 0 || iprev != i)) {
+      if (MODE == 0 && vp != 0.0) atomicAdd(sp + i, vp);
+      atomicAdd(sw + i, vw);
     }
   }
   res = warp_sum(res);
   wsq = warp_sum(wsq);
-  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   if (lane == 0) {
     s_red[wp][0] = res;
     s_red[wp][1] = wsq;
@@ -82,14 +148,9 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_edge_kernel(const int32_t *__
       r2 += s_red[q][0];
       w2 += s_red[q][1];
     }
-    if (MODE == 0) atomicAdd(gsum, r2);
-    atomicAdd(gsum + 1, w2);
+    if (MODE == 0) atomicAdd(gsum, 0.5 * r2);
+    atomicAdd(gsum + 1, 0.5 * w2);
   }
-}
-
-template <typename F> __global__ void knn_threshold_kernel(F *w, int64_t nnz, double edge_tol) {
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x)
-    if ((double)w[e] < edge_tol) w[e] = F(0);
 }
 
 template <typename F>
@@ -102,7 +163,14 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
   int *cnt = nullptr;
   int *h_flags = nullptr;
   cudaGraphExec_t gexec = nullptr;
+  // directed, source-sorted slots
+  const int64_t nslots = 2 * nnz;
+  int32_t *key_in = nullptr, *val_in = nullptr, *src = nullptr, *eid = nullptr, *dst = nullptr;
+  F *zs = nullptr, *ws = nullptr;
+  void *sort_tmp = nullptr;
   auto done = [&](int code) {
+    for (void *q : {(void *)key_in, (void *)val_in, (void *)src, (void *)eid, (void *)dst, (void *)zs, (void *)ws, sort_tmp})
+      if (q) cudaFree(q);
     if (cnt) cudaFree(cnt);
     if (h_flags) cudaFreeHost(h_flags);
     if (gexec) cudaGraphExecDestroy(gexec);
@@ -116,7 +184,9 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
       return done(fail(GL_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),   \
                        __FILE__, __LINE__));                                                \
   } while (0)
+  if (nslots >= (int64_t)1 << 31) return done(fail(GL_E_SHAPE, "edge list too long for 32-bit slot ids"));
   const int grid = (int)std::min<int64_t>((nnz + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+  const int sgrid = (int)std::min<int64_t>((nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
   // d_max of the support
   KNN_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * ((size_t)n + 1)));
   KNN_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int) * ((size_t)n + 1), st));
@@ -130,6 +200,27 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
     KNN_CUDA(cudaMemcpyAsync(&dmax, cnt + n, sizeof(int), cudaMemcpyDeviceToHost, st));
     KNN_CUDA(cudaStreamSynchronize(st));
   }
+  if (nnz > 0) {
+    const size_t ib = sizeof(int32_t) * (size_t)nslots, fb = sizeof(F) * (size_t)nslots;
+    KNN_CUDA(cudaMalloc((void **)&key_in, ib));
+    KNN_CUDA(cudaMalloc((void **)&val_in, ib));
+    KNN_CUDA(cudaMalloc((void **)&src, ib));
+    KNN_CUDA(cudaMalloc((void **)&eid, ib));
+    KNN_CUDA(cudaMalloc((void **)&dst, ib));
+    KNN_CUDA(cudaMalloc((void **)&zs, fb));
+    KNN_CUDA(cudaMalloc((void **)&ws, fb));
+    knn_expand_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, key_in, val_in);
+    g_launches.fetch_add(1);
+    int bits = 1;
+    while (bits < 31 && ((int64_t)1 << bits) < (int64_t)n) ++bits;
+    size_t tmp_bytes = 0;
+    KNN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, key_in, src, val_in, eid, (int)nslots, 0, bits, st));
+    KNN_CUDA(cudaMalloc(&sort_tmp, tmp_bytes ? tmp_bytes : 16));
+    KNN_CUDA(cub::DeviceRadixSort::SortPairs(sort_tmp, tmp_bytes, key_in, src, val_in, eid, (int)nslots, 0, bits, st));
+    knn_fill_kernel<F><<<sgrid, KNN_THREADS, 0, st>>>(ei, ej, z, w, nslots, src, eid, dst, zs, ws);
+    g_launches.fetch_add(1);
+    KNN_CUDA(cudaGetLastError());
+  }
   s->alpha = alpha; s->beta = beta; s->step = step_size; s->maxit = maxit; s->tol = tol;
   s->gamma = step_size / (2.0 * beta + std::sqrt(2.0 * (double)dmax));
   s->c = 1.0 - 2.0 * s->gamma * beta;
@@ -138,8 +229,8 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
   KNN_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
   KNN_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
   if (nnz > 0) {
-    knn_edge_kernel<F, 1><<<grid, KNN_THREADS, 0, st>>>(ei, ej, z, w, nnz, (const F *)s->a, (const F *)s->b, sp,
-                                                       sw, gsum, s->flags, c, tgz);
+    knn_slot_kernel<F, 1><<<sgrid, KNN_THREADS, 0, st>>>(src, dst, zs, ws, nslots, (const F *)s->a, (const F *)s->b,
+                                                        sp, sw, gsum, s->flags, c, tgz);
     g_launches.fetch_add(1);
     KNN_CUDA(cudaGetLastError());
   }
@@ -161,8 +252,8 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
   if (ce == cudaSuccess) {
     for (int i = 0; i < chunk && rc == GL_OK; ++i) {
       if (nnz > 0)
-        knn_edge_kernel<F, 0><<<grid, KNN_THREADS, 0, cs>>>(ei, ej, z, w, nnz, (const F *)s->a, (const F *)s->b,
-                                                           sp, sw, gsum, s->flags, c, tgz);
+        knn_slot_kernel<F, 0><<<sgrid, KNN_THREADS, 0, cs>>>(src, dst, zs, ws, nslots, (const F *)s->a,
+                                                            (const F *)s->b, sp, sw, gsum, s->flags, c, tgz);
       rc = launch_node_tail(s, false, cs);
     }
     ce = cudaStreamEndCapture(cs, &graph);
@@ -189,7 +280,7 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
   if (ce != cudaSuccess) return done(fail(GL_E_CUDA, "kNN solve failed: %s", cudaGetErrorString(ce)));
   rc = gl_solver_status(s, n_iter, rel_primal, rel_dual, nullptr, st);
   if (rc == GL_OK && nnz > 0) {
-    knn_threshold_kernel<F><<<grid, KNN_THREADS, 0, st>>>(w, nnz, edge_tol);
+    knn_writeback_kernel<F><<<sgrid, KNN_THREADS, 0, st>>>(ei, src, eid, ws, nslots, edge_tol, w);
     g_launches.fetch_add(1);
     KNN_CUDA(cudaGetLastError());
     KNN_CUDA(cudaStreamSynchronize(st));

@@ -13,9 +13,63 @@ import numpy as np
 import torch
 
 from . import _native as nat
-from .smooth_learning import SolveInfo, _gl_dtype, _ptr, _stream, _to_device, _torch_dtype
+from sklearn.base import BaseEstimator
 
-__all__ = ["gsp_learn_graph_log_degrees_knn"]
+from .smooth_learning import SolveInfo, _gl_dtype, _ptr, _stream, _theta_dense, _to_device, _torch_dtype
+
+__all__ = ["gsp_learn_graph_log_degrees_knn", "knn_search", "knn_graph", "theta_from_knn", "KNNLogModel"]
+
+
+def knn_search(x, k: int):
+    """k nearest neighbours between the COLUMNS of x (m, n) by exact brute force on the device
+    (``gl_knn_build``).  Returns CUDA tensors ``idx`` (n, k) int32 and ``d2`` (n, k) float32 of
+    squared distances, ascending per row, self excluded."""
+    xd = _to_device(x, torch.float32)
+    if xd.ndim != 2:
+        raise ValueError("signals must be a (n_samples, n_nodes) matrix")
+    m, n = xd.shape
+    idx = torch.empty((n, k), dtype=torch.int32, device=xd.device)
+    d2 = torch.empty((n, k), dtype=torch.float32, device=xd.device)
+    nat.check(nat.lib().gl_knn_build(_ptr(xd), m, n, xd.stride(0), int(k), _ptr(idx), _ptr(d2), _stream()))
+    return idx, d2
+
+
+def knn_graph(x, k: int):
+    """Symmetrised kNN support: the undirected edges {i, j} with j among the k nearest of i or i
+    among those of j, as ``(ei, ej, d2)`` with ei < ej, sorted by (ei, ej), plus the raw search
+    result.  The edge assembly (canonical order, de-duplication) is torch glue on the device."""
+    idx, d2 = knn_search(x, k)
+    n = idx.shape[0]
+    rows = torch.arange(n, device=idx.device, dtype=torch.int64)[:, None].expand(-1, k)
+    cols = idx.to(torch.int64)
+    ok = cols >= 0
+    lo = torch.minimum(rows, cols)[ok]
+    hi = torch.maximum(rows, cols)[ok]
+    key, first = _unique_first(lo * n + hi)
+    ei = torch.div(key, n, rounding_mode="floor").to(torch.int32)
+    ej = (key % n).to(torch.int32)
+    return ei, ej, d2[ok][first], (idx, d2)
+
+
+def _unique_first(key: torch.Tensor):
+    """Sorted unique keys and, for each, the position of one occurrence (d(i,j) == d(j,i) bit for
+    bit, so any occurrence carries the same distance)."""
+    order = torch.argsort(key)
+    ks = key[order]
+    keep = torch.ones_like(ks, dtype=torch.bool)
+    keep[1:] = ks[1:] != ks[:-1]
+    return ks[keep], order[keep]
+
+
+def theta_from_knn(d2_sorted: torch.Tensor, avg_degree: int) -> float:
+    """The reference's theta heuristic (smooth_learning.py:201-219) from kNN lists: the statistic only
+    reads the avg_degree + 1 smallest entries of every row of the square distance matrix (the zero
+    diagonal included), which the lists hold exactly when k >= avg_degree."""
+    n, k = d2_sorted.shape
+    if k < avg_degree:
+        raise ValueError(f"need k >= avg_degree neighbours per node (k={k}, avg_degree={avg_degree})")
+    mat = torch.cat([torch.zeros((n, 1), dtype=d2_sorted.dtype, device=d2_sorted.device), d2_sorted], dim=1)
+    return _theta_dense(mat.contiguous(), int(avg_degree))
 
 
 def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: float = 1.0, beta: float = 1.0,
@@ -46,3 +100,43 @@ def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: floa
     info = SolveInfo(it.value, rp.value, rd.value, bool(rp.value < tol and rd.value < tol))
     out = w.cpu().numpy() if is_np else w
     return (out, info) if return_info else out
+
+
+class KNNLogModel(BaseEstimator):
+    """LogModel on a kNN-restricted support (BASELINE config 5; Kalofolias & Perraudin 2019): kNN
+    search, theta for the requested degree from the kNN lists, and the sparse-support solve, all on
+    the device.  No reference estimator exists for it; the parameters mirror ``LogModel``.
+
+    Attributes: ``edges_`` (2, nnz) int32 with ei < ej, ``weights_`` (nnz,), ``theta_``,
+    ``n_iter_``; :meth:`to_sparse` gives the symmetric scipy CSR matrix."""
+
+    def __init__(self, avg_degree: int = 10, n_neighbors: int = 20, *, maxit: int = 1000, tol: float = 1e-5,
+                 step_size: float = 0.5, edge_tol: float = 1e-3) -> None:
+        self.avg_degree = avg_degree
+        self.n_neighbors = n_neighbors
+        self.maxit = maxit
+        self.tol = tol
+        self.step_size = step_size
+        self.edge_tol = edge_tol
+
+    def fit(self, x):
+        is_np = not isinstance(x, torch.Tensor)
+        ei, ej, d2, (_, d2_lists) = knn_graph(x, self.n_neighbors)
+        self.n_nodes_ = int(d2_lists.shape[0])
+        self.theta_ = theta_from_knn(d2_lists, self.avg_degree)
+        w, info = gsp_learn_graph_log_degrees_knn(ei, ej, d2 * self.theta_, self.n_nodes_, maxit=self.maxit,
+                                                  tol=self.tol, step_size=self.step_size, edge_tol=self.edge_tol,
+                                                  return_info=True)
+        edges = torch.stack([ei, ej])
+        self.edges_ = edges.cpu().numpy() if is_np else edges
+        self.weights_ = w.cpu().numpy() if is_np else w
+        self.n_iter_, self.rel_primal_, self.rel_dual_, self.converged_ = (info.n_iter, info.rel_primal,
+                                                                           info.rel_dual, info.converged)
+        return self
+
+    def to_sparse(self):
+        from scipy import sparse
+        e = np.asarray(self.edges_.cpu() if isinstance(self.edges_, torch.Tensor) else self.edges_)
+        w = np.asarray(self.weights_.cpu() if isinstance(self.weights_, torch.Tensor) else self.weights_)
+        a = sparse.coo_matrix((w, (e[0], e[1])), shape=(self.n_nodes_, self.n_nodes_))
+        return (a + a.T).tocsr()

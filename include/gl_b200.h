@@ -216,6 +216,15 @@ int gl_knn_logmodel_solve(const int32_t *ei_dev, const int32_t *ej_dev, const vo
                           double tol, double step_size, double edge_tol, void *w_dev, int *n_iter,
                           double *rel_primal, double *rel_dual, void *stream);
 
+/* k nearest neighbours between the COLUMNS of X (m, n) float32 (no reference code):
+ * exact brute force on squared Euclidean distances, fused distance + selection (the n x n matrix
+ * is never written).  idx_out (n, k) int32 and d2_out (n, k) float32, ascending per row, self
+ * excluded, ties by smaller index; unused entries (n - 1 < k) hold -1 / +inf.  1 <= k <= 32.
+ * theta for a requested degree then follows from gl_theta_dense on [0 | d2] (n, k + 1): the
+ * reference statistic (smooth_learning.py:201-219) only reads the k + 1 smallest entries of a row. */
+int gl_knn_build(const void *X_dev, int64_t m, int n, int64_t ldx, int k, int32_t *idx_out_dev,
+                 void *d2_out_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,3 +58,77 @@ def test_knn_warm_start_and_empty():
     w = knn(ei, ej, z, n, edge_init=init, maxit=20, edge_tol=-np.inf)
     assert rel(w, wo) < 1e-12
     assert knn(np.zeros(0, int), np.zeros(0, int), np.zeros(0), n, maxit=3).shape == (0,)
+
+
+# ---- kNN front end (N3): search, symmetrised support, theta from the lists, estimator ---------------
+def _points(n, dim, seed):
+    return np.random.default_rng(seed).uniform(size=(dim, n)).astype(np.float32)  # (m, n): nodes = columns
+
+
+@pytest.mark.parametrize("n,dim,k", [(50, 2, 4), (300, 3, 10), (1000, 8, 20), (129, 40, 32), (20, 3, 32)])
+def test_knn_search_vs_bruteforce(n, dim, k):
+    from graph_learning_b200.knn import knn_search
+    x = _points(n, dim, n + k)
+    idx, d2 = knn_search(x, k)
+    idx, d2 = idx.cpu().numpy(), d2.cpu().numpy()
+    zsq = orc.to_square(orc.pdist_sq(x.astype(np.float64)))
+    np.fill_diagonal(zsq, np.inf)
+    kk = min(k, n - 1)
+    order = np.argsort(zsq, axis=1, kind="stable")[:, :kk]
+    ref_d = np.take_along_axis(zsq, order, axis=1)
+    assert np.all(np.diff(d2[:, :kk], axis=1) >= 0)                      # ascending
+    assert np.allclose(d2[:, :kk], ref_d, rtol=2e-6, atol=1e-12)
+    assert (idx[:, :kk] != np.arange(n)[:, None]).all()                  # self excluded
+    # the index sets agree wherever the k-th and (k+1)-th distances are separated
+    if kk < n - 1:
+        nxt = np.sort(zsq, axis=1)[:, kk]
+        clear = (nxt - ref_d[:, -1]) > 1e-5 * nxt
+        same = np.array([set(a) == set(b) for a, b in zip(idx[:, :kk], order)])
+        assert same[clear].all() and clear.mean() > 0.9
+    else:
+        assert (np.sort(idx[:, :kk], axis=1) == np.sort(order, axis=1)).all()
+        assert (idx[:, kk:] == -1).all() and np.isinf(d2[:, kk:]).all()
+
+
+def test_knn_graph_matches_oracle_support():
+    from graph_learning_b200.knn import knn_graph
+    n, k = 400, 6
+    x = _points(n, 3, 7)
+    ei, ej, d2, _ = knn_graph(x, k)
+    zsq = orc.to_square(orc.pdist_sq(x.astype(np.float64)))
+    oi, oj = orc.knn_support(zsq, k)
+    assert np.array_equal(ei.cpu().numpy(), oi) and np.array_equal(ej.cpu().numpy(), oj)
+    assert np.allclose(d2.cpu().numpy(), zsq[oi, oj], rtol=2e-6)
+
+
+def test_theta_from_knn_equals_dense_theta():
+    from graph_learning_b200.knn import knn_search, theta_from_knn
+    n, k = 300, 12
+    x = _points(n, 3, 3)
+    _, d2 = knn_search(x, k)
+    zsq = orc.to_square(orc.pdist_sq(x.astype(np.float64)))
+    for deg in (3, 8, 12):
+        ref = orc.theta_for_degree(zsq, deg)
+        assert abs(theta_from_knn(d2, deg) - ref) < 5e-6 * ref
+    with pytest.raises(ValueError):
+        theta_from_knn(d2, 13)
+
+
+def test_knn_logmodel_estimator_end_to_end():
+    """KNNLogModel.fit = search + theta + sparse solve; against the oracle chain on the same data."""
+    from graph_learning_b200.knn import KNNLogModel
+    n, k, deg = 500, 10, 5
+    x = _points(n, 3, 11)
+    mdl = KNNLogModel(avg_degree=deg, n_neighbors=k, maxit=300).fit(x)
+    zsq = orc.to_square(orc.pdist_sq(x.astype(np.float64)))
+    oi, oj = orc.knn_support(zsq, k)
+    theta = orc.theta_for_degree(zsq, deg)
+    wo, io = orc.solve_knn(oi, oj, zsq[oi, oj] * theta, n, maxit=300)
+    assert np.array_equal(mdl.edges_[0], oi) and np.array_equal(mdl.edges_[1], oj)
+    assert abs(mdl.theta_ - theta) < 5e-6 * theta
+    assert mdl.n_iter_ == io.n_iter
+    assert rel(mdl.weights_, wo) < 1e-4
+    a = mdl.to_sparse()
+    assert a.shape == (n, n) and abs(a - a.T).max() == 0
+    mean_deg = (a > 0).sum() / n
+    assert 0.5 * deg < mean_deg < 2.0 * deg   # the heuristic targets avg_degree neighbours per node
