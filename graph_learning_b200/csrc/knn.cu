@@ -19,11 +19,17 @@
 // no tiles.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <math_constants.h>
+
 #include "solver.cuh"
 
 namespace gl {
 
 constexpr int KNN_THREADS = 256;
+constexpr int KNN_UNROLL = 4;
+template <typename F> struct Vec2;
+template <> struct Vec2<float> { using type = float2; };
+template <> struct Vec2<double> { using type = double2; };
 
 __global__ void knn_degree_count_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, int *cnt) {
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
@@ -84,55 +90,80 @@ template <typename F, int MODE>
 __global__ void __launch_bounds__(KNN_THREADS) knn_slot_kernel(const int32_t *__restrict__ src,
                                                                const int32_t *__restrict__ dst,
                                                                const F *__restrict__ z, F *__restrict__ w,
-                                                               int64_t nslots, const F *__restrict__ a,
-                                                               const F *__restrict__ b, double *sp, double *sw,
+                                                               int64_t nslots,
+                                                               const typename Vec2<F>::type *__restrict__ ab,
+                                                               double *sp, double *sw,
                                                                double *gsum, const int *flags, F c, F tgz) {
   if (MODE == 0 && *reinterpret_cast<const volatile int *>(flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][2];
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   double res = 0.0, wsq = 0.0;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t s0 = (int64_t)blockIdx.x * blockDim.x + wp * 32; s0 < nslots; s0 += stride) {
-    const int64_t s = s0 + lane;
-    const bool valid = s < nslots;
-    int i = -1;
-    double vp = 0.0, vw = 0.0;
-    if (valid) {
-      i = src[s];
-      const F wo = w[s];
-      if (MODE == 1) {
-        vw = (double)wo;
-        wsq += vw * vw;
-      } else {
-        const int j = dst[s];
-        const F y = c * wo - (a[i] + a[j]);
-        F p = y - tgz * z[s];
-        p = p > F(0) ? p : F(0);
-        const F q = c * p - (b[i] + b[j]);
-        const F r = q - y;
-        const F wn = (wo - y) + q;
-        w[s] = wn;
-        vp = (double)p;
-        vw = (double)wn;
-        res += (double)r * (double)r;
-        wsq += vw * vw;
-      }
-    }
-    // segmented suffix sums over runs of equal source (slots are sorted by source)
+  // Each warp takes KNN_UNROLL groups of 32 consecutive slots per step and issues all their loads
+  // (then all their gathers) before the first use: one group per step leaves the kernel
+  // latency-bound (measured 1.25 TB/s moved at 1.1e7 edges).
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * KNN_UNROLL;
+  for (int64_t s0 = ((int64_t)blockIdx.x * (KNN_THREADS / 32) + wp) * 32 * KNN_UNROLL; s0 < nslots; s0 += stride) {
+    int i[KNN_UNROLL], j[KNN_UNROLL];
+    F wo[KNN_UNROLL], zz[KNN_UNROLL];
 #pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const int io = __shfl_down_sync(0xffffffffu, i, off);
-      const double po = __shfl_down_sync(0xffffffffu, vp, off);
-      const double wo2 = __shfl_down_sync(0xffffffffu, vw, off);
-      if (lane + off < 32 && io == i) {
-        vp += po;
-        vw += wo2;
+    for (int u = 0; u < KNN_UNROLL; ++u) {
+      const int64_t s = s0 + u * 32 + lane;
+      const bool valid = s < nslots;
+      i[u] = valid ? src[s] : -1;
+      wo[u] = valid ? w[s] : F(0);
+      if (MODE == 0) {
+        j[u] = valid ? dst[s] : 0;
+        zz[u] = valid ? z[s] : F(0);
       }
     }
-    const int iprev = __shfl_up_sync(0xffffffffu, i, 1);
-    if (valid && (lane == 0 || iprev != i)) {
-      if (MODE == 0 && vp != 0.0) atomicAdd(sp + i, vp);
-      atomicAdd(sw + i, vw);
+    typename Vec2<F>::type abi[KNN_UNROLL], abj[KNN_UNROLL];
+    if (MODE == 0) {
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u) {
+        abi[u] = ab[i[u] < 0 ? 0 : i[u]];   // (a, b) of both ends: one gather each
+        abj[u] = ab[j[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < KNN_UNROLL; ++u) {
+      const int64_t s = s0 + u * 32 + lane;
+      const bool valid = s < nslots;
+      F vp = F(0), vw = F(0);   // segment sums in the edge dtype (<= 32 terms), float64 from the atomic on
+      if (valid) {
+        if (MODE == 1) {
+          vw = wo[u];
+          wsq += (double)vw * (double)vw;
+        } else {
+          const F y = c * wo[u] - (abi[u].x + abj[u].x);
+          F p = y - tgz * zz[u];
+          p = p > F(0) ? p : F(0);
+          const F q = c * p - (abi[u].y + abj[u].y);
+          const F r = q - y;
+          const F wn = (wo[u] - y) + q;
+          w[s] = wn;
+          vp = p;
+          vw = wn;
+          res += (double)r * (double)r;
+          wsq += (double)wn * (double)wn;
+        }
+      }
+      // segmented suffix sums over runs of equal source (slots are sorted by source)
+      const int iu = i[u];
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int io = __shfl_down_sync(0xffffffffu, iu, off);
+        const F po = __shfl_down_sync(0xffffffffu, vp, off);
+        const F wo2 = __shfl_down_sync(0xffffffffu, vw, off);
+        if (lane + off < 32 && io == iu) {
+          vp += po;
+          vw += wo2;
+        }
+      }
+      const int iprev = __shfl_up_sync(0xffffffffu, iu, 1);
+      if (valid && (lane == 0 || iprev != iu)) {
+        if (MODE == 0 && vp != F(0)) atomicAdd(sp + iu, (double)vp);
+        atomicAdd(sw + iu, (double)vw);
+      }
     }
   }
   res = warp_sum(res);
@@ -153,12 +184,156 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_slot_kernel(const int32_t *__
   }
 }
 
+// Node phase of the kNN path (single graph, single GPU): the arithmetic of node_tail.cu for K == 1
+// (smooth_learning.py:148-166) as a grid-stride kernel -- a few hundred CTAs however large n is,
+// several independent nodes in flight per thread -- because one CTA per 256 nodes (3,907 CTAs at
+// n = 1e6, each paying a fence, a barrier and a ticket) measured 123 us per launch, latency-bound.
+// Only the interleaved (a, b) pairs the slot kernel gathers are written, not a and b separately.
+constexpr int KNN_NODE_THREADS = 256;
+struct KnnNodeArgs {
+  double *d, *yb, *pb, *rb, *xch, *gprev, *resid, *node_partial;
+  void *ab;
+  int *flags;
+  int n, npad, init, maxit;
+  double gamma, four_ag, tol;
+};
+
+template <typename F>
+__global__ void __launch_bounds__(KNN_NODE_THREADS) knn_node_kernel(const KnnNodeArgs A) {
+  __shared__ int s_last;
+  __shared__ double s_blk[KNN_NODE_THREADS / 32][2];
+  if (!A.init && *reinterpret_cast<volatile int *>(A.flags + FLAG_DONE)) return;
+  const int tid = threadIdx.x;
+  double my_rb2 = 0.0, my_d2 = 0.0;
+  typename Vec2<F>::type *ab = static_cast<typename Vec2<F>::type *>(A.ab);
+  for (int64_t idx = (int64_t)blockIdx.x * KNN_NODE_THREADS + tid; idx < A.npad;
+       idx += (int64_t)gridDim.x * KNN_NODE_THREADS) {
+    const double sp = A.xch[idx], sw = A.xch[A.npad + idx];
+    A.xch[idx] = 0.0;
+    A.xch[A.npad + idx] = 0.0;
+    double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
+    if (idx < A.n) {
+      if (A.init) {
+        dn = sw;                                          // d0 = S w0            :144
+      } else {
+        const double dv = A.d[idx], ybv = A.yb[idx];
+        const double qb = A.pb[idx] + A.gamma * sp;       //                      :154
+        rbv = qb - ybv;
+        dn = (dv - ybv) + qb;                             //                      :164
+      }
+      ybn = dn + A.gamma * sw;                            //                      :148
+      pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;    //                      :151
+    }
+    my_rb2 += rbv * rbv;
+    my_d2 += dn * dn;
+    A.d[idx] = dn;
+    A.yb[idx] = ybn;
+    A.pb[idx] = pbn;
+    A.rb[idx] = rbv;
+    typename Vec2<F>::type pr;
+    pr.x = (F)(A.gamma * dn);
+    pr.y = (F)(A.gamma * pbn);
+    ab[idx] = pr;
+  }
+  my_rb2 = warp_sum(my_rb2);
+  my_d2 = warp_sum(my_d2);
+  if ((tid & 31) == 0) {
+    s_blk[tid >> 5][0] = my_rb2;
+    s_blk[tid >> 5][1] = my_d2;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double r2 = 0.0, d2 = 0.0;
+    for (int q = 0; q < KNN_NODE_THREADS / 32; ++q) {
+      r2 += s_blk[q][0];
+      d2 += s_blk[q][1];
+    }
+    A.node_partial[2 * blockIdx.x] = r2;
+    A.node_partial[2 * blockIdx.x + 1] = d2;
+    __threadfence();
+    const int ticket = atomicAdd(A.flags + FLAG_NODE_TICKET, 1);
+    s_last = (ticket == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // ---- last CTA: fixed-order sums, stop rule (smooth_learning.py:156-166) -------------------------
+  double r2 = 0.0, d2 = 0.0;
+  for (int i = tid; i < (int)gridDim.x; i += KNN_NODE_THREADS) {
+    r2 += __ldcg(A.node_partial + 2 * i);
+    d2 += __ldcg(A.node_partial + 2 * i + 1);
+  }
+  r2 = warp_sum(r2);
+  d2 = warp_sum(d2);
+  __syncthreads();
+  if ((tid & 31) == 0) {
+    s_blk[tid >> 5][0] = r2;
+    s_blk[tid >> 5][1] = d2;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  r2 = d2 = 0.0;
+  for (int q = 0; q < KNN_NODE_THREADS / 32; ++q) {
+    r2 += s_blk[q][0];
+    d2 += s_blk[q][1];
+  }
+  double *g = A.xch + 2 * (int64_t)A.npad;   // [ ||q - y||^2 , ||w'||^2 ] from the slot kernel
+  const double g_r = __ldcg(g), g_w = __ldcg(g + 1);
+  g[0] = 0.0;
+  g[1] = 0.0;
+  A.flags[FLAG_NODE_TICKET] = 0;
+  if (A.init) {
+    A.flags[FLAG_IT] = 0;
+    A.flags[FLAG_CONVERGED] = 0;
+    A.flags[FLAG_DONE] = (A.maxit <= 0);
+    A.resid[0] = CUDART_INF;
+    A.resid[1] = CUDART_INF;
+  } else {
+    const int it = A.flags[FLAG_IT];
+    bool conv = false;
+    if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+      const double rp = sqrt(g_r) / sqrt(A.gprev[0]);
+      const double rd = sqrt(r2) / sqrt(A.gprev[1]);
+      A.resid[0] = rp;
+      A.resid[1] = rd;
+      conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
+    }
+    A.flags[FLAG_IT] = it + 1;
+    if (conv) A.flags[FLAG_CONVERGED] = 1;
+    if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
+  }
+  A.gprev[0] = g_w;   // denominators of the next check: the iterate before the update (:157-159)
+  A.gprev[1] = d2;
+}
+
+template <typename F> static int launch_knn_node(gl_solver *s, bool init, cudaStream_t st) {
+  KnnNodeArgs A;
+  A.d = s->d; A.yb = s->yb; A.pb = s->pb; A.rb = s->rb;
+  A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.node_partial = s->node_partial;
+  A.ab = s->ab;
+  A.flags = s->flags;
+  A.n = s->n; A.npad = s->npad; A.init = init ? 1 : 0; A.maxit = s->maxit;
+  A.gamma = s->gamma;
+  A.four_ag = 4.0 * s->alpha * s->gamma;
+  A.tol = s->tol;
+  int grid = (s->npad + KNN_NODE_THREADS - 1) / KNN_NODE_THREADS;
+  if (grid > 148 * 4) grid = 148 * 4;
+  knn_node_kernel<F><<<grid, KNN_NODE_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
 template <typename F>
 static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t nnz, int n, double alpha,
                        double beta, int maxit, double tol, double step_size, double edge_tol, F *w, int *n_iter,
                        double *rel_primal, double *rel_dual, cudaStream_t st) {
   gl_solver *s = nullptr;
   GL_TRY(gl_solver_create(&s, n, 1, sizeof(F) == 4 ? GL_F32 : GL_F64, 0, 0));
+  if (cudaMalloc(&s->ab, 2 * sizeof(F) * (size_t)s->npad) != cudaSuccess) {
+    gl_solver_destroy(s);
+    return fail(GL_E_ALLOC, "kNN solve: out of device memory");
+  }
+  cudaMemsetAsync(s->ab, 0, 2 * sizeof(F) * (size_t)s->npad, st);
   int rc = GL_OK;
   int *cnt = nullptr;
   int *h_flags = nullptr;
@@ -229,12 +404,12 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
   KNN_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
   KNN_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
   if (nnz > 0) {
-    knn_slot_kernel<F, 1><<<sgrid, KNN_THREADS, 0, st>>>(src, dst, zs, ws, nslots, (const F *)s->a, (const F *)s->b,
+    knn_slot_kernel<F, 1><<<sgrid, KNN_THREADS, 0, st>>>(src, dst, zs, ws, nslots, (const typename Vec2<F>::type *)s->ab,
                                                         sp, sw, gsum, s->flags, c, tgz);
     g_launches.fetch_add(1);
     KNN_CUDA(cudaGetLastError());
   }
-  rc = launch_node_tail(s, true, st);
+  rc = launch_knn_node<F>(s, true, st);
   if (rc != GL_OK) return done(rc);
   s->begun = true;
 
@@ -252,9 +427,9 @@ static int knn_solve_t(const int32_t *ei, const int32_t *ej, const F *z, int64_t
   if (ce == cudaSuccess) {
     for (int i = 0; i < chunk && rc == GL_OK; ++i) {
       if (nnz > 0)
-        knn_slot_kernel<F, 0><<<sgrid, KNN_THREADS, 0, cs>>>(src, dst, zs, ws, nslots, (const F *)s->a,
-                                                            (const F *)s->b, sp, sw, gsum, s->flags, c, tgz);
-      rc = launch_node_tail(s, false, cs);
+        knn_slot_kernel<F, 0><<<sgrid, KNN_THREADS, 0, cs>>>(src, dst, zs, ws, nslots, (const typename Vec2<F>::type *)s->ab,
+                                                            sp, sw, gsum, s->flags, c, tgz);
+      rc = launch_knn_node<F>(s, false, cs);
     }
     ce = cudaStreamEndCapture(cs, &graph);
   }

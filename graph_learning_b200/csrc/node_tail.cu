@@ -22,6 +22,7 @@ constexpr int NODE_THREADS = 256;
 struct NodeArgs {
   double *d, *yb, *pb, *rb;
   void *a, *b;
+  void *ab;        // nullable: interleaved (a, b) pairs for the kNN slot kernel (one gather per far end)
   double *xch;     // [sp | sw | G_r | G_w]
   double *gprev;   // [Gram(W) | Gram(D)] of the previous iterate
   double *resid;   // rel_primal, rel_dual
@@ -236,9 +237,11 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     if (A.f32) {
       static_cast<float *>(A.a)[idx] = (float)(A.gamma * dn);
       static_cast<float *>(A.b)[idx] = (float)(A.gamma * pbn);
+      if (A.ab) static_cast<float2 *>(A.ab)[idx] = make_float2((float)(A.gamma * dn), (float)(A.gamma * pbn));
     } else {
       static_cast<double *>(A.a)[idx] = A.gamma * dn;
       static_cast<double *>(A.b)[idx] = A.gamma * pbn;
+      if (A.ab) static_cast<double2 *>(A.ab)[idx] = make_double2(A.gamma * dn, A.gamma * pbn);
     }
   }
   if (A.K == 1) {  // single graph: per-CTA partial sums, combined in fixed order by the last CTA
@@ -361,7 +364,7 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
   NodeArgs A;
   A.d = s->d; A.yb = s->yb; A.pb = s->pb; A.rb = s->rb;
-  A.a = s->a; A.b = s->b;
+  A.a = s->a; A.b = s->b; A.ab = s->ab;
   A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.eig = s->eig_scratch;
   A.node_partial = s->node_partial;
   A.hdr = reinterpret_cast<int *>(s->comm);

@@ -39,6 +39,7 @@ struct gl_solver {
   // node state
   double *d = nullptr, *yb = nullptr, *pb = nullptr, *rb = nullptr;  // [K][npad]
   void *a = nullptr, *b = nullptr;  // [K][npad] edge dtype: gamma*d, gamma*pb
+  void *ab = nullptr;               // kNN path only: [npad] interleaved (a, b) pairs
   // exchange buffer (float64): [sp K*npad | sw K*npad | G_r K*K | G_w K*K]
   double *comm = nullptr;  // the comm block; xch = comm + COMM_HDR
   double *xch = nullptr;

@@ -1,0 +1,50 @@
+"""Config 5 on one GPU: kNN search, theta, and the sparse-support solve at n nodes (default 1e6),
+points uniform in the unit cube (BASELINE gives no m for config 5: m = 3 coordinates is the choice).
+Prints one JSON line.  Development / measurement aid."""
+import json
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from graph_learning_b200 import _native as nat  # noqa: E402
+from graph_learning_b200.knn import gsp_learn_graph_log_degrees_knn, knn_graph, theta_from_knn  # noqa: E402
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+    k = int(sys.argv[2]) if len(sys.argv) > 2 else 20
+    iters = int(sys.argv[3]) if len(sys.argv) > 3 else 200
+    torch.cuda.set_device(0)
+    x = torch.rand((3, n), generator=torch.Generator(device="cuda").manual_seed(0), device="cuda")
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ei, ej, d2, (idx, d2l) = knn_graph(x, k)
+    torch.cuda.synchronize()
+    t_build = time.perf_counter() - t0
+    theta = theta_from_knn(d2l, 10)
+    z = d2 * theta
+    nnz = z.numel()
+    gsp_learn_graph_log_degrees_knn(ei, ej, z, n, maxit=20, tol=0.0)  # warm-up
+    torch.cuda.synchronize()
+    l0 = nat.launch_count()
+    t0 = time.perf_counter()
+    w, info = gsp_learn_graph_log_degrees_knn(ei, ej, z, n, maxit=iters, tol=0.0, return_info=True)
+    torch.cuda.synchronize()
+    t_solve = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    gsp_learn_graph_log_degrees_knn(ei, ej, z, n, maxit=0, tol=0.0)
+    torch.cuda.synchronize()
+    t_setup = time.perf_counter() - t0
+    per_it = (t_solve - t_setup) / iters
+    print(json.dumps({"n": n, "k": k, "edges": nnz, "knn_build_s": t_build, "theta": theta, "iters": info.n_iter,
+                      "solve_s": t_solve, "setup_s": t_setup, "ms_per_iteration": per_it * 1e3,
+                      "edge_iters_per_s": nnz / per_it, "algorithmic_GBps_20B_per_edge": 20 * nnz / per_it / 1e9,
+                      "moved_GBps_40B_per_edge": 40 * nnz / per_it / 1e9, "kept_edges": int((w > 0).sum()),
+                      "launches": nat.launch_count() - l0}))
+
+
+if __name__ == "__main__":
+    main()
