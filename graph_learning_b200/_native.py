@@ -74,6 +74,19 @@ SIGNATURES = {
                                   c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p]),
     "gl_logmodel_solve_host": (c_int, [c_void_p, _pd, c_int, c_int, c_int, c_double, c_double, c_void_p, c_int,
                                        c_double, c_double, c_double, c_void_p, _pi, _pd, _pd]),
+    "gl_knn_max_degree": (c_int, [c_void_p, c_void_p, c_int64, c_int, _pi, c_void_p]),
+    "gl_knn_create": (c_int, [POINTER(c_void_p), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+                              c_int, c_int64, c_void_p]),
+    "gl_knn_destroy": (c_int, [c_void_p]),
+    "gl_knn_local_slots": (c_int64, [c_void_p]),
+    "gl_knn_begin": (c_int, [c_void_p, c_double, c_double, c_double, c_int, c_double, c_int, c_void_p]),
+    "gl_knn_edge_step": (c_int, [c_void_p, c_void_p]),
+    "gl_knn_node_step": (c_int, [c_void_p, c_void_p]),
+    "gl_knn_decide": (c_int, [c_void_p, c_int, c_void_p]),
+    "gl_knn_ab_ptr": (c_void_p, [c_void_p, POINTER(c_int64)]),
+    "gl_knn_scalars_ptr": (c_void_p, [c_void_p]),
+    "gl_knn_status": (c_int, [c_void_p, _pi, _pd, _pd, _pi, c_void_p]),
+    "gl_knn_store": (c_int, [c_void_p, c_void_p, c_double, c_void_p]),
     "gl_knn_build": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "gl_knn_logmodel_solve": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_double, c_double,
                                       c_int, c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p]),

@@ -1,0 +1,360 @@
+// knn_kernels.cuh -- kernels of the kNN-support LogModel path (K6), shared by the one-shot solve
+// (knn.cu) and the sharded, stepwise solver (knn_sharded.cu).  See knn.cu for the layout notes.
+#pragma once
+#include <cub/device/device_radix_sort.cuh>
+
+#include <math_constants.h>
+
+#include "solver.cuh"
+
+namespace gl {
+
+constexpr int KNN_THREADS = 256;
+constexpr int KNN_UNROLL = 4;
+template <typename F> struct Vec2;
+template <> struct Vec2<float> { using type = float2; };
+template <> struct Vec2<double> { using type = double2; };
+
+static __global__ void knn_degree_count_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, int *cnt) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
+    atomicAdd(cnt + ei[e], 1);
+    atomicAdd(cnt + ej[e], 1);
+  }
+}
+static __global__ void knn_max_kernel(const int *cnt, int n, int *out) {
+  __shared__ int s[256];
+  int m = 0;
+  for (int i = threadIdx.x; i < n; i += 256) m = max(m, cnt[i]);
+  s[threadIdx.x] = m;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s[threadIdx.x] = max(s[threadIdx.x], s[threadIdx.x + o]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = s[0];
+}
+
+// undirected list -> unsorted directed slots (key = source node, value = undirected edge id)
+// Slots whose source lies outside [row_begin, row_end) (another shard's rows) get the sentinel key n,
+// sort to the end and are dropped; *count receives the number of local slots.
+static __global__ void knn_expand_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, int32_t *key, int32_t *val,
+                                  int row_begin, int row_end, int n, unsigned long long *count) {
+  unsigned long long mine = 0;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
+    const int i = ei[e], j = ej[e];
+    const bool oi = i >= row_begin && i < row_end, oj = j >= row_begin && j < row_end;
+    key[2 * e] = oi ? i : n;
+    val[2 * e] = (int32_t)e;
+    key[2 * e + 1] = oj ? j : n;
+    val[2 * e + 1] = (int32_t)e;
+    mine += (oi ? 1 : 0) + (oj ? 1 : 0);
+  }
+  mine = warp_sum(mine);
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(count, mine);
+}
+// sorted slots: fill in the far end and this slot's copies of z and w
+template <typename F>
+__global__ void knn_fill_kernel(const int32_t *ei, const int32_t *ej, const F *z, const F *w, int64_t nslots,
+                                const int32_t *src, const int32_t *eid, int32_t *dst, F *zs, F *ws) {
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t e = eid[s], i = ei[e], j = ej[e];
+    dst[s] = src[s] == i ? j : i;
+    zs[s] = z[e];
+    ws[s] = w[e];
+  }
+}
+// result back in the caller's edge order, from the slot whose source is the edge's first end; the
+// edge_tol threshold of smooth_learning.py:169 applied on the way
+template <typename F>
+__global__ void knn_writeback_kernel(const int32_t *ei, const int32_t *src, const int32_t *eid, const F *ws,
+                                     int64_t nslots, double edge_tol, F *w) {
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t e = eid[s];
+    if (src[s] == ei[e]) {
+      const F v = ws[s];
+      w[e] = (double)v < edge_tol ? F(0) : v;
+    }
+  }
+}
+
+// MODE 0: iteration.  MODE 1: initial degrees S w0 and ||w0||^2.  One thread per directed slot,
+// warps own 32 consecutive slots; gsum receives HALF the slot sums (every edge appears twice).
+template <typename F, int MODE>
+__global__ void __launch_bounds__(KNN_THREADS) knn_slot_kernel(const int32_t *__restrict__ src,
+                                                               const int32_t *__restrict__ dst,
+                                                               const F *__restrict__ z, F *__restrict__ w,
+                                                               int64_t nslots,
+                                                               const typename Vec2<F>::type *__restrict__ ab,
+                                                               double *sp, double *sw,
+                                                               double *gsum, const int *flags, F c, F tgz) {
+  if (MODE == 0 && *reinterpret_cast<const volatile int *>(flags + FLAG_DONE)) return;
+  __shared__ double s_red[KNN_THREADS / 32][2];
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  double res = 0.0, wsq = 0.0;
+  // Each warp takes KNN_UNROLL groups of 32 consecutive slots per step and issues all their loads
+  // (then all their gathers) before the first use: one group per step leaves the kernel
+  // latency-bound (measured 1.25 TB/s moved at 1.1e7 edges).
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * KNN_UNROLL;
+  for (int64_t s0 = ((int64_t)blockIdx.x * (KNN_THREADS / 32) + wp) * 32 * KNN_UNROLL; s0 < nslots; s0 += stride) {
+    int i[KNN_UNROLL], j[KNN_UNROLL];
+    F wo[KNN_UNROLL], zz[KNN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < KNN_UNROLL; ++u) {
+      const int64_t s = s0 + u * 32 + lane;
+      const bool valid = s < nslots;
+      i[u] = valid ? src[s] : -1;
+      wo[u] = valid ? w[s] : F(0);
+      if (MODE == 0) {
+        j[u] = valid ? dst[s] : 0;
+        zz[u] = valid ? z[s] : F(0);
+      }
+    }
+    typename Vec2<F>::type abi[KNN_UNROLL], abj[KNN_UNROLL];
+    if (MODE == 0) {
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u) {
+        abi[u] = ab[i[u] < 0 ? 0 : i[u]];   // (a, b) of both ends: one gather each
+        abj[u] = ab[j[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < KNN_UNROLL; ++u) {
+      const int64_t s = s0 + u * 32 + lane;
+      const bool valid = s < nslots;
+      F vp = F(0), vw = F(0);   // segment sums in the edge dtype (<= 32 terms), float64 from the atomic on
+      if (valid) {
+        if (MODE == 1) {
+          vw = wo[u];
+          wsq += (double)vw * (double)vw;
+        } else {
+          const F y = c * wo[u] - (abi[u].x + abj[u].x);
+          F p = y - tgz * zz[u];
+          p = p > F(0) ? p : F(0);
+          const F q = c * p - (abi[u].y + abj[u].y);
+          const F r = q - y;
+          const F wn = (wo[u] - y) + q;
+          w[s] = wn;
+          vp = p;
+          vw = wn;
+          res += (double)r * (double)r;
+          wsq += (double)wn * (double)wn;
+        }
+      }
+      // segmented suffix sums over runs of equal source (slots are sorted by source)
+      const int iu = i[u];
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int io = __shfl_down_sync(0xffffffffu, iu, off);
+        const F po = __shfl_down_sync(0xffffffffu, vp, off);
+        const F wo2 = __shfl_down_sync(0xffffffffu, vw, off);
+        if (lane + off < 32 && io == iu) {
+          vp += po;
+          vw += wo2;
+        }
+      }
+      const int iprev = __shfl_up_sync(0xffffffffu, iu, 1);
+      if (valid && (lane == 0 || iprev != iu)) {
+        if (MODE == 0 && vp != F(0)) atomicAdd(sp + iu, (double)vp);
+        atomicAdd(sw + iu, (double)vw);
+      }
+    }
+  }
+  res = warp_sum(res);
+  wsq = warp_sum(wsq);
+  if (lane == 0) {
+    s_red[wp][0] = res;
+    s_red[wp][1] = wsq;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r2 = 0.0, w2 = 0.0;
+    for (int q = 0; q < KNN_THREADS / 32; ++q) {
+      r2 += s_red[q][0];
+      w2 += s_red[q][1];
+    }
+    if (MODE == 0) atomicAdd(gsum, 0.5 * r2);
+    atomicAdd(gsum + 1, 0.5 * w2);
+  }
+}
+
+// Node phase of the kNN path (single graph, single GPU): the arithmetic of node_tail.cu for K == 1
+// (smooth_learning.py:148-166) as a grid-stride kernel -- a few hundred CTAs however large n is,
+// several independent nodes in flight per thread -- because one CTA per 256 nodes (3,907 CTAs at
+// n = 1e6, each paying a fence, a barrier and a ticket) measured 123 us per launch, latency-bound.
+// Only the interleaved (a, b) pairs the slot kernel gathers are written, not a and b separately.
+constexpr int KNN_NODE_THREADS = 256;
+struct KnnNodeArgs {
+  double *d, *yb, *pb, *rb, *xch, *gprev, *resid, *node_partial;
+  void *ab;
+  int *flags;
+  int n, npad, init, maxit;
+  int row_begin, row_end;   // nodes this rank updates ([0, npad) on a single GPU)
+  int fused;                // 1: the last CTA also applies the stop rule (single GPU)
+  double *scal;             // !fused: [||q-y||^2, ||w'||^2, ||qb-yb||^2, ||d'||^2] partials of this rank
+  double gamma, four_ag, tol;
+};
+
+template <typename F>
+__global__ void __launch_bounds__(KNN_NODE_THREADS) knn_node_kernel(const KnnNodeArgs A) {
+  __shared__ int s_last;
+  __shared__ double s_blk[KNN_NODE_THREADS / 32][2];
+  if (!A.init && *reinterpret_cast<volatile int *>(A.flags + FLAG_DONE)) return;
+  const int tid = threadIdx.x;
+  double my_rb2 = 0.0, my_d2 = 0.0;
+  typename Vec2<F>::type *ab = static_cast<typename Vec2<F>::type *>(A.ab);
+  for (int64_t idx = A.row_begin + (int64_t)blockIdx.x * KNN_NODE_THREADS + tid; idx < A.row_end;
+       idx += (int64_t)gridDim.x * KNN_NODE_THREADS) {
+    const double sp = A.xch[idx], sw = A.xch[A.npad + idx];
+    A.xch[idx] = 0.0;
+    A.xch[A.npad + idx] = 0.0;
+    double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
+    if (idx < A.n) {
+      if (A.init) {
+        dn = sw;                                          // d0 = S w0            :144
+      } else {
+        const double dv = A.d[idx], ybv = A.yb[idx];
+        const double qb = A.pb[idx] + A.gamma * sp;       //                      :154
+        rbv = qb - ybv;
+        dn = (dv - ybv) + qb;                             //                      :164
+      }
+      ybn = dn + A.gamma * sw;                            //                      :148
+      pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;    //                      :151
+    }
+    my_rb2 += rbv * rbv;
+    my_d2 += dn * dn;
+    A.d[idx] = dn;
+    A.yb[idx] = ybn;
+    A.pb[idx] = pbn;
+    A.rb[idx] = rbv;
+    typename Vec2<F>::type pr;
+    pr.x = (F)(A.gamma * dn);
+    pr.y = (F)(A.gamma * pbn);
+    ab[idx] = pr;
+  }
+  my_rb2 = warp_sum(my_rb2);
+  my_d2 = warp_sum(my_d2);
+  if ((tid & 31) == 0) {
+    s_blk[tid >> 5][0] = my_rb2;
+    s_blk[tid >> 5][1] = my_d2;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double r2 = 0.0, d2 = 0.0;
+    for (int q = 0; q < KNN_NODE_THREADS / 32; ++q) {
+      r2 += s_blk[q][0];
+      d2 += s_blk[q][1];
+    }
+    A.node_partial[2 * blockIdx.x] = r2;
+    A.node_partial[2 * blockIdx.x + 1] = d2;
+    __threadfence();
+    const int ticket = atomicAdd(A.flags + FLAG_NODE_TICKET, 1);
+    s_last = (ticket == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // ---- last CTA: fixed-order sums, stop rule (smooth_learning.py:156-166) -------------------------
+  double r2 = 0.0, d2 = 0.0;
+  for (int i = tid; i < (int)gridDim.x; i += KNN_NODE_THREADS) {
+    r2 += __ldcg(A.node_partial + 2 * i);
+    d2 += __ldcg(A.node_partial + 2 * i + 1);
+  }
+  r2 = warp_sum(r2);
+  d2 = warp_sum(d2);
+  __syncthreads();
+  if ((tid & 31) == 0) {
+    s_blk[tid >> 5][0] = r2;
+    s_blk[tid >> 5][1] = d2;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  r2 = d2 = 0.0;
+  for (int q = 0; q < KNN_NODE_THREADS / 32; ++q) {
+    r2 += s_blk[q][0];
+    d2 += s_blk[q][1];
+  }
+  double *g = A.xch + 2 * (int64_t)A.npad;   // [ ||q - y||^2 , ||w'||^2 ] from the slot kernel
+  const double g_r = __ldcg(g), g_w = __ldcg(g + 1);
+  g[0] = 0.0;
+  g[1] = 0.0;
+  A.flags[FLAG_NODE_TICKET] = 0;
+  if (!A.fused) {  // sharded: hand the partial sums to the exchange; knn_decide_kernel applies the rule
+    A.scal[0] = g_r;
+    A.scal[1] = g_w;
+    A.scal[2] = r2;
+    A.scal[3] = d2;
+    return;
+  }
+  if (A.init) {
+    A.flags[FLAG_IT] = 0;
+    A.flags[FLAG_CONVERGED] = 0;
+    A.flags[FLAG_DONE] = (A.maxit <= 0);
+    A.resid[0] = CUDART_INF;
+    A.resid[1] = CUDART_INF;
+  } else {
+    const int it = A.flags[FLAG_IT];
+    bool conv = false;
+    if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+      const double rp = sqrt(g_r) / sqrt(A.gprev[0]);
+      const double rd = sqrt(r2) / sqrt(A.gprev[1]);
+      A.resid[0] = rp;
+      A.resid[1] = rd;
+      conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
+    }
+    A.flags[FLAG_IT] = it + 1;
+    if (conv) A.flags[FLAG_CONVERGED] = 1;
+    if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
+  }
+  A.gprev[0] = g_w;   // denominators of the next check: the iterate before the update (:157-159)
+  A.gprev[1] = d2;
+}
+
+// Stop rule from the rank-summed scalars (identical inputs, identical decision on every rank).
+static __global__ void knn_decide_kernel(const double *scal, double *gprev, double *resid, int *flags, int init, int maxit,
+                                  double tol) {
+  if (!init && flags[FLAG_DONE]) return;
+  const double g_r = scal[0], g_w = scal[1], r2 = scal[2], d2 = scal[3];
+  if (init) {
+    flags[FLAG_IT] = 0;
+    flags[FLAG_CONVERGED] = 0;
+    flags[FLAG_DONE] = (maxit <= 0);
+    resid[0] = CUDART_INF;
+    resid[1] = CUDART_INF;
+  } else {
+    const int it = flags[FLAG_IT];
+    bool conv = false;
+    if (it >= 1) {
+      const double rp = sqrt(g_r) / sqrt(gprev[0]);
+      const double rd = sqrt(r2) / sqrt(gprev[1]);
+      resid[0] = rp;
+      resid[1] = rd;
+      conv = (rp < tol) && (rd < tol);
+    }
+    flags[FLAG_IT] = it + 1;
+    if (conv) flags[FLAG_CONVERGED] = 1;
+    if (conv || it + 1 >= maxit) flags[FLAG_DONE] = 1;
+  }
+  gprev[0] = g_w;
+  gprev[1] = d2;
+}
+
+template <typename F> static int launch_knn_node(gl_solver *s, bool init, cudaStream_t st) {
+  KnnNodeArgs A;
+  A.d = s->d; A.yb = s->yb; A.pb = s->pb; A.rb = s->rb;
+  A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.node_partial = s->node_partial;
+  A.ab = s->ab;
+  A.flags = s->flags;
+  A.n = s->n; A.npad = s->npad; A.init = init ? 1 : 0; A.maxit = s->maxit;
+  A.row_begin = 0; A.row_end = s->npad; A.fused = 1; A.scal = nullptr;
+  A.gamma = s->gamma;
+  A.four_ag = 4.0 * s->alpha * s->gamma;
+  A.tol = s->tol;
+  int grid = (s->npad + KNN_NODE_THREADS - 1) / KNN_NODE_THREADS;
+  if (grid > 148 * 4) grid = 148 * 4;
+  knn_node_kernel<F><<<grid, KNN_NODE_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+
+}  // namespace gl

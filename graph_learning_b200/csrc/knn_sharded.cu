@@ -1,0 +1,276 @@
+// knn_sharded.cu -- stepwise kNN-support solver for row-sharded multi-GPU runs (config 5, SURVEY 8(e):
+// "kNN variant: shard the edge list by contiguous ranges of the row index").
+//
+// Every rank owns the nodes [row_begin, row_end) and ALL directed slots whose source is one of them
+// (knn_kernels.cuh), so the degree sums of its nodes are complete locally: nothing is reduced across
+// ranks except four residual scalars.  What a rank lacks is the (a, b) pair of far-end nodes it does
+// not own; after its node step every rank's slice of the interleaved `ab` array is all-gathered
+// (8 B x n in fp32; by the caller: NCCL in-place all-gather, graph_learning_b200/sharded.py).
+// Per iteration:  edge_step -> node_step -> [all-gather ab | all-reduce 4 scalars] -> decide.
+// The node state (d, yb, pb) of foreign rows is never touched.
+#include "knn_kernels.cuh"
+
+struct gl_knn_solver {
+  gl_solver *s = nullptr;     // node-state workspace (no tiles)
+  int dtype = GL_F32;
+  int64_t nnz = 0, nslots = 0;
+  int row_begin = 0, row_end = 0;
+  int64_t ab_len = 0;          // entries of the ab array (>= npad; world x rows per rank)
+  const int32_t *ei = nullptr; // caller's edge list (kept alive by the caller until destroy)
+  int32_t *src = nullptr, *dst = nullptr, *eid = nullptr;
+  void *zs = nullptr, *ws = nullptr;
+  double *scal = nullptr;      // [4] partial sums for the exchange
+};
+
+namespace gl {
+
+template <typename F>
+static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, const F *z, const F *w0,
+                        cudaStream_t st) {
+  const int64_t nnz = k->nnz, all = 2 * nnz;
+  const int n = k->s->n;
+  if (nnz == 0) return GL_OK;
+  int32_t *key_in = nullptr, *val_in = nullptr, *src_all = nullptr, *eid_all = nullptr;
+  unsigned long long *count = nullptr;
+  void *tmp = nullptr;
+  F *w_zero = nullptr;
+  int rc = GL_OK;
+  auto cleanup = [&]() {
+    for (void *q : {(void *)key_in, (void *)val_in, (void *)src_all, (void *)eid_all, (void *)count, tmp, (void *)w_zero})
+      if (q) cudaFree(q);
+  };
+#define KS_CUDA(expr)                                                                                      \
+  do {                                                                                                     \
+    cudaError_t _e = (expr);                                                                               \
+    if (_e != cudaSuccess) {                                                                               \
+      cleanup();                                                                                           \
+      return fail(GL_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    }                                                                                                      \
+  } while (0)
+  const size_t ib = sizeof(int32_t) * (size_t)all;
+  KS_CUDA(cudaMalloc((void **)&key_in, ib));
+  KS_CUDA(cudaMalloc((void **)&val_in, ib));
+  KS_CUDA(cudaMalloc((void **)&src_all, ib));
+  KS_CUDA(cudaMalloc((void **)&eid_all, ib));
+  KS_CUDA(cudaMalloc((void **)&count, sizeof(unsigned long long)));
+  KS_CUDA(cudaMemsetAsync(count, 0, sizeof(unsigned long long), st));
+  const int grid = (int)std::min<int64_t>((nnz + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+  knn_expand_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, key_in, val_in, k->row_begin, k->row_end, n, count);
+  g_launches.fetch_add(1);
+  int bits = 1;
+  while (bits < 31 && ((int64_t)1 << bits) <= (int64_t)n) ++bits;   // the sentinel key n must fit
+  size_t tmp_bytes = 0;
+  KS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, key_in, src_all, val_in, eid_all, (int)all, 0, bits, st));
+  KS_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
+  KS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, key_in, src_all, val_in, eid_all, (int)all, 0, bits, st));
+  unsigned long long h_count = 0;
+  KS_CUDA(cudaMemcpyAsync(&h_count, count, sizeof(h_count), cudaMemcpyDeviceToHost, st));
+  KS_CUDA(cudaStreamSynchronize(st));
+  k->nslots = (int64_t)h_count;
+  if (k->nslots > 0) {
+    const size_t lb = sizeof(int32_t) * (size_t)k->nslots, fb = sizeof(F) * (size_t)k->nslots;
+    KS_CUDA(cudaMalloc((void **)&k->src, lb));
+    KS_CUDA(cudaMalloc((void **)&k->eid, lb));
+    KS_CUDA(cudaMalloc((void **)&k->dst, lb));
+    KS_CUDA(cudaMalloc(&k->zs, fb));
+    KS_CUDA(cudaMalloc(&k->ws, fb));
+    KS_CUDA(cudaMemcpyAsync(k->src, src_all, lb, cudaMemcpyDeviceToDevice, st));   // local slots sort first
+    KS_CUDA(cudaMemcpyAsync(k->eid, eid_all, lb, cudaMemcpyDeviceToDevice, st));
+    const F *w_init = w0;
+    if (!w_init) {
+      KS_CUDA(cudaMalloc((void **)&w_zero, sizeof(F) * (size_t)nnz));
+      KS_CUDA(cudaMemsetAsync(w_zero, 0, sizeof(F) * (size_t)nnz, st));
+      w_init = w_zero;
+    }
+    const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+    knn_fill_kernel<F><<<sgrid, KNN_THREADS, 0, st>>>(ei, ej, z, w_init, k->nslots, k->src, k->eid, k->dst,
+                                                      (F *)k->zs, (F *)k->ws);
+    g_launches.fetch_add(1);
+    KS_CUDA(cudaGetLastError());
+  }
+  KS_CUDA(cudaStreamSynchronize(st));
+#undef KS_CUDA
+  cleanup();
+  return rc;
+}
+
+template <typename F> static int knn_slot_launch(gl_knn_solver *k, bool init, cudaStream_t st) {
+  gl_solver *s = k->s;
+  if (k->nslots == 0) return GL_OK;
+  double *sp = s->xch, *sw = s->xch + s->npad, *gsum = s->xch + 2 * (int64_t)s->npad;
+  const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS * KNN_UNROLL - 1) / (KNN_THREADS * KNN_UNROLL), 148 * 8);
+  const F c = (F)s->c, tgz = (F)(2.0 * s->gamma);
+  using V = typename Vec2<F>::type;
+  if (init)
+    knn_slot_kernel<F, 1><<<sgrid, KNN_THREADS, 0, st>>>(k->src, k->dst, (const F *)k->zs, (F *)k->ws, k->nslots,
+                                                        (const V *)s->ab, sp, sw, gsum, s->flags, c, tgz);
+  else
+    knn_slot_kernel<F, 0><<<sgrid, KNN_THREADS, 0, st>>>(k->src, k->dst, (const F *)k->zs, (F *)k->ws, k->nslots,
+                                                        (const V *)s->ab, sp, sw, gsum, s->flags, c, tgz);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+template <typename F> static int knn_node_launch(gl_knn_solver *k, bool init, cudaStream_t st) {
+  gl_solver *s = k->s;
+  KnnNodeArgs A;
+  A.d = s->d; A.yb = s->yb; A.pb = s->pb; A.rb = s->rb;
+  A.xch = s->xch; A.gprev = s->gprev; A.resid = s->resid; A.node_partial = s->node_partial;
+  A.ab = s->ab;
+  A.flags = s->flags;
+  A.n = s->n; A.npad = s->npad; A.init = init ? 1 : 0; A.maxit = s->maxit;
+  A.row_begin = k->row_begin; A.row_end = k->row_end; A.fused = 0; A.scal = k->scal;
+  A.gamma = s->gamma;
+  A.four_ag = 4.0 * s->alpha * s->gamma;
+  A.tol = s->tol;
+  const int rows = k->row_end - k->row_begin;
+  int grid = (rows + KNN_NODE_THREADS - 1) / KNN_NODE_THREADS;
+  grid = std::max(1, std::min(grid, 148 * 4));
+  knn_node_kernel<F><<<grid, KNN_NODE_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+}  // namespace gl
+using namespace gl;
+
+extern "C" int gl_knn_max_degree(const int32_t *ei, const int32_t *ej, int64_t nnz, int n, int *dmax_host,
+                                 void *stream) {
+  if (n < 2 || nnz < 0 || !dmax_host) return fail(GL_E_ARG, "bad arguments");
+  *dmax_host = 0;
+  if (nnz == 0) return GL_OK;
+  cudaStream_t st = as_stream(stream);
+  int *cnt = nullptr;
+  GL_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * ((size_t)n + 1)));
+  cudaMemsetAsync(cnt, 0, sizeof(int) * ((size_t)n + 1), st);
+  const int grid = (int)std::min<int64_t>((nnz + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+  knn_degree_count_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, cnt);
+  knn_max_kernel<<<1, 256, 0, st>>>(cnt, n, cnt + n);
+  g_launches.fetch_add(2);
+  cudaError_t e = cudaMemcpyAsync(dmax_host, cnt + n, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(cnt);
+  if (e != cudaSuccess) return fail(GL_E_CUDA, "gl_knn_max_degree: %s", cudaGetErrorString(e));
+  return GL_OK;
+}
+
+extern "C" int gl_knn_create(gl_knn_solver **out, const int32_t *ei, const int32_t *ej, const void *z, const void *w0,
+                             int64_t nnz, int n, int dtype, int row_begin, int row_end, int64_t ab_len, void *stream) {
+  if (!out) return fail(GL_E_ARG, "null output");
+  *out = nullptr;
+  if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
+  if (nnz < 0 || 2 * nnz >= ((int64_t)1 << 31)) return fail(GL_E_SHAPE, "bad edge count %lld", (long long)nnz);
+  if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
+  if (row_begin < 0 || row_end < row_begin) return fail(GL_E_ARG, "bad row range [%d,%d)", row_begin, row_end);
+  gl_knn_solver *k = new gl_knn_solver();
+  int rc = gl_solver_create(&k->s, n, 1, dtype, 0, 0);
+  if (rc != GL_OK) {
+    delete k;
+    return rc;
+  }
+  k->dtype = dtype;
+  k->nnz = nnz;
+  k->ei = ei;
+  k->row_begin = row_begin;
+  k->row_end = std::min(row_end, k->s->npad);
+  k->ab_len = std::max<int64_t>(ab_len, k->s->npad);
+  const size_t esz = dtype == GL_F32 ? 4 : 8;
+  cudaStream_t st = as_stream(stream);
+  cudaError_t e = cudaMalloc(&k->s->ab, 2 * esz * (size_t)k->ab_len);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->s->ab, 0, 2 * esz * (size_t)k->ab_len, st);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&k->scal, 4 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->scal, 0, 4 * sizeof(double), st);
+  if (e != cudaSuccess) {
+    gl_knn_destroy(k);
+    return fail(GL_E_ALLOC, "gl_knn_create: %s", cudaGetErrorString(e));
+  }
+  rc = dtype == GL_F32 ? knn_create_t<float>(k, ei, ej, (const float *)z, (const float *)w0, st)
+                       : knn_create_t<double>(k, ei, ej, (const double *)z, (const double *)w0, st);
+  if (rc != GL_OK) {
+    gl_knn_destroy(k);
+    return rc;
+  }
+  *out = k;
+  return GL_OK;
+}
+
+extern "C" int gl_knn_destroy(gl_knn_solver *k) {
+  if (!k) return GL_OK;
+  for (void *q : {(void *)k->src, (void *)k->dst, (void *)k->eid, k->zs, k->ws, (void *)k->scal})
+    if (q) cudaFree(q);
+  if (k->s) gl_solver_destroy(k->s);
+  delete k;
+  return GL_OK;
+}
+
+extern "C" int64_t gl_knn_local_slots(gl_knn_solver *k) { return k ? k->nslots : -1; }
+
+extern "C" int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
+                            int dmax, void *stream) {
+  if (!k) return fail(GL_E_ARG, "null solver");
+  gl_solver *s = k->s;
+  cudaStream_t st = as_stream(stream);
+  s->alpha = alpha; s->beta = beta; s->step = step_size; s->maxit = maxit; s->tol = tol;
+  s->gamma = step_size / (2.0 * beta + std::sqrt(2.0 * (double)dmax));
+  s->c = 1.0 - 2.0 * s->gamma * beta;
+  GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
+  GL_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
+  if (k->dtype == GL_F32) {
+    GL_TRY(knn_slot_launch<float>(k, true, st));
+    GL_TRY(knn_node_launch<float>(k, true, st));
+  } else {
+    GL_TRY(knn_slot_launch<double>(k, true, st));
+    GL_TRY(knn_node_launch<double>(k, true, st));
+  }
+  s->begun = true;
+  return GL_OK;   // caller: exchange ab / scalars, then gl_knn_decide(k, 1, stream)
+}
+
+extern "C" int gl_knn_edge_step(gl_knn_solver *k, void *stream) {
+  if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
+  return k->dtype == GL_F32 ? knn_slot_launch<float>(k, false, as_stream(stream))
+                            : knn_slot_launch<double>(k, false, as_stream(stream));
+}
+
+extern "C" int gl_knn_node_step(gl_knn_solver *k, void *stream) {
+  if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
+  return k->dtype == GL_F32 ? knn_node_launch<float>(k, false, as_stream(stream))
+                            : knn_node_launch<double>(k, false, as_stream(stream));
+}
+
+extern "C" int gl_knn_decide(gl_knn_solver *k, int init, void *stream) {
+  if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
+  gl_solver *s = k->s;
+  knn_decide_kernel<<<1, 1, 0, as_stream(stream)>>>(k->scal, s->gprev, s->resid, s->flags, init, s->maxit, s->tol);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+extern "C" void *gl_knn_ab_ptr(gl_knn_solver *k, int64_t *n_entries) {
+  if (!k) return nullptr;
+  if (n_entries) *n_entries = k->ab_len;
+  return k->s->ab;
+}
+
+extern "C" void *gl_knn_scalars_ptr(gl_knn_solver *k) { return k ? k->scal : nullptr; }
+
+extern "C" int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, double *rel_dual, int *converged,
+                             void *stream) {
+  if (!k) return fail(GL_E_ARG, "null solver");
+  return gl_solver_status(k->s, n_iter, rel_primal, rel_dual, converged, stream);
+}
+
+extern "C" int gl_knn_store(gl_knn_solver *k, void *w_out, double edge_tol, void *stream) {
+  if (!k) return fail(GL_E_ARG, "null solver");
+  if (k->nslots == 0) return GL_OK;
+  cudaStream_t st = as_stream(stream);
+  const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+  if (k->dtype == GL_F32)
+    knn_writeback_kernel<float><<<sgrid, KNN_THREADS, 0, st>>>(k->ei, k->src, k->eid, (const float *)k->ws, k->nslots,
+                                                              edge_tol, (float *)w_out);
+  else
+    knn_writeback_kernel<double><<<sgrid, KNN_THREADS, 0, st>>>(k->ei, k->src, k->eid, (const double *)k->ws,
+                                                               k->nslots, edge_tol, (double *)w_out);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}

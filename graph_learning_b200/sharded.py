@@ -18,7 +18,8 @@ import torch.distributed as dist
 
 from . import _native as nat
 
-__all__ = ["shard_tiles", "ShardBackend", "sharded_schedule", "ShardedLogModelSolver"]
+__all__ = ["shard_tiles", "ShardBackend", "sharded_schedule", "ShardedLogModelSolver", "shard_rows", "KnnShardBackend",
+           "knn_exchange", "knn_sharded_schedule", "ShardedKNNSolver"]
 
 
 def shard_tiles(n: int, rank: int, world: int) -> tuple[int, int]:
@@ -165,3 +166,184 @@ class ShardedLogModelSolver:
             torch.cuda.synchronize()
             dist.barrier(group=self.group)  # nobody unmaps memory a peer may still read
         self.solver.close()
+
+
+# ----------------------------------------------------------------------------------------------------
+# kNN-support variant (config 5): rows sharded, (a, b) slices all-gathered, 4 scalars all-reduced
+# ----------------------------------------------------------------------------------------------------
+def shard_rows(n: int, rank: int, world: int) -> tuple[int, int, int]:
+    """Equal contiguous node ranges: (row_begin, row_end, rows_per_rank); the last ranks' ranges
+    may run past n (padding) so that every slice of the all-gather has the same length."""
+    per = -(-int(n) // int(world))
+    per = -(-per // 128) * 128   # whole 128-node blocks keep the slices aligned with the node padding
+    return rank * per, (rank + 1) * per, per
+
+
+class KnnShardBackend(Protocol):
+    def begin(self) -> None: ...        # initial degrees + node step of the own rows
+    def edge_step(self) -> None: ...    # slot sweep over the own rows' slots
+    def node_step(self) -> None: ...    # node update of the own rows, own (a, b) slice, scalar partials
+    def decide(self, init: bool) -> None: ...
+    def ab(self): ...                   # full (world * rows_per_rank, 2) array; own slice is current
+    def scalars(self): ...              # (4,) float64 partial sums
+    def done(self) -> bool: ...
+
+
+def knn_exchange(backend: KnnShardBackend, rank: int, world: int, group=None) -> None:
+    """What crosses ranks per iteration: the in-place all-gather of the (a, b) slices and the
+    all-reduce of the four residual scalars.  Nothing edge-sized moves."""
+    if world == 1:
+        return
+    full = backend.ab()
+    per = full.shape[0] // world
+    dist.all_gather_into_tensor(full, full[rank * per:(rank + 1) * per], group=group)
+    dist.all_reduce(backend.scalars(), group=group)
+
+
+def knn_sharded_schedule(backend: KnnShardBackend, maxit: int, rank: int, world: int, group=None,
+                         poll_every: int = 1) -> None:
+    """begin -> exchange -> decide(init) -> [edge step -> node step -> exchange -> decide]*"""
+    backend.begin()
+    knn_exchange(backend, rank, world, group)
+    backend.decide(True)
+    it = 0
+    while it < maxit:
+        for _ in range(min(poll_every, maxit - it)):
+            backend.edge_step()
+            backend.node_step()
+            knn_exchange(backend, rank, world, group)
+            backend.decide(False)
+            it += 1
+        if backend.done():
+            break
+
+
+class ShardedKNNSolver:
+    """CUDA backend of the row-sharded kNN-support solve (``gl_knn_*``): one process per GPU, each
+    rank builds the directed slots of its own rows from the edges touching them; iterations
+    (slot sweep, node step, NCCL all-gather + all-reduce, decision) are captured in a CUDA graph."""
+
+    def __init__(self, ei, ej, z, n_nodes: int, dtype=torch.float32, edge_init=None, group=None, rank=None,
+                 world=None):
+        """``rank`` / ``world`` override the process group's (single-process emulation of several
+        shards in the tests; the caller then performs the exchange itself)."""
+        from .smooth_learning import _device, _gl_dtype, _to_device
+        self.lib = nat.lib()
+        self.group = group
+        self.emulated = world is not None
+        self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
+        self.rank = rank if rank is not None else (dist.get_rank(group) if dist.is_initialized() else 0)
+        self.n, self.dtype = int(n_nodes), dtype
+        dev = _device()
+        ei = torch.as_tensor(ei, device=dev).to(torch.int32).contiguous()
+        ej = torch.as_tensor(ej, device=dev).to(torch.int32).contiguous()
+        z = _to_device(z, dtype)
+        self.nnz_global = int(z.numel())
+        dm = ctypes.c_int()
+        nat.check(self.lib.gl_knn_max_degree(ei.data_ptr(), ej.data_ptr(), self.nnz_global, self.n, ctypes.byref(dm), None))
+        self.dmax = dm.value
+        self.row_begin, self.row_end, self.per = shard_rows(self.n, self.rank, self.world)
+        # only the edges touching this rank's rows are kept (torch glue; setup)
+        touch = ((ei >= self.row_begin) & (ei < self.row_end)) | ((ej >= self.row_begin) & (ej < self.row_end))
+        self.local_ids = touch.nonzero(as_tuple=True)[0]
+        self._ei, self._ej = ei[touch].contiguous(), ej[touch].contiguous()
+        self._z = z[touch].contiguous()
+        self._w0 = None if edge_init is None else _to_device(edge_init, dtype)[touch].contiguous()
+        h = ctypes.c_void_p()
+        nat.check(self.lib.gl_knn_create(ctypes.byref(h), self._ei.data_ptr(), self._ej.data_ptr(), self._z.data_ptr(),
+                                         None if self._w0 is None else self._w0.data_ptr(), int(self._z.numel()), self.n,
+                                         _gl_dtype(dtype), self.row_begin, self.row_end, self.per * self.world, None))
+        self._h = h
+        from .smooth_learning import _wrap_device_memory
+        cnt = ctypes.c_int64()
+        ab_ptr = self.lib.gl_knn_ab_ptr(self._h, ctypes.byref(cnt))
+        self._ab = _wrap_device_memory(ab_ptr, 2 * cnt.value, dtype, dev, owner=self).view(cnt.value, 2)[:self.per * self.world]
+        self._scal = _wrap_device_memory(self.lib.gl_knn_scalars_ptr(self._h), 4, torch.float64, dev, owner=self)
+        self._graph = None
+        self.launches = 0
+
+    # -- backend protocol ---------------------------------------------------------------------------------
+    def begin(self, alpha=1.0, beta=1.0, step_size=0.5, maxit=1000, tol=1e-5):
+        self.maxit = int(maxit)
+        nat.check(self.lib.gl_knn_begin(self._h, float(alpha), float(beta), float(step_size), int(maxit), float(tol),
+                                        self.dmax, _cur_stream()))
+        self._graph = None
+        if self.emulated:
+            return   # the caller exchanges and calls decide(True)
+        knn_exchange(self, self.rank, self.world, self.group)
+        self.decide(True)
+
+    def edge_step(self):
+        nat.check(self.lib.gl_knn_edge_step(self._h, _cur_stream()))
+
+    def node_step(self):
+        nat.check(self.lib.gl_knn_node_step(self._h, _cur_stream()))
+
+    def decide(self, init: bool):
+        nat.check(self.lib.gl_knn_decide(self._h, 1 if init else 0, _cur_stream()))
+
+    def ab(self):
+        return self._ab
+
+    def scalars(self):
+        return self._scal
+
+    def status(self):
+        from .smooth_learning import SolveInfo
+        it, cv = ctypes.c_int(), ctypes.c_int()
+        rp, rd = ctypes.c_double(), ctypes.c_double()
+        nat.check(self.lib.gl_knn_status(self._h, ctypes.byref(it), ctypes.byref(rp), ctypes.byref(rd), ctypes.byref(cv),
+                                         _cur_stream()))
+        return SolveInfo(it.value, rp.value, rd.value, bool(cv.value))
+
+    def done(self) -> bool:
+        st = self.status()
+        return st.converged or st.n_iter >= self.maxit
+
+    # -- driver ----------------------------------------------------------------------------------------------
+    def _capture(self, iters: int):
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            for _ in range(iters):
+                self.edge_step()
+                self.node_step()
+                knn_exchange(self, self.rank, self.world, self.group)
+                self.decide(False)
+        self._graph, self._graph_iters = g, iters
+
+    def run(self, poll_every: int = 20) -> None:
+        if self.maxit <= 0:
+            return
+        poll_every = max(1, min(poll_every, self.maxit))
+        if self._graph is None or self._graph_iters != poll_every:
+            self._capture(poll_every)
+        it = 0
+        while it < self.maxit:
+            self._graph.replay()
+            it += poll_every
+            self.launches += 3 * poll_every
+            if self.done():
+                break
+
+    def gather(self, edge_tol: float = 1e-3) -> torch.Tensor:
+        """Weights over the GLOBAL edge list on every rank (each edge is written by the owner of its
+        first end; sum of disjoint stores)."""
+        loc = torch.zeros_like(self._z)
+        nat.check(self.lib.gl_knn_store(self._h, loc.data_ptr(), float(edge_tol), _cur_stream()))
+        out = torch.zeros(self.nnz_global, dtype=self._z.dtype, device=self._z.device)
+        out[self.local_ids] = loc
+        if self.world > 1 and not self.emulated:
+            dist.all_reduce(out, group=self.group)
+        return out
+
+    def close(self):
+        self._graph = None
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize()
+            self.lib.gl_knn_destroy(self._h)
+            self._h = None
+
+
+def _cur_stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)

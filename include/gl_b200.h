@@ -216,6 +216,37 @@ int gl_knn_logmodel_solve(const int32_t *ei_dev, const int32_t *ej_dev, const vo
                           double tol, double step_size, double edge_tol, void *w_dev, int *n_iter,
                           double *rel_primal, double *rel_dual, void *stream);
 
+/* Stepwise form of the same solver for row-sharded multi-GPU runs ("shard the edge list
+ * by contiguous ranges of the row index").  A rank owns the nodes [row_begin, row_end) and every
+ * directed slot i->j with i among them, so its degree sums are complete locally.  Per iteration:
+ *   gl_knn_edge_step -> gl_knn_node_step -> caller all-gathers the rank's slice of the interleaved
+ *   (gamma d, gamma pb) array (gl_knn_ab_ptr: ab_len entries of 2 x edge dtype; rank r's slice
+ *   starts at entry r's row_begin) and all-reduces the 4 float64 scalars of gl_knn_scalars_ptr
+ *   -> gl_knn_decide (stop rule, identical on every rank).
+ * gl_knn_begin performs the initial degrees and node step; the caller exchanges likewise and calls
+ * gl_knn_decide(k, 1, ...).  The edge list passed to gl_knn_create may be the full list or only the
+ * edges touching the rank's rows; it must stay alive until gl_knn_destroy (gl_knn_store reads it).
+ * gl_knn_store writes the weights of the edges whose FIRST end the rank owns, in that list's order.
+ * d_max for the step size is global: gl_knn_max_degree on the full list (or any other way). */
+typedef struct gl_knn_solver gl_knn_solver;
+int gl_knn_max_degree(const int32_t *ei_dev, const int32_t *ej_dev, int64_t nnz, int n, int *dmax_host,
+                      void *stream);
+int gl_knn_create(gl_knn_solver **out, const int32_t *ei_dev, const int32_t *ej_dev, const void *z_dev,
+                  const void *w0_dev /* nullable: zeros */, int64_t nnz, int n, int dtype, int row_begin,
+                  int row_end, int64_t ab_len, void *stream);
+int gl_knn_destroy(gl_knn_solver *k);
+int64_t gl_knn_local_slots(gl_knn_solver *k);
+int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
+                 int dmax, void *stream);
+int gl_knn_edge_step(gl_knn_solver *k, void *stream);
+int gl_knn_node_step(gl_knn_solver *k, void *stream);
+int gl_knn_decide(gl_knn_solver *k, int init, void *stream);
+void *gl_knn_ab_ptr(gl_knn_solver *k, int64_t *n_entries);
+void *gl_knn_scalars_ptr(gl_knn_solver *k);
+int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, double *rel_dual, int *converged,
+                  void *stream);
+int gl_knn_store(gl_knn_solver *k, void *w_out_dev, double edge_tol, void *stream);
+
 /* k nearest neighbours between the COLUMNS of X (m, n) float32 (no reference code):
  * exact brute force on squared Euclidean distances, fused distance + selection (the n x n matrix
  * is never written).  idx_out (n, k) int32 and d2_out (n, k) float32, ascending per row, self

@@ -132,3 +132,77 @@ def test_knn_logmodel_estimator_end_to_end():
     assert a.shape == (n, n) and abs(a - a.T).max() == 0
     mean_deg = (a > 0).sum() / n
     assert 0.5 * deg < mean_deg < 2.0 * deg   # the heuristic targets avg_degree neighbours per node
+
+
+# ---- row-sharded stepwise solver (gl_knn_*), SURVEY 8(e) ------------------------------------------------
+def _knn_case(n, k):
+    rng = np.random.default_rng(n)
+    pts = rng.uniform(size=(n, 3))
+    zsq = ((pts[:, None] - pts[None]) ** 2).sum(-1)
+    ei, ej = orc.knn_support(zsq, k)
+    return ei, ej, zsq[ei, ej] * (n ** (2 / 3))
+
+
+@pytest.mark.parametrize("dtype,tol", [("float64", 1e-10), ("float32", 1e-4)])
+def test_stepwise_knn_solver_single_shard(dtype, tol):
+    from graph_learning_b200.sharded import ShardedKNNSolver
+    n, k, maxit = 700, 8, 250
+    ei, ej, z = _knn_case(n, k)
+    wo, io = orc.solve_knn(ei, ej, z, n, maxit=maxit)
+    dt = torch.float64 if dtype == "float64" else torch.float32
+    sv = ShardedKNNSolver(ei, ej, z, n, dtype=dt)
+    sv.begin(maxit=maxit)
+    sv.run(poll_every=16)
+    st = sv.status()
+    w = sv.gather().cpu().numpy()
+    sv.close()
+    assert st.n_iter == io.n_iter
+    assert rel(w, wo) < tol
+    if dtype == "float64":
+        assert np.array_equal(w > 0, wo > 0)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_stepwise_knn_solver_emulated_shards(world):
+    """Several row shards in one process on one GPU: the exchange (all-gather of the (a, b) slices,
+    sum of the four scalars) is done by hand between the shards' buffers; results must equal the
+    oracle and every shard must take the same stop decision."""
+    from graph_learning_b200.sharded import ShardedKNNSolver
+    n, k, maxit = 900, 6, 1000
+    ei, ej, z = _knn_case(n, k)
+    wo, io = orc.solve_knn(ei, ej, z, n, maxit=maxit)
+    shards = [ShardedKNNSolver(ei, ej, z, n, dtype=torch.float64, rank=r, world=world) for r in range(world)]
+    per = shards[0].per
+    assert sum(s.lib.gl_knn_local_slots(s._h) for s in shards) == 2 * len(ei)
+
+    def exchange():
+        for r, s in enumerate(shards):
+            for t in shards:
+                if t is not s:
+                    t.ab()[r * per:(r + 1) * per].copy_(s.ab()[r * per:(r + 1) * per])
+        tot = sum(s.scalars().clone() for s in shards)
+        for s in shards:
+            s.scalars().copy_(tot)
+
+    for s in shards:
+        s.begin(maxit=maxit)
+    exchange()
+    for s in shards:
+        s.decide(True)
+    for it in range(maxit):
+        for s in shards:
+            s.edge_step()
+            s.node_step()
+        exchange()
+        for s in shards:
+            s.decide(False)
+        if it % 25 == 24 and shards[0].done():
+            break
+    sts = [s.status() for s in shards]
+    w = sum(s.gather() for s in shards).cpu().numpy()
+    for s in shards:
+        s.close()
+    assert all(st.n_iter == sts[0].n_iter and st.converged == sts[0].converged for st in sts)
+    assert sts[0].n_iter == io.n_iter
+    assert rel(w, wo) < 1e-10
+    assert np.array_equal(w > 0, wo > 0)

@@ -1,0 +1,63 @@
+"""Config 4 (K = 8 graphs, n = 1,000 nodes, m = 100,000 signals): one GLMM M-step on the device =
+8 responsibility-weighted distance builds + 8 thetas + one batched (K, E) solve.
+Prints one JSON line.  Measurement aid."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import graph_learning_b200.smooth_learning as sl  # noqa: E402
+from graph_learning_b200.synthetic import rgg_signals_filtered  # noqa: E402
+
+
+def timed(fn, reps=3):
+    fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        out = fn()
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t0)
+    return out, float(np.median(ts)) * 1e3
+
+
+def main():
+    K, n, m = 8, 1000, 100_000
+    torch.cuda.set_device(0)
+    x = rgg_signals_filtered(n, m, seed=0, device="cuda", dtype=torch.float32)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    resp = torch.softmax(3.0 * torch.randn((m, K), generator=g, device="cuda"), dim=1)
+    w = resp.sum(0)
+    means = (resp.t() @ x) / w[:, None]
+    rd = resp.t().contiguous()
+    rec = {"K": K, "n": n, "m": m}
+    for method in ("direct", "gram"):
+        fn = lambda: torch.stack([sl.pdist_sq(x, row_scale=rd[k], col_shift=means[k], method=method) for k in range(K)])  # noqa: E731
+        z, ms = timed(fn)
+        rec[f"dist_{method}_ms"] = ms
+        if method == "direct":
+            zref = z
+        else:
+            rec["gram_vs_direct_rel"] = float((z.double() - zref.double()).norm() / zref.double().norm())
+    E = n * (n - 1) // 2
+    rec["dist_algorithmic_tflops_gram"] = 2.0 * E * m * K / (rec["dist_gram_ms"] * 1e-3) / 1e12
+    thetas, ms = timed(lambda: [sl._theta_packed(z[k], n, 10) for k in range(K)])
+    rec["theta_ms"] = ms
+    zs = z * torch.tensor(thetas, device="cuda", dtype=torch.float32)[:, None]
+    for maxit, tol in ((200, 0.0), (1000, 1e-5)):
+        (wts, info), ms = timed(lambda: sl.gsp_learn_graph_log_degrees(zs, 1, 1, maxit=maxit, tol=tol, dtype="float32",
+                                                                       return_info=True))
+        rec[f"solve_maxit{maxit}_tol{tol:g}_ms"] = ms
+        rec[f"solve_maxit{maxit}_tol{tol:g}_iters"] = info.n_iter
+    rec["solve_us_per_iteration"] = rec["solve_maxit200_tol0_ms"] * 1e3 / 200
+    rec["solve_edge_iters_per_s"] = K * E * 200 / (rec["solve_maxit200_tol0_ms"] * 1e-3)
+    print(json.dumps(rec))
+
+
+if __name__ == "__main__":
+    main()
