@@ -79,6 +79,7 @@ SIGNATURES = {
                               c_int, c_int64, c_void_p]),
     "gl_knn_destroy": (c_int, [c_void_p]),
     "gl_knn_local_slots": (c_int64, [c_void_p]),
+    "gl_knn_set_fused": (c_int, [c_void_p, c_int]),
     "gl_knn_begin": (c_int, [c_void_p, c_double, c_double, c_double, c_int, c_double, c_int, c_void_p]),
     "gl_knn_edge_step": (c_int, [c_void_p, c_void_p]),
     "gl_knn_node_step": (c_int, [c_void_p, c_void_p]),

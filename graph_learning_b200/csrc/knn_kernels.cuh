@@ -52,112 +52,134 @@ static __global__ void knn_expand_kernel(const int32_t *ei, const int32_t *ej, i
   mine = warp_sum(mine);
   if ((threadIdx.x & 31) == 0 && mine) atomicAdd(count, mine);
 }
-// sorted slots: fill in the far end and this slot's copies of z and w
+// ---- sliced-ELL layout of the directed slots (SELL-32) ----------------------------------------------
+// Rows (= source nodes, local index r = node - row_begin) are grouped into slices of 32 consecutive
+// rows; slice s stores width[s] = max degree of its rows "columns" of 32 entries each, column-major:
+//   entry(t, r) of slice s  at  slice_off[s] + t * 32 + (r & 31).
+// Lane r of the warp that owns the slice walks its row with unit-stride (coalesced) warp accesses, keeps
+// the row's degree sums in registers and STORES them: no shuffles, no atomics, deterministic sums.
+// Padding entries hold dst = -1.
+
+static __global__ void knn_row_count_kernel(const int32_t *src, int64_t nslots, int row_begin, int *cnt) {
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x)
+    atomicAdd(cnt + (src[s] - row_begin), 1);
+}
+// width of every slice (max row count) as the number of entries it occupies (width * 32)
+static __global__ void knn_slice_size_kernel(const int *cnt, int rows, int nslices, long long *size) {
+  const int s = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (s >= nslices) return;
+  const int r = s * 32 + lane;
+  int c = r < rows ? cnt[r] : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c = max(c, __shfl_xor_sync(0xffffffffu, c, o));
+  if (lane == 0) size[s] = 32LL * c;
+}
+// scatter the source-sorted slots into the SELL arrays; eid_canon = undirected edge id on the copy whose
+// source is the edge's first end (the copy gl_knn_store / the one-shot solve reads back), else -1
 template <typename F>
-__global__ void knn_fill_kernel(const int32_t *ei, const int32_t *ej, const F *z, const F *w, int64_t nslots,
-                                const int32_t *src, const int32_t *eid, int32_t *dst, F *zs, F *ws) {
+__global__ void knn_sell_fill_kernel(const int32_t *ei, const int32_t *ej, const F *z, const F *w, int64_t nslots,
+                                     const int32_t *src, const int32_t *eid, int row_begin, const int *row_ptr,
+                                     const long long *slice_off, int32_t *dst_s, F *z_s, F *w_s, int32_t *eid_canon) {
   for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
-    const int32_t e = eid[s], i = ei[e], j = ej[e];
-    dst[s] = src[s] == i ? j : i;
-    zs[s] = z[e];
-    ws[s] = w[e];
+    const int32_t e = eid[s], i = ei[e], j = ej[e], me = src[s];
+    const int r = me - row_begin;
+    const int t = (int)(s - row_ptr[r]);
+    const long long pos = slice_off[r >> 5] + 32LL * t + (r & 31);
+    dst_s[pos] = me == i ? j : i;
+    z_s[pos] = z[e];
+    w_s[pos] = w[e];
+    eid_canon[pos] = me == i ? e : -1;
   }
 }
-// result back in the caller's edge order, from the slot whose source is the edge's first end; the
-// edge_tol threshold of smooth_learning.py:169 applied on the way
 template <typename F>
-__global__ void knn_writeback_kernel(const int32_t *ei, const int32_t *src, const int32_t *eid, const F *ws,
-                                     int64_t nslots, double edge_tol, F *w) {
-  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
-    const int32_t e = eid[s];
-    if (src[s] == ei[e]) {
-      const F v = ws[s];
+__global__ void knn_sell_writeback_kernel(const int32_t *eid_canon, const F *w_s, long long total, double edge_tol,
+                                          F *w) {
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long long)gridDim.x * blockDim.x) {
+    const int32_t e = eid_canon[p];
+    if (e >= 0) {
+      const F v = w_s[p];
       w[e] = (double)v < edge_tol ? F(0) : v;
     }
   }
 }
 
-// MODE 0: iteration.  MODE 1: initial degrees S w0 and ||w0||^2.  One thread per directed slot,
-// warps own 32 consecutive slots; gsum receives HALF the slot sums (every edge appears twice).
+// MODE 0: iteration.  MODE 1: initial degrees S w0 and ||w0||^2.  One warp per slice (grid-stride), lane
+// = row; KNN_UNROLL columns of the slice are loaded (then gathered) together before the first use.
+// gsum receives HALF the slot sums (every undirected edge appears twice).
 template <typename F, int MODE>
-__global__ void __launch_bounds__(KNN_THREADS) knn_slot_kernel(const int32_t *__restrict__ src,
-                                                               const int32_t *__restrict__ dst,
+__global__ void __launch_bounds__(KNN_THREADS) knn_sell_kernel(const int32_t *__restrict__ dst,
                                                                const F *__restrict__ z, F *__restrict__ w,
-                                                               int64_t nslots,
+                                                               const long long *__restrict__ slice_off, int nslices,
+                                                               int row_begin,
                                                                const typename Vec2<F>::type *__restrict__ ab,
-                                                               double *sp, double *sw,
-                                                               double *gsum, const int *flags, F c, F tgz) {
+                                                               double *sp, double *sw, double *gsum,
+                                                               const int *flags, F c, F tgz) {
   if (MODE == 0 && *reinterpret_cast<const volatile int *>(flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][2];
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   double res = 0.0, wsq = 0.0;
-  // Each warp takes KNN_UNROLL groups of 32 consecutive slots per step and issues all their loads
-  // (then all their gathers) before the first use: one group per step leaves the kernel
-  // latency-bound (measured 1.25 TB/s moved at 1.1e7 edges).
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x * KNN_UNROLL;
-  for (int64_t s0 = ((int64_t)blockIdx.x * (KNN_THREADS / 32) + wp) * 32 * KNN_UNROLL; s0 < nslots; s0 += stride) {
-    int i[KNN_UNROLL], j[KNN_UNROLL];
-    F wo[KNN_UNROLL], zz[KNN_UNROLL];
-#pragma unroll
-    for (int u = 0; u < KNN_UNROLL; ++u) {
-      const int64_t s = s0 + u * 32 + lane;
-      const bool valid = s < nslots;
-      i[u] = valid ? src[s] : -1;
-      wo[u] = valid ? w[s] : F(0);
-      if (MODE == 0) {
-        j[u] = valid ? dst[s] : 0;
-        zz[u] = valid ? z[s] : F(0);
-      }
-    }
-    typename Vec2<F>::type abi[KNN_UNROLL], abj[KNN_UNROLL];
-    if (MODE == 0) {
+  const int warps = gridDim.x * (KNN_THREADS / 32);
+  for (int s = blockIdx.x * (KNN_THREADS / 32) + wp; s < nslices; s += warps) {
+    const long long base = slice_off[s] + lane, end = slice_off[s + 1];
+    const int me = row_begin + s * 32 + lane;
+    typename Vec2<F>::type abi;
+    abi.x = abi.y = F(0);
+    if (MODE == 0) abi = ab[me];
+    double acc_p = 0.0, acc_w = 0.0;
+    // two batches of KNN_UNROLL columns in flight: the next batch's (dst, w, z) loads are issued before
+    // this batch's gathers are consumed
+    int j[KNN_UNROLL], jn[KNN_UNROLL];
+    F wo[KNN_UNROLL], zz[KNN_UNROLL], won[KNN_UNROLL], zzn[KNN_UNROLL];
+    auto fetch = [&](long long p0, int *jj, F *ww, F *zv) {
 #pragma unroll
       for (int u = 0; u < KNN_UNROLL; ++u) {
-        abi[u] = ab[i[u] < 0 ? 0 : i[u]];   // (a, b) of both ends: one gather each
-        abj[u] = ab[j[u]];
+        const long long p = p0 + 32LL * u;
+        const bool in = p < end;
+        jj[u] = in ? dst[p] : -1;
+        ww[u] = in ? w[p] : F(0);
+        zv[u] = (MODE == 0 && in) ? z[p] : F(0);
       }
-    }
+    };
+    fetch(base, j, wo, zz);
+    for (long long p0 = base; p0 < end; p0 += 32LL * KNN_UNROLL) {
+      if (MODE == 1) {
 #pragma unroll
-    for (int u = 0; u < KNN_UNROLL; ++u) {
-      const int64_t s = s0 + u * 32 + lane;
-      const bool valid = s < nslots;
-      F vp = F(0), vw = F(0);   // segment sums in the edge dtype (<= 32 terms), float64 from the atomic on
-      if (valid) {
-        if (MODE == 1) {
-          vw = wo[u];
-          wsq += (double)vw * (double)vw;
-        } else {
-          const F y = c * wo[u] - (abi[u].x + abj[u].x);
-          F p = y - tgz * zz[u];
-          p = p > F(0) ? p : F(0);
-          const F q = c * p - (abi[u].y + abj[u].y);
+        for (int u = 0; u < KNN_UNROLL; ++u)
+          if (j[u] >= 0) {
+            acc_w += (double)wo[u];
+            wsq += (double)wo[u] * (double)wo[u];
+          }
+        fetch(p0 + 32LL * KNN_UNROLL, j, wo, zz);
+        continue;
+      }
+      typename Vec2<F>::type abj[KNN_UNROLL];
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u) abj[u] = ab[j[u] < 0 ? me : j[u]];   // far end: one gather
+      fetch(p0 + 32LL * KNN_UNROLL, jn, won, zzn);
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u)
+        if (j[u] >= 0) {
+          const F y = c * wo[u] - (abi.x + abj[u].x);
+          F pv = y - tgz * zz[u];
+          pv = pv > F(0) ? pv : F(0);
+          const F q = c * pv - (abi.y + abj[u].y);
           const F r = q - y;
           const F wn = (wo[u] - y) + q;
-          w[s] = wn;
-          vp = p;
-          vw = wn;
+          w[p0 + 32LL * u] = wn;
+          acc_p += (double)pv;
+          acc_w += (double)wn;
           res += (double)r * (double)r;
           wsq += (double)wn * (double)wn;
         }
-      }
-      // segmented suffix sums over runs of equal source (slots are sorted by source)
-      const int iu = i[u];
 #pragma unroll
-      for (int off = 1; off < 32; off <<= 1) {
-        const int io = __shfl_down_sync(0xffffffffu, iu, off);
-        const F po = __shfl_down_sync(0xffffffffu, vp, off);
-        const F wo2 = __shfl_down_sync(0xffffffffu, vw, off);
-        if (lane + off < 32 && io == iu) {
-          vp += po;
-          vw += wo2;
-        }
-      }
-      const int iprev = __shfl_up_sync(0xffffffffu, iu, 1);
-      if (valid && (lane == 0 || iprev != iu)) {
-        if (MODE == 0 && vp != F(0)) atomicAdd(sp + iu, (double)vp);
-        atomicAdd(sw + iu, (double)vw);
+      for (int u = 0; u < KNN_UNROLL; ++u) {
+        j[u] = jn[u];
+        wo[u] = won[u];
+        zz[u] = zzn[u];
       }
     }
+    if (MODE == 0) sp[me] = acc_p;   // every row is owned by exactly one lane: plain stores
+    sw[me] = acc_w;
   }
   res = warp_sum(res);
   wsq = warp_sum(wsq);
@@ -183,6 +205,7 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_slot_kernel(const int32_t *__
 // n = 1e6, each paying a fence, a barrier and a ticket) measured 123 us per launch, latency-bound.
 // Only the interleaved (a, b) pairs the slot kernel gathers are written, not a and b separately.
 constexpr int KNN_NODE_THREADS = 256;
+constexpr int KNN_NODE_UNROLL = 4;
 struct KnnNodeArgs {
   double *d, *yb, *pb, *rb, *xch, *gprev, *resid, *node_partial;
   void *ab;
@@ -202,34 +225,50 @@ __global__ void __launch_bounds__(KNN_NODE_THREADS) knn_node_kernel(const KnnNod
   const int tid = threadIdx.x;
   double my_rb2 = 0.0, my_d2 = 0.0;
   typename Vec2<F>::type *ab = static_cast<typename Vec2<F>::type *>(A.ab);
-  for (int64_t idx = A.row_begin + (int64_t)blockIdx.x * KNN_NODE_THREADS + tid; idx < A.row_end;
-       idx += (int64_t)gridDim.x * KNN_NODE_THREADS) {
-    const double sp = A.xch[idx], sw = A.xch[A.npad + idx];
-    A.xch[idx] = 0.0;
-    A.xch[A.npad + idx] = 0.0;
-    double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
-    if (idx < A.n) {
-      if (A.init) {
-        dn = sw;                                          // d0 = S w0            :144
-      } else {
-        const double dv = A.d[idx], ybv = A.yb[idx];
-        const double qb = A.pb[idx] + A.gamma * sp;       //                      :154
-        rbv = qb - ybv;
-        dn = (dv - ybv) + qb;                             //                      :164
-      }
-      ybn = dn + A.gamma * sw;                            //                      :148
-      pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;    //                      :151
+  // KNN_NODE_UNROLL independent nodes per thread: all loads first (the stores below could alias them
+  // as far as the compiler knows, so it would not hoist the next node's loads by itself)
+  const int64_t gstride = (int64_t)gridDim.x * KNN_NODE_THREADS;
+  for (int64_t idx0 = A.row_begin + (int64_t)blockIdx.x * KNN_NODE_THREADS + tid; idx0 < A.row_end;
+       idx0 += gstride * KNN_NODE_UNROLL) {
+    double sp[KNN_NODE_UNROLL], sw[KNN_NODE_UNROLL], dv[KNN_NODE_UNROLL], ybv[KNN_NODE_UNROLL], pbv[KNN_NODE_UNROLL];
+#pragma unroll
+    for (int u = 0; u < KNN_NODE_UNROLL; ++u) {
+      const int64_t idx = idx0 + u * gstride;
+      const bool in = idx < A.row_end;
+      sp[u] = in ? A.xch[idx] : 0.0;
+      sw[u] = in ? A.xch[A.npad + idx] : 0.0;
+      const bool live = in && idx < A.n && !A.init;
+      dv[u] = live ? A.d[idx] : 0.0;
+      ybv[u] = live ? A.yb[idx] : 0.0;
+      pbv[u] = live ? A.pb[idx] : 0.0;
     }
-    my_rb2 += rbv * rbv;
-    my_d2 += dn * dn;
-    A.d[idx] = dn;
-    A.yb[idx] = ybn;
-    A.pb[idx] = pbn;
-    A.rb[idx] = rbv;
-    typename Vec2<F>::type pr;
-    pr.x = (F)(A.gamma * dn);
-    pr.y = (F)(A.gamma * pbn);
-    ab[idx] = pr;
+#pragma unroll
+    for (int u = 0; u < KNN_NODE_UNROLL; ++u) {
+      const int64_t idx = idx0 + u * gstride;
+      if (idx >= A.row_end) continue;
+      double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
+      if (idx < A.n) {
+        if (A.init) {
+          dn = sw[u];                                       // d0 = S w0            :144
+        } else {
+          const double qb = pbv[u] + A.gamma * sp[u];       //                      :154
+          rbv = qb - ybv[u];
+          dn = (dv[u] - ybv[u]) + qb;                       //                      :164
+        }
+        ybn = dn + A.gamma * sw[u];                         //                      :148
+        pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;    //                      :151
+      }
+      my_rb2 += rbv * rbv;
+      my_d2 += dn * dn;
+      A.d[idx] = dn;
+      A.yb[idx] = ybn;
+      A.pb[idx] = pbn;
+      A.rb[idx] = rbv;
+      typename Vec2<F>::type pr;
+      pr.x = (F)(A.gamma * dn);
+      pr.y = (F)(A.gamma * pbn);
+      ab[idx] = pr;
+    }
   }
   my_rb2 = warp_sum(my_rb2);
   my_d2 = warp_sum(my_d2);
@@ -350,7 +389,7 @@ template <typename F> static int launch_knn_node(gl_solver *s, bool init, cudaSt
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
   int grid = (s->npad + KNN_NODE_THREADS - 1) / KNN_NODE_THREADS;
-  if (grid > 148 * 4) grid = 148 * 4;
+  if (grid > 148 * 2) grid = 148 * 2;
   knn_node_kernel<F><<<grid, KNN_NODE_THREADS, 0, st>>>(A);
   GL_LAUNCH_CHECK();
   return GL_OK;

@@ -8,6 +8,8 @@
 // (8 B x n in fp32; by the caller: NCCL in-place all-gather, graph_learning_b200/sharded.py).
 // Per iteration:  edge_step -> node_step -> [all-gather ab | all-reduce 4 scalars] -> decide.
 // The node state (d, yb, pb) of foreign rows is never touched.
+#include <cub/device/device_scan.cuh>
+
 #include "knn_kernels.cuh"
 
 struct gl_knn_solver {
@@ -16,9 +18,13 @@ struct gl_knn_solver {
   int64_t nnz = 0, nslots = 0;
   int row_begin = 0, row_end = 0;
   int64_t ab_len = 0;          // entries of the ab array (>= npad; world x rows per rank)
-  const int32_t *ei = nullptr; // caller's edge list (kept alive by the caller until destroy)
-  int32_t *src = nullptr, *dst = nullptr, *eid = nullptr;
+  // SELL-32 arrays of the own rows' directed slots (knn_kernels.cuh)
+  int32_t *dst = nullptr, *eid_canon = nullptr;
   void *zs = nullptr, *ws = nullptr;
+  long long *slice_off = nullptr;   // [nslices + 1]
+  int nslices = 0;
+  long long total = 0;              // entries incl. padding
+  int fused = 0;                    // 1: single shard, the node kernel applies the stop rule itself
   double *scal = nullptr;      // [4] partial sums for the exchange
 };
 
@@ -67,28 +73,74 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
   KS_CUDA(cudaMemcpyAsync(&h_count, count, sizeof(h_count), cudaMemcpyDeviceToHost, st));
   KS_CUDA(cudaStreamSynchronize(st));
   k->nslots = (int64_t)h_count;
+  // ---- SELL-32 build: row counts -> row_ptr, slice sizes -> slice_off, scatter -----------------------
+  const int rows = k->row_end - k->row_begin;
+  k->nslices = (rows + 31) / 32;
+  int *cnt = nullptr, *row_ptr = nullptr;
+  long long *size = nullptr;
+  void *scan_tmp = nullptr;
+  auto cleanup2 = [&]() {
+    for (void *q : {(void *)cnt, (void *)row_ptr, (void *)size, scan_tmp})
+      if (q) cudaFree(q);
+  };
+#define KS2_CUDA(expr)                                                                                     \
+  do {                                                                                                     \
+    cudaError_t _e = (expr);                                                                               \
+    if (_e != cudaSuccess) {                                                                               \
+      cleanup2();                                                                                          \
+      cleanup();                                                                                           \
+      return fail(GL_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    }                                                                                                      \
+  } while (0)
+  KS2_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * (size_t)(rows + 1)));
+  KS2_CUDA(cudaMalloc((void **)&row_ptr, sizeof(int) * (size_t)(rows + 1)));
+  KS2_CUDA(cudaMalloc((void **)&size, sizeof(long long) * (size_t)(k->nslices + 1)));
+  KS2_CUDA(cudaMalloc((void **)&k->slice_off, sizeof(long long) * (size_t)(k->nslices + 1)));
+  KS2_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int) * (size_t)(rows + 1), st));
+  KS2_CUDA(cudaMemsetAsync(size, 0, sizeof(long long) * (size_t)(k->nslices + 1), st));
   if (k->nslots > 0) {
-    const size_t lb = sizeof(int32_t) * (size_t)k->nslots, fb = sizeof(F) * (size_t)k->nslots;
-    KS_CUDA(cudaMalloc((void **)&k->src, lb));
-    KS_CUDA(cudaMalloc((void **)&k->eid, lb));
-    KS_CUDA(cudaMalloc((void **)&k->dst, lb));
-    KS_CUDA(cudaMalloc(&k->zs, fb));
-    KS_CUDA(cudaMalloc(&k->ws, fb));
-    KS_CUDA(cudaMemcpyAsync(k->src, src_all, lb, cudaMemcpyDeviceToDevice, st));   // local slots sort first
-    KS_CUDA(cudaMemcpyAsync(k->eid, eid_all, lb, cudaMemcpyDeviceToDevice, st));
+    const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+    knn_row_count_kernel<<<sgrid, KNN_THREADS, 0, st>>>(src_all, k->nslots, k->row_begin, cnt);
+    g_launches.fetch_add(1);
+  }
+  size_t b1 = 0, b2 = 0;
+  KS2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, b1, cnt, row_ptr, rows + 1, st));
+  KS2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, b2, size, k->slice_off, k->nslices + 1, st));
+  KS2_CUDA(cudaMalloc(&scan_tmp, std::max(b1, b2) + 16));
+  KS2_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, b1, cnt, row_ptr, rows + 1, st));
+  if (k->nslices > 0) {
+    knn_slice_size_kernel<<<(k->nslices + 7) / 8, 256, 0, st>>>(cnt, rows, k->nslices, size);
+    g_launches.fetch_add(1);
+  }
+  KS2_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, b2, size, k->slice_off, k->nslices + 1, st));
+  KS2_CUDA(cudaMemcpyAsync(&k->total, k->slice_off + k->nslices, sizeof(long long), cudaMemcpyDeviceToHost, st));
+  KS2_CUDA(cudaStreamSynchronize(st));
+  if (k->total > 0) {
+    const size_t lb = sizeof(int32_t) * (size_t)k->total, fb = sizeof(F) * (size_t)k->total;
+    KS2_CUDA(cudaMalloc((void **)&k->dst, lb));
+    KS2_CUDA(cudaMalloc((void **)&k->eid_canon, lb));
+    KS2_CUDA(cudaMalloc(&k->zs, fb));
+    KS2_CUDA(cudaMalloc(&k->ws, fb));
+    KS2_CUDA(cudaMemsetAsync(k->dst, 0xFF, lb, st));          // -1: padding
+    KS2_CUDA(cudaMemsetAsync(k->eid_canon, 0xFF, lb, st));
+    KS2_CUDA(cudaMemsetAsync(k->zs, 0, fb, st));
+    KS2_CUDA(cudaMemsetAsync(k->ws, 0, fb, st));
     const F *w_init = w0;
     if (!w_init) {
-      KS_CUDA(cudaMalloc((void **)&w_zero, sizeof(F) * (size_t)nnz));
-      KS_CUDA(cudaMemsetAsync(w_zero, 0, sizeof(F) * (size_t)nnz, st));
+      KS2_CUDA(cudaMalloc((void **)&w_zero, sizeof(F) * (size_t)nnz));
+      KS2_CUDA(cudaMemsetAsync(w_zero, 0, sizeof(F) * (size_t)nnz, st));
       w_init = w_zero;
     }
     const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
-    knn_fill_kernel<F><<<sgrid, KNN_THREADS, 0, st>>>(ei, ej, z, w_init, k->nslots, k->src, k->eid, k->dst,
-                                                      (F *)k->zs, (F *)k->ws);
+    knn_sell_fill_kernel<F><<<sgrid, KNN_THREADS, 0, st>>>(ei, ej, z, w_init, k->nslots, src_all, eid_all, k->row_begin,
+                                                           row_ptr, k->slice_off, k->dst, (F *)k->zs, (F *)k->ws,
+                                                           k->eid_canon);
     g_launches.fetch_add(1);
-    KS_CUDA(cudaGetLastError());
+    KS2_CUDA(cudaGetLastError());
   }
-  KS_CUDA(cudaStreamSynchronize(st));
+  KS2_CUDA(cudaStreamSynchronize(st));
+  cleanup2();
+#undef KS2_CUDA
 #undef KS_CUDA
   cleanup();
   return rc;
@@ -96,17 +148,17 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
 
 template <typename F> static int knn_slot_launch(gl_knn_solver *k, bool init, cudaStream_t st) {
   gl_solver *s = k->s;
-  if (k->nslots == 0) return GL_OK;
+  if (k->nslices == 0) return GL_OK;
   double *sp = s->xch, *sw = s->xch + s->npad, *gsum = s->xch + 2 * (int64_t)s->npad;
-  const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS * KNN_UNROLL - 1) / (KNN_THREADS * KNN_UNROLL), 148 * 8);
+  const int grid = std::max(1, std::min((k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32), 148 * 8));
   const F c = (F)s->c, tgz = (F)(2.0 * s->gamma);
   using V = typename Vec2<F>::type;
   if (init)
-    knn_slot_kernel<F, 1><<<sgrid, KNN_THREADS, 0, st>>>(k->src, k->dst, (const F *)k->zs, (F *)k->ws, k->nslots,
-                                                        (const V *)s->ab, sp, sw, gsum, s->flags, c, tgz);
+    knn_sell_kernel<F, 1><<<grid, KNN_THREADS, 0, st>>>(k->dst, (const F *)k->zs, (F *)k->ws, k->slice_off, k->nslices,
+                                                       k->row_begin, (const V *)s->ab, sp, sw, gsum, s->flags, c, tgz);
   else
-    knn_slot_kernel<F, 0><<<sgrid, KNN_THREADS, 0, st>>>(k->src, k->dst, (const F *)k->zs, (F *)k->ws, k->nslots,
-                                                        (const V *)s->ab, sp, sw, gsum, s->flags, c, tgz);
+    knn_sell_kernel<F, 0><<<grid, KNN_THREADS, 0, st>>>(k->dst, (const F *)k->zs, (F *)k->ws, k->slice_off, k->nslices,
+                                                       k->row_begin, (const V *)s->ab, sp, sw, gsum, s->flags, c, tgz);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }
@@ -119,13 +171,13 @@ template <typename F> static int knn_node_launch(gl_knn_solver *k, bool init, cu
   A.ab = s->ab;
   A.flags = s->flags;
   A.n = s->n; A.npad = s->npad; A.init = init ? 1 : 0; A.maxit = s->maxit;
-  A.row_begin = k->row_begin; A.row_end = k->row_end; A.fused = 0; A.scal = k->scal;
+  A.row_begin = k->row_begin; A.row_end = k->row_end; A.fused = k->fused; A.scal = k->scal;
   A.gamma = s->gamma;
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
   const int rows = k->row_end - k->row_begin;
   int grid = (rows + KNN_NODE_THREADS - 1) / KNN_NODE_THREADS;
-  grid = std::max(1, std::min(grid, 148 * 4));
+  grid = std::max(1, std::min(grid, 148 * 2));
   knn_node_kernel<F><<<grid, KNN_NODE_THREADS, 0, st>>>(A);
   GL_LAUNCH_CHECK();
   return GL_OK;
@@ -170,7 +222,6 @@ extern "C" int gl_knn_create(gl_knn_solver **out, const int32_t *ei, const int32
   }
   k->dtype = dtype;
   k->nnz = nnz;
-  k->ei = ei;
   k->row_begin = row_begin;
   k->row_end = std::min(row_end, k->s->npad);
   k->ab_len = std::max<int64_t>(ab_len, k->s->npad);
@@ -196,7 +247,7 @@ extern "C" int gl_knn_create(gl_knn_solver **out, const int32_t *ei, const int32
 
 extern "C" int gl_knn_destroy(gl_knn_solver *k) {
   if (!k) return GL_OK;
-  for (void *q : {(void *)k->src, (void *)k->dst, (void *)k->eid, k->zs, k->ws, (void *)k->scal})
+  for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal})
     if (q) cudaFree(q);
   if (k->s) gl_solver_destroy(k->s);
   delete k;
@@ -241,6 +292,7 @@ extern "C" int gl_knn_node_step(gl_knn_solver *k, void *stream) {
 extern "C" int gl_knn_decide(gl_knn_solver *k, int init, void *stream) {
   if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
   gl_solver *s = k->s;
+  if (k->fused) return GL_OK;   // single shard: the node kernel has applied the stop rule
   knn_decide_kernel<<<1, 1, 0, as_stream(stream)>>>(k->scal, s->gprev, s->resid, s->flags, init, s->maxit, s->tol);
   GL_LAUNCH_CHECK();
   return GL_OK;
@@ -262,15 +314,22 @@ extern "C" int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, 
 
 extern "C" int gl_knn_store(gl_knn_solver *k, void *w_out, double edge_tol, void *stream) {
   if (!k) return fail(GL_E_ARG, "null solver");
-  if (k->nslots == 0) return GL_OK;
+  if (k->total == 0) return GL_OK;
   cudaStream_t st = as_stream(stream);
-  const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+  const int grid = (int)std::min<long long>((k->total + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
   if (k->dtype == GL_F32)
-    knn_writeback_kernel<float><<<sgrid, KNN_THREADS, 0, st>>>(k->ei, k->src, k->eid, (const float *)k->ws, k->nslots,
-                                                              edge_tol, (float *)w_out);
+    knn_sell_writeback_kernel<float><<<grid, KNN_THREADS, 0, st>>>(k->eid_canon, (const float *)k->ws, k->total, edge_tol,
+                                                                  (float *)w_out);
   else
-    knn_writeback_kernel<double><<<sgrid, KNN_THREADS, 0, st>>>(k->ei, k->src, k->eid, (const double *)k->ws,
-                                                               k->nslots, edge_tol, (double *)w_out);
+    knn_sell_writeback_kernel<double><<<grid, KNN_THREADS, 0, st>>>(k->eid_canon, (const double *)k->ws, k->total,
+                                                                   edge_tol, (double *)w_out);
   GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+// single shard with the stop rule fused into the node kernel (what the one-shot solve uses)
+extern "C" int gl_knn_set_fused(gl_knn_solver *k, int fused) {
+  if (!k) return fail(GL_E_ARG, "null solver");
+  k->fused = fused ? 1 : 0;
   return GL_OK;
 }
