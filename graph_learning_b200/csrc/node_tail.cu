@@ -52,7 +52,11 @@ __device__ void lambda_max4(const double *const *G, int K, double *scratch, doub
     __syncthreads();
     return;
   }
-  double *B = scratch + (int64_t)q * 2 * KK, *C = B + KK;
+  // the squarings ping-pong between two buffers: in shared memory for K <= 16 (26 x 3 barriers with a
+  // global round trip each measured ~50 us at K = 8), in the global scratch beyond that
+  __shared__ double s_mat[4][2][256];
+  double *B = KK <= 256 ? s_mat[q][0] : scratch + (int64_t)q * 2 * KK;
+  double *C = KK <= 256 ? s_mat[q][1] : B + KK;
   __shared__ double s_tr[4];
   __shared__ int s_bad[4];
   if (lt == 0) {
@@ -453,8 +457,10 @@ int launch_gram_edges(gl_solver *s, cudaStream_t st) {
   if (s->K == 1 || s->ntl == 0) return GL_OK;
   const int nb = (s->K + GB - 1) / GB;
   const int64_t len = s->gstride;
-  int chunks = (int)((len + 8191) / 8192);
-  if (chunks > 592) chunks = 592;
+  // 16 edges per thread: the kernel is latency-bound (a thread's loop is serial), so it wants many
+  // short CTAs rather than a few long ones (8192-edge chunks measured 88 us at K = 8, n = 1,000)
+  int chunks = (int)((len + 2047) / 2048);
+  if (chunks > 2368) chunks = 2368;
   if (chunks < 1) chunks = 1;
   dim3 grid(chunks, nb * (nb + 1) / 2, 2);
   const int64_t total = (int64_t)s->K * s->npad;
