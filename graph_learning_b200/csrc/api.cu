@@ -57,7 +57,7 @@ void free_all(gl_solver *s) {
   for (void *p : s->ipc_opened)
     if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
-                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace, s->ab};
+                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace, s->ab, s->gram_part};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -153,6 +153,12 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
   if (rc == GL_OK) rc = alloc_zero((void **)&s->gprev, 8 * 2 * KK);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->resid, 16);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->eig_scratch, 8 * 10 * KK + 8 * K);
+  if (rc == GL_OK && K > 1 && K <= 128) {  // batch node tail: one CTA per 256/K' nodes, all K graphs
+    int kp = 1;
+    while (kp < K) kp <<= 1;
+    const size_t ctas = (size_t)s->npad / (256 / kp);
+    rc = alloc_zero((void **)&s->gram_part, sizeof(double) * ctas * 2 * KK);
+  }
   if (rc == GL_OK) rc = alloc_zero((void **)&s->flags, sizeof(int) * FLAG_COUNT);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->grid_bar, 64);
   if (rc == GL_OK) rc = fill_tile_table(s);

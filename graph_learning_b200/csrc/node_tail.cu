@@ -28,6 +28,8 @@ struct NodeArgs {
   double *resid;   // rel_primal, rel_dual
   double *eig;     // scratch 4 x 2 x K*K
   double *node_partial;  // [gridDim.x][2] (K == 1)
+  double *gram_part;     // batch mapping: [gridDim.x][2][K*K] per-CTA partial node Grams
+  int npc;               // batch mapping: nodes per CTA (every CTA holds all K graphs of its nodes); 0 = flat mapping
   int *hdr;              // comm header (peer mode)
   int64_t xch_stride;
   int world, rank;
@@ -164,7 +166,17 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   const int tid = threadIdx.x;
   double my_rb2 = 0.0, my_d2 = 0.0;
   const int64_t total = (int64_t)A.K * A.npad;
-  const int64_t idx = (int64_t)blockIdx.x * NODE_THREADS + tid;
+  // flat mapping: thread = entry of the (K, npad) arrays.  Batch mapping (K > 1): a CTA owns npc
+  // consecutive nodes of ALL K graphs (thread = graph tid / npc, node tid % npc), so the K x K Grams
+  // of the dual residual and of d' are formed per CTA from shared memory instead of by one CTA
+  // walking all nodes serially (measured 71 us at K = 8, n = 1,000).
+  int64_t idx = (int64_t)blockIdx.x * NODE_THREADS + tid;
+  bool active = idx < total;
+  if (A.npc > 0) {
+    const int k = tid / A.npc;
+    active = k < A.K;
+    idx = (int64_t)k * A.npad + (int64_t)blockIdx.x * A.npc + tid % A.npc;
+  }
   // ---- peer mode: wait until every rank has published its partials of this exchange, then read
   //      them straight out of the peers' memory over NVLink (fixed rank order -> bit-identical
   //      replicated state on all ranks).  Buffers alternate by exchange parity; the one NOT being
@@ -192,7 +204,8 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     }
     __syncthreads();
   }
-  if (idx < total) {
+  double rb_keep = 0.0, d_keep = 0.0;
+  if (active) {
     const int v = (int)(idx % A.npad);
     double sp, sw;
     if (A.world > 1) {
@@ -234,6 +247,8 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     }
     my_rb2 = rbv * rbv;
     my_d2 = dn * dn;
+    rb_keep = rbv;
+    d_keep = dn;
     A.d[idx] = dn;
     A.yb[idx] = ybn;
     A.pb[idx] = pbn;
@@ -246,6 +261,20 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
       static_cast<double *>(A.a)[idx] = A.gamma * dn;
       static_cast<double *>(A.b)[idx] = A.gamma * pbn;
       if (A.ab) static_cast<double2 *>(A.ab)[idx] = make_double2(A.gamma * dn, A.gamma * pbn);
+    }
+  }
+  if (A.npc > 0) {  // batch mapping: K x K partial Grams of this CTA's nodes, fixed summation order
+    __shared__ double s_val[2][NODE_THREADS];
+    s_val[0][tid] = rb_keep;
+    s_val[1][tid] = d_keep;
+    __syncthreads();
+    const int KKb = A.K * A.K, npc = A.npc;
+    for (int p = tid; p < 2 * KKb; p += NODE_THREADS) {
+      const int which = p / KKb, e = p % KKb, k = e / A.K, l = e % A.K;
+      const double *xk = s_val[which] + k * npc, *xl = s_val[which] + l * npc;
+      double acc = 0.0;
+      for (int j = 0; j < npc; ++j) acc += xk[j] * xl[j];
+      A.gram_part[((int64_t)blockIdx.x * 2 + which) * KKb + e] = acc;
     }
   }
   if (A.K == 1) {  // single graph: per-CTA partial sums, combined in fixed order by the last CTA
@@ -320,6 +349,14 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
       g_d[0] = d2;
     }
     __syncthreads();
+  } else if (A.npc > 0) {
+    for (int p = tid; p < 2 * KK; p += NODE_THREADS) {
+      const int which = p / KK, e = p % KK;
+      double acc = 0.0;
+      for (int c = 0; c < (int)gridDim.x; ++c) acc += __ldcg(A.gram_part + ((int64_t)c * 2 + which) * KK + e);
+      (which == 0 ? g_rb : g_d)[e] = acc;
+    }
+    __syncthreads();
   } else {
     node_gram2(A.rb, A.d, A.K, A.n, A.npad, g_rb, g_d);
   }
@@ -384,7 +421,15 @@ int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
   const int64_t total = (int64_t)s->K * s->npad;
-  const int grid = (int)((total + NODE_THREADS - 1) / NODE_THREADS);
+  int grid = (int)((total + NODE_THREADS - 1) / NODE_THREADS);
+  A.npc = 0;
+  A.gram_part = s->gram_part;
+  if (s->K > 1 && s->gram_part) {   // batch mapping (K <= 128: at least 2 nodes per CTA)
+    int kp = 1;
+    while (kp < s->K) kp <<= 1;
+    A.npc = NODE_THREADS / kp;
+    grid = s->npad / A.npc;
+  }
   node_tail_kernel<<<grid, NODE_THREADS, 0, st>>>(A);
   GL_LAUNCH_CHECK();
   return GL_OK;

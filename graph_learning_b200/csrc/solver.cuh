@@ -49,6 +49,7 @@ struct gl_solver {
   void *ipc_opened[GL_MAX_PEERS] = {};
   double *cta_partial = nullptr;  // [ntl][2] per-CTA residual sums of the edge pass (K == 1)
   double *node_partial = nullptr; // [node CTAs][2] per-CTA dual residual sums of the node tail (K == 1)
+  double *gram_part = nullptr;    // K > 1: [node CTAs][2][K*K] per-CTA partial node Grams (batch mapping)
   double *gprev = nullptr;        // [2][K*K]: Gram(W), Gram(D) of the previous iterate (denominators)
   double *resid = nullptr;        // [2]: rel_primal, rel_dual of the last checked iteration
   double *eig_scratch = nullptr;  // [4][2][K*K] repeated-squaring buffers

@@ -14,7 +14,7 @@ import graph_learning_b200.smooth_learning as sl  # noqa: E402
 from graph_learning_b200.synthetic import rgg_signals_filtered  # noqa: E402
 
 
-def timed(fn, reps=3):
+def timed(fn, reps=5):
     fn()
     torch.cuda.synchronize()
     ts = []
@@ -54,8 +54,12 @@ def main():
                                                                        return_info=True))
         rec[f"solve_maxit{maxit}_tol{tol:g}_ms"] = ms
         rec[f"solve_maxit{maxit}_tol{tol:g}_iters"] = info.n_iter
-    rec["solve_us_per_iteration"] = rec["solve_maxit200_tol0_ms"] * 1e3 / 200
-    rec["solve_edge_iters_per_s"] = K * E * 200 / (rec["solve_maxit200_tol0_ms"] * 1e-3)
+    if rec["solve_maxit1000_tol1e-05_iters"] == 1000:   # did not converge early: difference removes the fixed cost
+        per = (rec["solve_maxit1000_tol1e-05_ms"] - rec["solve_maxit200_tol0_ms"]) * 1e3 / 800
+    else:
+        per = rec["solve_maxit200_tol0_ms"] * 1e3 / 200
+    rec["solve_us_per_iteration"] = per
+    rec["solve_edge_iters_per_s"] = K * E / (per * 1e-6)
     print(json.dumps(rec))
 
 
