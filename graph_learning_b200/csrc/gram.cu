@@ -519,6 +519,10 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   }
 }
 
+}  // namespace gl
+#include "gram_2cta.cuh"
+namespace gl {
+
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -629,6 +633,34 @@ static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &b
   return GL_OK;
 }
 
+static int launch_gram_2cta(const GramLayout &L, unsigned char *ws, const GramArgs &base, int n_sms, cudaStream_t st) {
+  using C = Gram2Cfg;
+  EncodeTiledFn encode;
+  GL_TRY(get_encode_fn(&encode));
+  CUtensorMap map_a, map_b;
+  const cuuint64_t gdim[3] = {(cuuint64_t)L.m_pad, (cuuint64_t)L.n_pad, (cuuint64_t)C::TERMS};
+  const cuuint64_t gstride[2] = {(cuuint64_t)L.m_pad * 2, (cuuint64_t)L.n_pad * (cuuint64_t)L.m_pad * 2};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  const cuuint32_t box_a[3] = {C::BK, GR_BM, C::TERMS};
+  const cuuint32_t box_b[3] = {C::BK, C::BN / 2, C::TERMS};
+  CUresult r1 = encode(&map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_a, estride,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r2 = encode(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_b, estride,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS)
+    return fail(GL_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d)", (int)r1, (int)r2);
+  GramArgs a = base;
+  a.num_kb = (int)(L.m_pad / C::BK);
+  a.kb_per_chunk = std::max(1, a.kb_per_chunk / C::BK);
+  GL_CUDA(cudaFuncSetAttribute(gram_kernel_2cta, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+  const int clusters = std::max(1, std::min(n_sms / 2, a.n_units));
+  gram_kernel_2cta<<<2 * clusters, C::THREADS, C::SMEM_BYTES, st>>>(map_a, map_b, a);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
 }  // namespace gl
 using namespace gl;
 
@@ -646,7 +678,8 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
                                     (long long)m, (long long)ldx, n);
   if (layout != GL_LAYOUT_PACKED && layout != GL_LAYOUT_TILED) return fail(GL_E_ARG, "bad layout");
   if (terms != 2 && terms != 3) return fail(GL_E_ARG, "terms must be 2 or 3");
-  if (variant < 0 || variant > 5) return fail(GL_E_ARG, "variant must be 0..5");
+  if (variant < 0 || variant > 6) return fail(GL_E_ARG, "variant must be 0..6");
+  if (variant == 6 && terms != 3) return fail(GL_E_ARG, "the CTA-pair variant needs terms = 3");
   if (layout == GL_LAYOUT_PACKED) {
     tile_begin = 0;
     tile_end = num_tiles(n);
@@ -679,7 +712,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   // The split-accumulator variants of the 3-term form carry the exact leading slice.  With 2 terms
   // the residual slice alone cannot hold the bits the quantisation pushes into it, so the 2-term
   // form keeps plain round-to-nearest bf16 slices (still with separate accumulators).
-  const bool exact0 = variant <= 1 && terms == 3;
+  const bool exact0 = (variant <= 1 || variant == 6) && terms == 3;
   int *colmax = reinterpret_cast<int *>(ws + L.off_colmax);
   const float *Xf = (const float *)X, *rsf = (const float *)row_scale, *csf = (const float *)col_shift;
   if (exact0) {
@@ -704,7 +737,10 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   const int bn = (variant == 2 || variant == 4) ? 256 : 128;
   const int nt = tiles_per_side(n);
   std::vector<int2> units;
-  build_units(nt, bn / T, tile_begin, tile_end, units);
+  if (variant == 6)
+    build_units_2cta(nt, tile_begin, tile_end, units);
+  else
+    build_units(nt, bn / T, tile_begin, tile_end, units);
   if ((int)units.size() > L.max_units) return fail(GL_E_STATE, "unit list overflow");
   int2 *units_dev = reinterpret_cast<int2 *>(ws + L.off_units);
   // pageable source: the runtime stages it before returning, so the vector may die afterwards
@@ -725,6 +761,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   //          1 = same with 64-sample k-blocks (SWIZZLE_128B)
   //          2 / 3 = single accumulator, 256- / 128-wide units, 32-sample k-blocks
   //          4 / 5 = single accumulator, 256- / 128-wide units, 64-sample k-blocks
+  if (variant == 6) return launch_gram_2cta(L, ws, a, n_sms, st);
   if (terms == 3) {
     switch (variant) {
       case 0: return launch_gram<3, 128, 32, true>(L, ws, a, n_sms, st);

@@ -114,7 +114,9 @@ int gl_pdist_sq(const void *X_dev, int64_t m, int n, int64_t ldx, const void *ro
  *            1 = same with 64-sample k-blocks (SWIZZLE_128B);
  *            2 / 3 = one fp32 accumulator, 256- / 128-wide units, 32-sample k-blocks (faster; the
  *                tensor core's truncating accumulation leaves a bias of ~1e-5 |y|^2);
- *            4 / 5 = same with 64-sample k-blocks (4 needs terms = 2).
+ *            4 / 5 = same with 64-sample k-blocks (4 needs terms = 2);
+ *            6 = the precise scheme as a CTA pair: tcgen05.mma.cta_group::2 (M = 256) on 2-CTA clusters,
+ *                each CTA loading its own rows and half of the shared operand (terms = 3).
  * `workspace_dev` (any alignment, gl_gram_workspace_bytes(m, n, terms) bytes) receives the split,
  * transposed operand planes.  Needs an sm_100 device. */
 int64_t gl_gram_workspace_bytes(int64_t m, int n, int terms);

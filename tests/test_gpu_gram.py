@@ -53,13 +53,18 @@ def test_gram_shapes_vs_oracle(sl, m, n, method, tol):
     assert rel(z, orc.pdist_sq(x.astype(np.float64))) < tol
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6])
 @pytest.mark.parametrize("method", ["gram", "gram2"])
 def test_gram_variants_on_smooth_signals(sl, nat, smooth300, method, variant):
     """Every kernel variant (split / single accumulator, unit width 128/256, k-block 32/64 =
-    SWIZZLE_64B/128B) on signals where the Gram form cancels (smooth on the graph)."""
+    SWIZZLE_64B/128B, and the CTA-pair cta_group::2 kernel) on signals where the Gram form cancels
+    (smooth on the graph)."""
     x = smooth300.astype(np.float32)
     ref = orc.pdist_sq(x.astype(np.float64))
+    if method == "gram2" and variant == 6:
+        with pytest.raises(nat.GLError, match="terms = 3"):
+            sl.pdist_sq(x, method=method, variant=variant)
+        return
     if method == "gram" and variant == 4:
         with pytest.raises(nat.GLError, match="does not fit"):
             sl.pdist_sq(x, method=method, variant=variant)
@@ -98,7 +103,7 @@ def test_gram_strided_input(sl):
     assert rel(out.cpu().numpy(), orc.pdist_sq(view.cpu().numpy().astype(np.float64))) < TOL3
 
 
-@pytest.mark.parametrize("variant", [0, 2])
+@pytest.mark.parametrize("variant", [0, 2, 6])
 def test_gram_tiled_ranges_match_direct(sl, nat, variant):
     """Tiled output for a shard's tile range: same slots as the exact kernel, zeros in the invalid
     slots (i >= j, j >= n), nothing written outside the range."""
