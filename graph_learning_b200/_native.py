@@ -89,6 +89,11 @@ SIGNATURES = {
     "gl_knn_status": (c_int, [c_void_p, _pi, _pd, _pd, _pi, c_void_p]),
     "gl_knn_store": (c_int, [c_void_p, c_void_p, c_double, c_void_p]),
     "gl_knn_build": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
+    "gl_quadform_create": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_double, c_void_p]),
+    "gl_quadform_destroy": (c_int, [c_void_p]),
+    "gl_quadform_nnz": (c_int64, [c_void_p]),
+    "gl_quadform_apply": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p]),
     "gl_knn_logmodel_solve": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_double, c_double,
                                       c_int, c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p]),
 }

@@ -8,8 +8,11 @@ Here the distances come from ``gl_pdist_sq`` with ``row_scale = resp[:, k]`` and
 solve from the fused CUDA iteration, and the Laplacians from ``gl_laplacian_from_packed``.
 
 The EM driver is scikit-learn's private ``BaseMixture`` exactly as in the reference (:88); the
-hooks accept the ``xp=`` keyword scikit-learn >= 1.8 passes.  The E-step (:238-279) is host NumPy
-here as in the reference -- it is a "next" row, not the hot path.
+hooks accept the ``xp=`` keyword scikit-learn >= 1.8 passes.  The E-step (:238-279; SURVEY.md section
+8(f) N1) keeps the reference's ``eigh`` (LAPACK for small n, cuSOLVER through torch otherwise) and
+replaces the (m, n) x (n, n-1) projection + weighted square sum by the sparse quadratic-form kernel
+(``assign.py``): sum_{j>=1} (lam_j + r)(v_j . y)^2 = y^T (L + r I) y - (lam_0 + r)(v_0 . y)^2.  The signal
+matrix is uploaded once per ``fit`` and reused by every E- and M-step.
 """
 from __future__ import annotations
 
@@ -22,6 +25,8 @@ from sklearn.mixture._base import BaseMixture
 from ..operators import laplacian_squareform_vec, square_to_vec
 from ..smooth_learning import (_theta_packed, _to_device, _torch_dtype, get_theta,
                                gsp_learn_graph_log_degrees, pdist_sq)
+
+EIGH_DEVICE_MIN_NODES = 256   # below this LAPACK on the host is faster than the cuSOLVER launch chain
 
 
 def weighted_sq_dists(x, resp, means, dtype=None) -> torch.Tensor:
@@ -44,6 +49,7 @@ def _estimate_gauss_laplacian_parameters(
     blocks=None,
     laplacians=None,
     dtype="float64",
+    return_device: bool = False,
 ):
     """Weights, means and Laplacians of every component given the associations.
 
@@ -52,8 +58,10 @@ def _estimate_gauss_laplacian_parameters(
     """
     if (theta is None) == (avg_degree is None):
         raise ValueError("Exactly one of theta and avg_degree should be provided")
-    x = np.asarray(x, dtype=np.float64)
     resp = np.asarray(resp, dtype=np.float64)
+    x_dev = x if isinstance(x, torch.Tensor) else None      # already resident (GLMM keeps it for the whole fit)
+    if x_dev is None:
+        x = np.asarray(x, dtype=np.float64)
     _n_samples, n_nodes = x.shape
     n_components = resp.shape[1]
 
@@ -63,7 +71,11 @@ def _estimate_gauss_laplacian_parameters(
         edge_init = -square_to_vec(np.asarray(laplacians)).T
 
     weights = resp.sum(axis=0)                       # (K,)
-    means = resp.T @ x / weights[:, None]            # (K, n)                      :62
+    if x_dev is None:
+        means = resp.T @ x / weights[:, None]        # (K, n)                      :62
+    else:
+        rt = _to_device(resp, x_dev.dtype).t()
+        means = ((rt @ x_dev).double().cpu().numpy()) / weights[:, None]
     weights = weights / n_nodes                      #                             :63
 
     sq_dist = weighted_sq_dists(x, resp, means, dtype)   # (K, E) on the device    :67-68
@@ -88,7 +100,10 @@ def _estimate_gauss_laplacian_parameters(
     edge_weights = gsp_learn_graph_log_degrees(sq_dist * theta_inv, alpha=1, beta=1, edge_init=edge_init,
                                                dtype=dtype)                          # :79
     lapl = laplacian_squareform_vec(delta * edge_weights)                           # :83
-    return weights, means, lapl.cpu().numpy().astype(np.float64)
+    lapl_host = lapl.cpu().numpy().astype(np.float64)
+    if return_device:
+        return weights, means, lapl_host, lapl
+    return weights, means, lapl_host
 
 
 class GLMM(BaseMixture):
@@ -136,13 +151,17 @@ class GLMM(BaseMixture):
         pass
 
     def _mstep(self, x, resp):
-        return _estimate_gauss_laplacian_parameters(
+        weights, means, lapl, lapl_dev = _estimate_gauss_laplacian_parameters(
             x, resp, self.delta, theta=self.theta, avg_degree=self.avg_degree, blocks=self.blocks,
             laplacians=self.laplacians_ if self._propagate_laplacians else None, dtype=self.dtype,
+            return_device=True,
         )
+        self._lap_cache = (lapl, lapl_dev)      # device twin of the array about to become laplacians_
+        return weights, means, lapl
 
     def _initialize(self, x, resp, xp=None):
         _n_samples, self.n_nodes_ = x.shape
+        x = self._resident(x)
         init = self.laplacian_init
         if init is None:
             self.laplacians_ = None
@@ -164,24 +183,55 @@ class GLMM(BaseMixture):
         self.weights_, self.means_, self.laplacians_ = self._mstep(x, resp)
 
     def _m_step(self, x, log_resp, xp=None):
-        self.weights_, self.means_, self.laplacians_ = self._mstep(x, np.exp(log_resp))
+        self.weights_, self.means_, self.laplacians_ = self._mstep(self._resident(x), np.exp(log_resp))
         self.weights_ /= self.weights_.sum()
+
+    def _resident(self, x) -> torch.Tensor:
+        """Device copy of the signal matrix, uploaded once per ``fit`` (the cache holds a reference to
+        the host array, so the identity test cannot be fooled by a recycled address; do not mutate
+        ``x`` in place between calls)."""
+        if isinstance(x, torch.Tensor):
+            return x
+        cache = getattr(self, "_x_cache", None)
+        if cache is not None and cache[0] is x:
+            return cache[1]
+        xd = _to_device(x, _torch_dtype(self.dtype))
+        if getattr(self, "_fitting", False):
+            self._x_cache = (x, xd)
+        return xd
+
+    def fit_predict(self, X, y=None):
+        self._fitting = True
+        try:
+            return super().fit_predict(X, y)
+        finally:
+            self._fitting = False
+            self._x_cache = None
+            self._lap_cache = None
 
     def _estimate_log_prob(self, x, xp=None):
         """Assignment log-probabilities under N(mean_k, pinv(L_k + regul)) restricted to the
         non-constant eigenvectors (reference :238-279)."""
-        x = np.asarray(x)
-        eigval, eigvec = np.linalg.eigh(self.laplacians_)
-        eigval = eigval + self.regul
-        log_prob = np.empty((x.shape[0], self.n_components))
-        for k in range(self.n_components):
-            proj = (x - self.means_[k]) @ eigvec[k, :, 1:]
-            log_prob[:, k] = (
-                -(self.n_nodes_ - 1) * np.log(2 * np.pi)
-                + np.log(np.prod(eigval[k, 1:]))
-                - np.sum(proj * proj * eigval[k, 1:], axis=-1)
-            ) / 2
-        return log_prob
+        from .assign import QuadForm
+        xd = self._resident(x)
+        lap = np.asarray(self.laplacians_, dtype=np.float64)
+        cache = getattr(self, "_lap_cache", None)
+        lap_dev = cache[1] if cache is not None and cache[0] is self.laplacians_ else _to_device(lap, xd.dtype)
+        if self.n_nodes_ < EIGH_DEVICE_MIN_NODES:
+            eigval, eigvec = np.linalg.eigh(lap)                                     # :253
+            first = np.ascontiguousarray(eigvec[:, :, 0])
+        else:
+            ev, evec = torch.linalg.eigh(lap_dev.double())
+            eigval, first = ev.cpu().numpy(), evec[:, :, 0].contiguous()
+        eigval = eigval + self.regul                                                 # :254
+        with QuadForm(lap_dev, diag_add=self.regul, dtype=xd.dtype) as qf:
+            quad, dot = qf.apply(xd, shift=self.means_, vectors=first)
+        lam0 = torch.as_tensor(eigval[:, 0], device=quad.device, dtype=torch.float64)
+        data = quad.double() - lam0[None, :] * dot.double() ** 2                      # :267-274
+        with np.errstate(over="ignore", divide="ignore"):
+            logdet = np.log(np.prod(eigval[:, 1:], axis=1))                          # :272 (overflows like the reference)
+        const = -(self.n_nodes_ - 1) * np.log(2 * np.pi)
+        return (const + logdet[None, :] - data.cpu().numpy()) / 2
 
     def _estimate_log_weights(self, xp=None):
         return np.log(self.weights_)

@@ -3,8 +3,9 @@
 The graph-update step (reference ``KGraphs._single_fit``, :93-108) is a batched caller of the
 LogModel hot path: per-cluster squared distances (:96), per-cluster
 theta (:103), ONE batched (K, E) solve (:102-106) and the Laplacians (:108), all on the device.
-The assignment step (:112-113, ``einsum('ni,kij,nj->nk')``) is K GEMMs with a row-dot epilogue in
-torch -- a "next" row, not the hot path.
+The assignment step (:87-88, :112-113: ``einsum('ni,kij,nj->nk')`` + ``argmin``; SURVEY.md section
+8(f) N2) runs as the sparse quadratic-form kernel of ``assign.py`` / ``csrc/quadform.cu``; the signals,
+labels and Laplacians stay on the device for the whole outer loop.
 """
 from __future__ import annotations
 
@@ -18,6 +19,7 @@ from sklearn.utils import check_random_state
 
 from ..operators import laplacian_squareform_vec
 from ..smooth_learning import _theta_packed, _to_device, _torch_dtype, gsp_learn_graph_log_degrees, pdist_sq
+from .assign import QuadForm
 from .glmm import _estimate_gauss_laplacian_parameters
 from .utils import init_labels, one_hot
 
@@ -58,33 +60,39 @@ class KGraphs(BaseEstimator, ClusterMixin):
 
     def _smoothness(self, x) -> np.ndarray:
         """x_n^T L_k x_n for every sample and cluster, shape (n_samples, n_clusters) (:87-88)."""
-        xd = _to_device(x, torch.float64)
-        lap = _to_device(self.laplacians_, torch.float64)
-        out = torch.stack([((xd @ lap[k]) * xd).sum(dim=1) for k in range(lap.shape[0])], dim=1)
-        return out.cpu().numpy()
+        with QuadForm(self.laplacians_, dtype=torch.float64) as qf:
+            return qf.apply(x).cpu().numpy()
 
-    def _graph_step(self, x_dev: torch.Tensor) -> np.ndarray:
-        """Laplacians of all clusters from the current labels (:96-108)."""
+    def _graph_step_dev(self, x_dev: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Laplacians (K, n, n) of all clusters from the current labels, on the device (:96-108)."""
         n_nodes = x_dev.shape[1]
-        labels = torch.as_tensor(self.labels_, device=x_dev.device)
         sq_dist = torch.stack([pdist_sq(x_dev[labels == k], dtype=x_dev.dtype) for k in range(self.n_clusters)])
         theta = torch.tensor([[_theta_packed(sq_dist[k], n_nodes, self.avg_degree)] for k in range(self.n_clusters)],
                              dtype=sq_dist.dtype, device=sq_dist.device)
         edge_weights = self.delta * gsp_learn_graph_log_degrees(sq_dist * theta, alpha=1, beta=1, dtype=self.dtype)
-        return laplacian_squareform_vec(edge_weights).cpu().numpy().astype(np.float64)
+        return laplacian_squareform_vec(edge_weights)
+
+    def _graph_step(self, x_dev: torch.Tensor) -> np.ndarray:
+        labels = torch.as_tensor(self.labels_, device=x_dev.device)
+        return self._graph_step_dev(x_dev, labels).cpu().numpy().astype(np.float64)
 
     def _single_fit(self, x, _y=None) -> None:
         self._init_parameters(x)
         x_dev = _to_device(x, _torch_dtype(self.dtype))
+        labels_dev = torch.as_tensor(np.asarray(self.labels_), device=x_dev.device).to(torch.int32)
+        lap_dev = None
         for _i in range(self.max_iter):
-            self.laplacians_ = self._graph_step(x_dev)
-            smoothness = self._smoothness(x)
-            labels = np.argmin(smoothness, axis=1)
-            self.score_ = np.sum(smoothness[np.arange(len(labels)), labels])
-            if np.allclose(labels, self.labels_):
+            lap_dev = self._graph_step_dev(x_dev, labels_dev)
+            with QuadForm(lap_dev, dtype=x_dev.dtype) as qf:
+                smooth, new_labels = qf.apply(x_dev, labels=True)          # :112-113, argmin fused
+            self.score_ = float(smooth.gather(1, new_labels.long()[:, None]).sum())
+            if torch.equal(new_labels, labels_dev):
                 self.converged_ = True
-                return
-            self.labels_ = labels
+                break
+            labels_dev = new_labels
+        self.labels_ = labels_dev.cpu().numpy().astype(np.int64)
+        if lap_dev is not None:
+            self.laplacians_ = lap_dev.cpu().numpy().astype(np.float64)
 
     def fit_predict(self, x, _y=None):
         best_score, best_params = np.inf, {}
@@ -145,18 +153,17 @@ class KGraphsV2(KGraphs):
         self.score_ = np.inf
 
     def _centered_smoothness(self, x) -> np.ndarray:
-        xd = _to_device(x, torch.float64)
-        lap = _to_device(self.laplacians_, torch.float64)
-        mu = _to_device(self.means_, torch.float64)
-        out = torch.stack([(((xd - mu[k]) @ lap[k]) * (xd - mu[k])).sum(dim=1) for k in range(lap.shape[0])], dim=1)
-        return out.cpu().numpy()
+        with QuadForm(self.laplacians_, dtype=torch.float64) as qf:
+            return qf.apply(x, shift=self.means_).cpu().numpy()
 
     def _single_fit(self, x, _y=None) -> None:
         self._init_parameters(x)
+        x_dev = _to_device(x, torch.float64)
         for _i in range(self.max_iter):
-            smoothness = self._smoothness(x)
-            labels = np.argmin(smoothness, axis=1)
-            self.score_ = np.sum(smoothness[np.arange(len(labels)), labels])
+            with QuadForm(self.laplacians_, dtype=torch.float64) as qf:
+                smooth, lab = qf.apply(x_dev, labels=True)                  # uncentred, as the reference (:214)
+            self.score_ = float(smooth.gather(1, lab.long()[:, None]).sum())
+            labels = lab.cpu().numpy().astype(np.int64)
             _, self.means_, self.laplacians_ = self._mstep(x, labels)
             if np.allclose(labels, self.labels_):
                 self.converged_ = True

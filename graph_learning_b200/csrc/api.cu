@@ -242,9 +242,7 @@ int gl_solver_begin(gl_solver *s, double alpha, double beta, double step_size, i
   // other one may still be read by a peer -- never touch them from the host side
   if (s->world <= 1) GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
   GL_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
-  if (s->K > 1 && s->ntl) GL_CUDA(cudaMemsetAsync(s->r, 0, (size_t)s->K * s->gstride * s->esz, st));
-  GL_TRY(launch_edge_init(s, st));   // local partial of S w0 (and ||w0||^2 for K == 1)
-  GL_TRY(launch_gram_edges(s, st));  // K > 1: Gram(W0)
+  GL_TRY(launch_edge_init(s, st));   // local partial of S w0 and the squared norm of every graph's w0
   return GL_OK;
 }
 
@@ -258,13 +256,15 @@ int gl_solver_begin_finish(gl_solver *s, void *stream) {
 int gl_solver_edge_pass(gl_solver *s, void *stream) {
   if (!s || !s->begun) return fail(GL_E_STATE, "gl_solver_begin/begin_finish must be called first");
   cudaStream_t st = as_stream(stream);
-  GL_TRY(launch_edge_pass(s, st));
-  return launch_gram_edges(s, st);
+  return launch_edge_pass(s, st);
 }
 
 int gl_solver_node_tail(gl_solver *s, void *stream) {
   if (!s || !s->begun) return fail(GL_E_STATE, "gl_solver_begin/begin_finish must be called first");
-  return launch_node_tail(s, false, as_stream(stream));
+  cudaStream_t st = as_stream(stream);
+  GL_TRY(launch_node_tail(s, false, st));
+  GL_TRY(launch_gram_edges(s, st));    // K > 1: no-ops unless the node tail asked for the exact norms
+  return launch_batch_decide(s, st);
 }
 
 void *gl_solver_comm_ptr(gl_solver *s, int64_t *n_bytes) {
@@ -373,7 +373,7 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   RUN_CUDA(cudaEventCreateWithFlags(&evs[0], cudaEventDisableTiming));
   RUN_CUDA(cudaEventCreateWithFlags(&evs[1], cudaEventDisableTiming));
 
-  const int per_iter = (s->ntl ? 1 : 0) + ((s->K > 1 && s->ntl) ? 1 : 0) + 1;
+  const int per_iter = (s->ntl ? 1 : 0) + ((s->K > 1 && s->ntl) ? 2 : 0) + 1;
   if (!persistent && (!s->graph_exec || s->graph_iters != poll_every)) {
     if (s->graph_exec) {
       cudaGraphExecDestroy(s->graph_exec);
@@ -384,8 +384,9 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
     RUN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
     for (int i = 0; i < poll_every && rc == GL_OK; ++i) {
       rc = launch_edge_pass(s, st);
-      if (rc == GL_OK) rc = launch_gram_edges(s, st);
       if (rc == GL_OK) rc = launch_node_tail(s, false, st);
+      if (rc == GL_OK) rc = launch_gram_edges(s, st);
+      if (rc == GL_OK) rc = launch_batch_decide(s, st);
     }
     cudaError_t ce = cudaStreamEndCapture(st, &graph);
     g_launches.store(before);  // capture records, it does not launch

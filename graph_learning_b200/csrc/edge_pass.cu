@@ -36,7 +36,17 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) edge_pas
   double *const g_sum = xb + 2 * (int64_t)gridDim.y * A.npad;
   double r2 = 0.0, w2 = 0.0;
   edge_cta_tile<F, BATCH, false>(A, sm, t, k, g_sp, g_sw, r2, w2);
-  if (BATCH) return;
+  if (BATCH) {
+    // batch mode: only the DIAGONALS of Gram(q - y) and Gram(w') are kept up every iteration (the
+    // graph's own squared norms); the node tail bounds the spectral-norm stop rule with them and asks
+    // for the full K x K Grams (gram_edges_kernel) only when the bound cannot rule the stop out
+    if (tid == 0) {
+      const int K = gridDim.y;
+      atomicAdd(g_sum + (int64_t)k * K + k, r2);
+      atomicAdd(g_sum + (int64_t)K * K + (int64_t)k * K + k, w2);
+    }
+    return;
+  }
 
   // ---- residual sums: fixed-order two-stage reduction (deterministic) -------------------------
   if (tid == 0) {
@@ -115,8 +125,8 @@ __global__ void __launch_bounds__(EDGE_THREADS) edge_init_kernel(const F *w, int
   if (lane == 0) atomicAdd(&s_sq, sq);
   __syncthreads();
   if (tid < T && J * T + tid < n) atomicAdd(sw + (int64_t)k * npad + J * T + tid, s_col[tid]);
-  // Gram diagonal only here; the off-diagonal entries of Gram(W0) come from gram_edges (K > 1)
-  if (tid == 0 && K == 1) atomicAdd(gw, s_sq);
+  // Gram diagonal only: the denominators of the cheap stop bound (K > 1) / of the stop rule (K == 1)
+  if (tid == 0) atomicAdd(gw + (int64_t)k * K + k, s_sq);
 }
 
 template <typename F> static int edge_pass_t(gl_solver *s, cudaStream_t st) {

@@ -152,7 +152,7 @@ template <typename F> struct EdgeSmem {
 // One CTA sweeps tile `t` of graph `k`: loads, update, stores, and the tile's 512 float64 atomics
 // into the degree accumulators g_sp / g_sw.  COHERENT_AB: read a/b through L2 (persistent kernel:
 // they were rewritten by other SMs during this launch).  On return thread 0 holds the tile's
-// residual sums in (r2, w2) (BATCH == false).  Ends with a __syncthreads-safe state for reuse.
+// residual sums in (r2, w2).  Ends with a __syncthreads-safe state for reuse.
 template <typename F, bool BATCH, bool COHERENT_AB>
 __device__ __forceinline__ void edge_cta_tile(const EdgeArgs<F> &A, EdgeSmem<F> &sm, int t, int k,
                                               double *g_sp, double *g_sw, double &r2, double &w2) {
@@ -206,7 +206,7 @@ __device__ __forceinline__ void edge_cta_tile(const EdgeArgs<F> &A, EdgeSmem<F> 
     *reinterpret_cast<V *>(&sm.col[wp][0][col]) = vec_pack<F>(csp + v * VEC);
     *reinterpret_cast<V *>(&sm.col[wp][1][col]) = vec_pack<F>(csw + v * VEC);
   }
-  if (!BATCH) {
+  {
     const double rr = warp_sum((double)res), ww = warp_sum((double)wsq);
     if (lane == 0) {
       sm.red[wp][0] = rr;
@@ -222,7 +222,7 @@ __device__ __forceinline__ void edge_cta_tile(const EdgeArgs<F> &A, EdgeSmem<F> 
     const int gj = J * T + col;
     if (gj < A.n) atomicAdd((qty ? g_sw : g_sp) + (int64_t)k * A.npad + gj, acc);
   }
-  if (!BATCH && tid == 0) {
+  if (tid == 0) {
     r2 = w2 = 0.0;
 #pragma unroll
     for (int q = 0; q < EDGE_THREADS / 32; ++q) {

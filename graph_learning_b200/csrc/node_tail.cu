@@ -362,9 +362,30 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   }
 
   const int it = A.flags[FLAG_IT];
+  // K > 1: the primal residual ratio needs the spectral norms of the (E, K) operands, i.e. full K x K
+  // Grams over the edge axis.  Only their diagonals are maintained every iteration (edge pass); with
+  //   sigma_max(R)^2 >= max_k ||r_k||^2   and   sigma_max(W)^2 <= sum_k ||w_k||^2
+  // rel_primal >= s_lo, so the stop rule is RULED OUT exactly whenever s_lo >= tol (or the dual
+  // ratio, exact here, is >= tol).  Otherwise FLAG_NEED hands the decision to gram_edges_kernel +
+  // batch_decide_kernel, which evaluate the exact norms: the decisions are those of the full rule.
+  const bool lazy = A.K > 1;
+  __shared__ double s_lo;
+  __shared__ int s_nan;
   if (!A.init && it >= 1) {
-    const double *G[4] = {g_r, A.gprev, g_rb, A.gprev + KK};
+    const double *G[4] = {lazy ? g_rb : g_r, lazy ? A.gprev + KK : A.gprev, g_rb, A.gprev + KK};
     lambda_max4(G, A.K, A.eig, s_lam);
+    if (lazy && tid == 0) {
+      double mx = 0.0, tr = 0.0;
+      int bad = 0;
+      for (int k = 0; k < A.K; ++k) {
+        const double v = __ldcg(g_r + k * A.K + k), u = A.gprev[k * A.K + k];
+        bad |= (v != v) || (u != u);
+        mx = v > mx ? v : mx;
+        tr += u;
+      }
+      s_lo = sqrt(mx) / sqrt(tr);
+      s_nan = bad || (s_lo != s_lo);
+    }
   }
   __syncthreads();
   // rotate the denominators and clear the exchange slots
@@ -383,23 +404,79 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
     if (A.init) {
       A.flags[FLAG_IT] = 0;
       A.flags[FLAG_CONVERGED] = 0;
+      A.flags[FLAG_NEED] = 0;
       A.flags[FLAG_DONE] = (A.maxit <= 0);
       A.resid[0] = CUDART_INF;
       A.resid[1] = CUDART_INF;
     } else {
-      bool conv = false;
+      bool conv = false, need = false;
       if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
-        const double rp = sqrt(s_lam[0]) / sqrt(s_lam[1]);
         const double rd = sqrt(s_lam[2]) / sqrt(s_lam[3]);
-        A.resid[0] = rp;
         A.resid[1] = rd;
-        conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
+        if (!lazy) {
+          const double rp = sqrt(s_lam[0]) / sqrt(s_lam[1]);
+          A.resid[0] = rp;
+          conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
+        } else {
+          // 1e-3 slack covers the rounding of the float32 partial sums behind the bound
+          const bool ruled_out = !(rd < A.tol) || (!s_nan && s_lo * (1.0 - 1e-3) >= A.tol);
+          need = !ruled_out || it + 1 >= A.maxit;   // the last iteration reports exact residuals
+          if (!need) A.resid[0] = s_lo;              // a lower bound; exact on the deciding iterations
+        }
       }
       A.flags[FLAG_IT] = it + 1;
-      if (conv) A.flags[FLAG_CONVERGED] = 1;
-      if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
+      if (need) {
+        A.flags[FLAG_NEED] = 1;
+      } else {
+        if (conv) A.flags[FLAG_CONVERGED] = 1;
+        if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
+      }
     }
   }
+}
+
+// K > 1, after gram_edges_kernel ran for real (FLAG_NEED): exact rel_primal from the spectral norms of
+// Gram(q - y) and Gram(w) of the previous iterate, then the reference's stop rule (:158-166).
+struct DecideArgs {
+  double *g_r, *g_w, *resid, *eig;
+  int *flags;
+  int K, maxit;
+  double tol;
+};
+
+__global__ void __launch_bounds__(NODE_THREADS) batch_decide_kernel(const DecideArgs A) {
+  __shared__ double s_lam[4];
+  if (!*reinterpret_cast<volatile int *>(A.flags + FLAG_NEED)) return;
+  const int tid = threadIdx.x, KK = A.K * A.K;
+  const double *G[4] = {A.g_r, A.g_w, A.g_r, A.g_w};
+  lambda_max4(G, A.K, A.eig, s_lam);
+  __syncthreads();
+  for (int e = tid; e < 2 * KK; e += NODE_THREADS) A.g_r[e] = 0.0;   // g_w follows g_r: slots for the next pass
+  if (tid == 0) {
+    const double rp = sqrt(s_lam[0]) / sqrt(s_lam[1]), rd = A.resid[1];
+    A.resid[0] = rp;
+    const bool conv = (rp < A.tol) && (rd < A.tol);
+    A.flags[FLAG_NEED] = 0;
+    if (conv) A.flags[FLAG_CONVERGED] = 1;
+    if (conv || A.flags[FLAG_IT] >= A.maxit) A.flags[FLAG_DONE] = 1;
+  }
+}
+
+int launch_batch_decide(gl_solver *s, cudaStream_t st) {
+  if (s->K == 1 || s->ntl == 0) return GL_OK;
+  const int64_t total = (int64_t)s->K * s->npad;
+  DecideArgs A;
+  A.g_r = s->xch + 2 * total;
+  A.g_w = A.g_r + (int64_t)s->K * s->K;
+  A.resid = s->resid;
+  A.eig = s->eig_scratch;
+  A.flags = s->flags;
+  A.K = s->K;
+  A.maxit = s->maxit;
+  A.tol = s->tol;
+  batch_decide_kernel<<<1, NODE_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
 }
 
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
@@ -435,7 +512,8 @@ int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
   return GL_OK;
 }
 
-// ---- batch mode: Gram matrices of R = Q - Y and of W' over the local edge shard --------------
+// ---- batch mode: Gram matrices of R = Q - Y and of the previous iterate W = W' - R over the local edge
+// shard, only on the iterations whose stop decision needs them (FLAG_NEED, see node_tail_kernel).
 // 8 x 8 register-blocked; grid = (chunks, graph-block pairs kb <= lb, {R, W}).
 constexpr int GRAM_THREADS = 128;
 constexpr int GB = 8;
@@ -443,9 +521,8 @@ constexpr int GB = 8;
 template <typename F>
 __global__ void __launch_bounds__(GRAM_THREADS) gram_edges_kernel(const F *r, const F *w, int64_t gstride,
                                                                    int64_t len, int K, double *g_r,
-                                                                   double *g_w, const int *flags,
-                                                                   int check_done) {
-  if (check_done && *reinterpret_cast<const volatile int *>(flags + FLAG_DONE)) return;
+                                                                   double *g_w, const int *flags) {
+  if (!*reinterpret_cast<const volatile int *>(flags + FLAG_NEED)) return;
   __shared__ double s_acc[GRAM_THREADS / 32][GB * GB];
   const int nb = (K + GB - 1) / GB;
   // decode pair index blockIdx.y -> (kb <= lb)
@@ -455,8 +532,8 @@ __global__ void __launch_bounds__(GRAM_THREADS) gram_edges_kernel(const F *r, co
     ++kb;
   }
   const int lb = kb + rem;
-  const F *x = blockIdx.z == 0 ? r : w;
-  double *g = blockIdx.z == 0 ? g_r : g_w;
+  const bool prev = blockIdx.z == 1;   // W of the previous iterate = w' - (q - y)   (:163)
+  double *g = prev ? g_w : g_r;
   double acc[GB][GB];
 #pragma unroll
   for (int i = 0; i < GB; ++i)
@@ -469,8 +546,11 @@ __global__ void __launch_bounds__(GRAM_THREADS) gram_edges_kernel(const F *r, co
 #pragma unroll
     for (int i = 0; i < GB; ++i) {
       const int k = kb * GB + i, l = lb * GB + i;
-      xa[i] = k < K ? (double)x[(int64_t)k * gstride + e] : 0.0;
-      xb[i] = l < K ? (double)x[(int64_t)l * gstride + e] : 0.0;
+      xa[i] = xb[i] = 0.0;
+      if (k < K) xa[i] = prev ? (double)w[(int64_t)k * gstride + e] - (double)r[(int64_t)k * gstride + e]
+                              : (double)r[(int64_t)k * gstride + e];
+      if (l < K) xb[i] = prev ? (double)w[(int64_t)l * gstride + e] - (double)r[(int64_t)l * gstride + e]
+                              : (double)r[(int64_t)l * gstride + e];
     }
 #pragma unroll
     for (int i = 0; i < GB; ++i)
@@ -513,11 +593,11 @@ int launch_gram_edges(gl_solver *s, cudaStream_t st) {
   if (s->dtype == GL_F32)
     gram_edges_kernel<float><<<grid, GRAM_THREADS, 0, st>>>(static_cast<const float *>(s->r),
                                                            static_cast<const float *>(s->w), s->gstride,
-                                                           len, s->K, g_r, g_w, s->flags, s->begun ? 1 : 0);
+                                                           len, s->K, g_r, g_w, s->flags);
   else
     gram_edges_kernel<double><<<grid, GRAM_THREADS, 0, st>>>(static_cast<const double *>(s->r),
                                                             static_cast<const double *>(s->w), s->gstride,
-                                                            len, s->K, g_r, g_w, s->flags, s->begun ? 1 : 0);
+                                                            len, s->K, g_r, g_w, s->flags);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }

@@ -1,0 +1,316 @@
+// quadform.cu -- N2 / N1: the assignment step of the batched callers.
+//
+//   k-Graphs   (reference kgraphs.py:87-88, :112-113): smoothness[s, k] = x_s^T L_k x_s, labels = argmin_k
+//   GLMM E-step (reference glmm.py:253-274): sum_{j>=1} (lambda_j + regul) (v_j^T y)^2 with y = x_s - mu_k,
+//              which equals y^T (L_k + regul I) y - (lambda_0 + regul) (v_0^T y)^2 (orthonormal v_j).
+//
+// The reference contracts the samples against DENSE (n, n) Laplacians (2 m n^2 K flops).  The learned
+// Laplacians are sparse (a few edges per node survive the solver's threshold), so the quadratic form
+// is evaluated over the non-zero entries only: q = sum_i A_ii y_i^2 + sum_{i<j} (A_ij + A_ji) y_i y_j.
+// That identity holds for ANY square matrix, so the kernel does not assume a Laplacian.
+//
+//   gl_quadform_create : compacts K dense matrices into entry lists (i, j, value), deterministic order
+//                        (row-major; warp-ballot ordered compaction, one cub scan).
+//   gl_quadform_apply  : one CTA per block of S samples.  The block's signals are staged transposed in
+//                        shared memory (node-major, padded: lane = sample reads are conflict-free), each
+//                        warp walks a strided share of the entry list (entry loads are warp-uniform
+//                        broadcasts), partial sums are combined across warps in a fixed order, and the
+//                        argmin over k is fused into the tail.  X is read exactly once: the kernel is
+//                        bound by the shared-memory gathers, 2 per entry per 32 samples.
+#include <cub/device/device_scan.cuh>
+
+#include "common.cuh"
+
+struct gl_quadform {
+  int K, n, dtype;
+  int64_t nnz;
+  int32_t *rowoff;   // (K*n + 1) entry offsets; graph k owns [rowoff[k*n], rowoff[(k+1)*n])
+  int2 *idx;         // (nnz) node pairs, i <= j
+  void *val;         // (nnz) values of dtype
+};
+
+namespace gl {
+
+constexpr int QF_THREADS = 512;
+constexpr int QF_WARPS = QF_THREADS / 32;
+constexpr int QF_UNROLL = 4;
+constexpr int QF_STAGE = 8;                   // row loads in flight per lane while staging
+constexpr size_t QF_SMEM_CAP = 200 * 1024;   // one CTA per SM
+constexpr size_t QF_SMEM_PAIR = 100 * 1024;  // two CTAs per SM: one stages while the other computes
+
+// ---- compaction -------------------------------------------------------------------------------------
+// one warp per (k, i) row: 1 (the diagonal, always kept) + #{j > i : A_ij + A_ji != 0}
+template <typename F>
+__global__ void qf_count_kernel(const F *__restrict__ A, int K, int n, int32_t *__restrict__ cnt) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= K * n) return;
+  const int k = row / n, i = row % n;
+  const F *Ak = A + (size_t)k * n * n;
+  int c = 0;
+  for (int j = i + 1 + lane; j < n; j += 32) c += (Ak[(size_t)i * n + j] + Ak[(size_t)j * n + i]) != F(0);
+  c = warp_sum(c);
+  if (lane == 0) cnt[row] = c + 1;
+}
+
+template <typename F>
+__global__ void qf_fill_kernel(const F *__restrict__ A, int K, int n, F diag_add, const int32_t *__restrict__ rowoff,
+                               int2 *__restrict__ idx, F *__restrict__ val) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= K * n) return;
+  const int k = row / n, i = row % n;
+  const F *Ak = A + (size_t)k * n * n;
+  int pos = rowoff[row];
+  if (lane == 0) {
+    idx[pos] = make_int2(i, i);
+    val[pos] = Ak[(size_t)i * n + i] + diag_add;
+  }
+  ++pos;
+  for (int j0 = i + 1; j0 < n; j0 += 32) {
+    const int j = j0 + lane;
+    F v = F(0);
+    if (j < n) v = Ak[(size_t)i * n + j] + Ak[(size_t)j * n + i];
+    const unsigned keep = __ballot_sync(0xffffffffu, v != F(0));
+    if (v != F(0)) {
+      const int p = pos + __popc(keep & ((1u << lane) - 1u));
+      idx[p] = make_int2(i, j);
+      val[p] = v;
+    }
+    pos += __popc(keep);
+  }
+}
+
+// ---- evaluation ---------------------------------------------------------------------------------------
+struct QfArgs {
+  const void *X;
+  int64_t m, ldx;
+  int n, K;
+  const int32_t *rowoff;
+  const int2 *idx;
+  const void *val;
+  const void *shift;   // (K, n) or null
+  const void *U;       // (K, n) or null
+  void *Q;             // (m, K)
+  void *D;             // (m, K) or null
+  int32_t *labels;     // (m) or null
+};
+
+// S samples per CTA; a warp holds R = 32 / S entry sub-slots of S samples each.
+template <typename F, int S, bool SHIFT>
+__global__ void __launch_bounds__(QF_THREADS, 2) quadform_kernel(QfArgs a) {
+  constexpr int R = 32 / S;
+  constexpr int SP = S + 1;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  F *xs = reinterpret_cast<F *>(smem_raw);                 // [n][SP]
+  F *mus = xs + (size_t)a.n * SP;                          // [n]
+  F *us = mus + a.n;                                       // [n]
+  double *red = reinterpret_cast<double *>(us + a.n + (a.n & 1));   // [2][QF_WARPS * R][S]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int s = lane % S, sub = lane / S;
+  const int n = a.n, K = a.K;
+  const int64_t s0 = (int64_t)blockIdx.x * S;
+  const F *X = static_cast<const F *>(a.X);
+  const F *val = static_cast<const F *>(a.val);
+
+  // staging: a warp takes whole sample rows, QF_STAGE coalesced 128-byte loads in flight per lane;
+  // the transposed stores have stride SP = S + 1 words (odd): conflict-free
+  for (int r = warp; r < S; r += QF_WARPS) {
+    const int64_t gs = s0 + r;
+    if (gs < a.m) {
+      const F *row = X + gs * a.ldx;
+      int i = lane;
+      for (; i + (QF_STAGE - 1) * 32 < n; i += QF_STAGE * 32) {
+        F v[QF_STAGE];
+#pragma unroll
+        for (int u = 0; u < QF_STAGE; ++u) v[u] = __ldcs(row + i + 32 * u);
+#pragma unroll
+        for (int u = 0; u < QF_STAGE; ++u) xs[(size_t)(i + 32 * u) * SP + r] = v[u];
+      }
+      for (; i < n; i += 32) xs[(size_t)i * SP + r] = __ldcs(row + i);
+    } else {
+      for (int i = lane; i < n; i += 32) xs[(size_t)i * SP + r] = F(0);
+    }
+  }
+  const bool dots = a.U != nullptr;
+
+  double best = 0.0;
+  int best_k = 0;
+  const int slot = warp * R + sub, nslots = QF_WARPS * R;
+  for (int k = 0; k < K; ++k) {
+    __syncthreads();   // xs ready (k = 0); previous graph's mus / us / red consumed
+    if (SHIFT) {
+      const F *mu = static_cast<const F *>(a.shift) + (size_t)k * n;
+      for (int i = tid; i < n; i += QF_THREADS) mus[i] = mu[i];
+    }
+    if (dots) {
+      const F *u = static_cast<const F *>(a.U) + (size_t)k * n;
+      for (int i = tid; i < n; i += QF_THREADS) us[i] = u[i];
+    }
+    __syncthreads();
+    const int e0 = a.rowoff[(size_t)k * n], e1 = a.rowoff[(size_t)(k + 1) * n];
+    F acc[QF_UNROLL];
+#pragma unroll
+    for (int u = 0; u < QF_UNROLL; ++u) acc[u] = F(0);
+    int e = e0 + slot;
+    for (; e + (QF_UNROLL - 1) * nslots < e1; e += QF_UNROLL * nslots) {
+      int2 ij[QF_UNROLL];
+      F v[QF_UNROLL];
+#pragma unroll
+      for (int u = 0; u < QF_UNROLL; ++u) {
+        ij[u] = __ldg(a.idx + e + u * nslots);
+        v[u] = __ldg(val + e + u * nslots);
+      }
+#pragma unroll
+      for (int u = 0; u < QF_UNROLL; ++u) {
+        F yi = xs[(size_t)ij[u].x * SP + s], yj = xs[(size_t)ij[u].y * SP + s];
+        if (SHIFT) {
+          yi -= mus[ij[u].x];
+          yj -= mus[ij[u].y];
+        }
+        acc[u] += v[u] * yi * yj;
+      }
+    }
+    for (; e < e1; e += nslots) {
+      const int2 ij = __ldg(a.idx + e);
+      F yi = xs[(size_t)ij.x * SP + s], yj = xs[(size_t)ij.y * SP + s];
+      if (SHIFT) {
+        yi -= mus[ij.x];
+        yj -= mus[ij.y];
+      }
+      acc[0] += __ldg(val + e) * yi * yj;
+    }
+    double q = 0.0;
+#pragma unroll
+    for (int u = 0; u < QF_UNROLL; ++u) q += (double)acc[u];
+    red[(size_t)slot * S + s] = q;
+    if (dots) {
+      F d = F(0);
+      for (int i = slot; i < n; i += nslots) d += us[i] * (xs[(size_t)i * SP + s] - (SHIFT ? mus[i] : F(0)));
+      red[(size_t)(nslots + slot) * S + s] = (double)d;
+    }
+    __syncthreads();
+    if (tid < S) {
+      double tot = 0.0, dot = 0.0;
+      for (int w = 0; w < nslots; ++w) tot += red[(size_t)w * S + tid];
+      if (dots)
+        for (int w = 0; w < nslots; ++w) dot += red[(size_t)(nslots + w) * S + tid];
+      const int64_t gs = s0 + tid;
+      if (gs < a.m) {
+        static_cast<F *>(a.Q)[gs * K + k] = (F)tot;
+        if (dots) static_cast<F *>(a.D)[gs * K + k] = (F)dot;
+      }
+      const double cmp = (double)(F)tot;   // the argmin sees the stored value
+      if (k == 0 || cmp < best) {
+        best = cmp;
+        best_k = k;
+      }
+    }
+  }
+  if (tid < S && a.labels != nullptr && s0 + tid < a.m) a.labels[s0 + tid] = best_k;
+}
+
+template <typename F, int S> static size_t qf_smem(int n) {
+  constexpr int R = 32 / S;
+  return sizeof(F) * ((size_t)n * (S + 1) + 2 * (size_t)n + (n & 1)) + sizeof(double) * 2 * QF_WARPS * R * S;
+}
+
+template <typename F, int S> static int qf_launch(const QfArgs &a, cudaStream_t st) {
+  const size_t smem = qf_smem<F, S>(a.n);
+  const int64_t grid = (a.m + S - 1) / S;
+  if (a.shift != nullptr) {
+    GL_CUDA(cudaFuncSetAttribute(quadform_kernel<F, S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    quadform_kernel<F, S, true><<<(unsigned)grid, QF_THREADS, smem, st>>>(a);
+  } else {
+    GL_CUDA(cudaFuncSetAttribute(quadform_kernel<F, S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    quadform_kernel<F, S, false><<<(unsigned)grid, QF_THREADS, smem, st>>>(a);
+  }
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+template <typename F> static int qf_apply_t(const QfArgs &a, cudaStream_t st) {
+  // widest block that still lets two CTAs share an SM (staging of one overlaps the gathers of the
+  // other); else the widest block that fits at all
+  if (qf_smem<F, 32>(a.n) <= QF_SMEM_PAIR) return qf_launch<F, 32>(a, st);
+  if (qf_smem<F, 16>(a.n) <= QF_SMEM_PAIR) return qf_launch<F, 16>(a, st);
+  if (qf_smem<F, 8>(a.n) <= QF_SMEM_PAIR) return qf_launch<F, 8>(a, st);
+  if (qf_smem<F, 32>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 32>(a, st);
+  if (qf_smem<F, 16>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 16>(a, st);
+  if (qf_smem<F, 8>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 8>(a, st);
+  if (qf_smem<F, 4>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 4>(a, st);
+  return fail(GL_E_SHAPE, "n=%d: a block of 4 samples does not fit in shared memory", a.n);
+}
+
+template <typename F> static int qf_create_t(gl_quadform *q, const void *A, double diag_add, cudaStream_t st) {
+  const int rows = q->K * q->n;
+  int32_t *cnt = nullptr;
+  void *tmp = nullptr;
+  size_t tmp_bytes = 0;
+  GL_CUDA(cudaMalloc(&q->rowoff, sizeof(int32_t) * ((size_t)rows + 1)));
+  GL_CUDA(cudaMalloc(&cnt, sizeof(int32_t) * ((size_t)rows + 1)));
+  GL_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * ((size_t)rows + 1), st));
+  const int wpb = 8, grid = (rows + wpb - 1) / wpb;
+  qf_count_kernel<F><<<grid, wpb * 32, 0, st>>>(static_cast<const F *>(A), q->K, q->n, cnt);
+  ::gl::g_launches.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, cnt, q->rowoff, rows + 1, st);
+  if (e == cudaSuccess) e = cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1);
+  if (e == cudaSuccess) e = cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, cnt, q->rowoff, rows + 1, st);
+  int32_t total = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&total, q->rowoff + rows, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(cnt);
+  cudaFree(tmp);
+  if (e != cudaSuccess) return fail(GL_E_CUDA, "quadform compaction failed: %s", cudaGetErrorString(e));
+  q->nnz = total;
+  GL_CUDA(cudaMalloc(&q->idx, sizeof(int2) * (size_t)total));
+  GL_CUDA(cudaMalloc(&q->val, sizeof(F) * (size_t)total));
+  qf_fill_kernel<F><<<grid, wpb * 32, 0, st>>>(static_cast<const F *>(A), q->K, q->n, (F)diag_add, q->rowoff, q->idx,
+                                              static_cast<F *>(q->val));
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+}  // namespace gl
+using namespace gl;
+
+extern "C" int gl_quadform_create(gl_quadform **out, const void *A_dev, int K, int n, int dtype, double diag_add,
+                                  void *stream) {
+  if (out == nullptr) return fail(GL_E_ARG, "out is null");
+  *out = nullptr;
+  if (K < 1 || n < 1) return fail(GL_E_SHAPE, "need K >= 1 matrices of n >= 1 nodes (K=%d, n=%d)", K, n);
+  if ((int64_t)K * n * n > (int64_t)INT32_MAX) return fail(GL_E_SHAPE, "K*n*n = %lld entries exceed int32 offsets",
+                                                           (long long)K * n * n);
+  if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "bad dtype %d", dtype);
+  gl_quadform *q = new gl_quadform{K, n, dtype, 0, nullptr, nullptr, nullptr};
+  const int rc = dtype == GL_F32 ? qf_create_t<float>(q, A_dev, diag_add, as_stream(stream))
+                                 : qf_create_t<double>(q, A_dev, diag_add, as_stream(stream));
+  if (rc != GL_OK) {
+    gl_quadform_destroy(q);
+    return rc;
+  }
+  *out = q;
+  return GL_OK;
+}
+
+extern "C" int gl_quadform_destroy(gl_quadform *q) {
+  if (q == nullptr) return GL_OK;
+  cudaFree(q->rowoff);
+  cudaFree(q->idx);
+  cudaFree(q->val);
+  delete q;
+  return GL_OK;
+}
+
+extern "C" int64_t gl_quadform_nnz(const gl_quadform *q) { return q ? q->nnz : -1; }
+
+extern "C" int gl_quadform_apply(gl_quadform *q, const void *X_dev, int64_t m, int64_t ldx, const void *shift_dev,
+                                 const void *U_dev, void *Q_dev, void *D_dev, int32_t *labels_dev, void *stream) {
+  if (q == nullptr) return fail(GL_E_ARG, "quadform handle is null");
+  if (m < 0 || ldx < q->n) return fail(GL_E_SHAPE, "bad signal matrix shape (m=%lld, ldx=%lld, n=%d)", (long long)m,
+                                       (long long)ldx, q->n);
+  if (m == 0) return GL_OK;
+  if (Q_dev == nullptr) return fail(GL_E_ARG, "Q_out is null");
+  if ((U_dev == nullptr) != (D_dev == nullptr)) return fail(GL_E_ARG, "U and D_out go together");
+  QfArgs a{X_dev, m, ldx, q->n, q->K, q->rowoff, q->idx, q->val, shift_dev, U_dev, Q_dev, D_dev, labels_dev};
+  return q->dtype == GL_F32 ? qf_apply_t<float>(a, as_stream(stream)) : qf_apply_t<double>(a, as_stream(stream));
+}

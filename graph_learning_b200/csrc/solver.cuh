@@ -10,6 +10,8 @@ enum {
   FLAG_EDGE_TICKET = 3, // last-CTA-done counter of the edge pass
   FLAG_NODE_TICKET = 4, // last-CTA-done counter of the node tail
   FLAG_ERROR = 5,       // peer exchange timed out
+  FLAG_NEED = 6,        // K > 1: the node tail could not rule the stop out from the cheap bound; the
+                        // edge Gram + decide kernels evaluate the exact spectral norms this iteration
   FLAG_COUNT = 8
 };
 
@@ -75,6 +77,7 @@ int launch_edge_init(gl_solver *s, cudaStream_t st);
 int launch_signal(gl_solver *s, cudaStream_t st);
 int launch_gram_edges(gl_solver *s, cudaStream_t st);
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
+int launch_batch_decide(gl_solver *s, cudaStream_t st);
 int launch_persistent(gl_solver *s, int iters, cudaStream_t st);
 int fill_tile_table(gl_solver *s);
 }  // namespace gl

@@ -182,7 +182,10 @@ int gl_solver_comm_publish(gl_solver *s, void *stream);
 /* Single-GPU driver: runs iterations from an internally captured CUDA graph until the device
  * stop flag is set; polls every `poll_every` iterations (<=0: default).  Synchronises. */
 int gl_solver_run(gl_solver *s, int poll_every, void *stream);
-/* Read back iteration count and the last relative residuals (synchronises the stream). */
+/* Read back iteration count and the last relative residuals (synchronises the stream).  For K > 1
+ * rel_primal is exact on the iteration that ended the solve (stop rule or maxit); in between it is the
+ * lower bound max_k ||q_k - y_k|| / ||W||_F the node tail uses to rule the stop out without forming
+ * the K x K edge Grams (the stop decisions are those of the exact rule, smooth_learning.py:158-166). */
 int gl_solver_status(gl_solver *s, int *n_iter, double *rel_primal, double *rel_dual,
                      int *converged, void *stream);
 /* Optional phase tracing of the persistent iteration kernel (K == 1): after enabling, CTA 0 stamps
@@ -259,6 +262,26 @@ int gl_knn_store(gl_knn_solver *k, void *w_out_dev, double edge_tol, void *strea
  * reference statistic (smooth_learning.py:201-219) only reads the k + 1 smallest entries of a row. */
 int gl_knn_build(const void *X_dev, int64_t m, int n, int64_t ldx, int k, int32_t *idx_out_dev,
                  void *d2_out_dev, void *stream);
+
+/* Assignment step of the batched callers: per-sample quadratic forms against K
+ * square matrices A_k (K, n, n), e.g. the learned Laplacians,
+ *     Q[s, k] = y^T (A_k + diag_add I) y,   y = X[s, :] - shift[k, :]   (shift nullable = 0)
+ * replacing the dense contractions np.einsum("ni,kij,nj->nk") of reference kgraphs.py:87-88 and the
+ * eigenvector projection of glmm.py:253-274 (which equals Q - (lambda_0 + regul) D^2 with
+ * diag_add = regul, U[k] = the first eigenvector and D[s, k] = U[k] . y).  Evaluated over the non-zero
+ * entries of A_k only (diagonal + symmetrised upper triangle), exact for any square matrix.
+ * gl_quadform_create compacts the matrices (synchronises once for the entry count); the handle owns
+ * its device arrays.  gl_quadform_apply: X (m, n) row-major with leading dimension ldx, Q_out (m, K);
+ * U (K, n) and D_out (m, K) go together (both nullable); labels_out (m) int32 = argmin_k Q[s, k], first
+ * minimum on ties as np.argmin (kgraphs.py:113), nullable.  All arrays of the handle's dtype. */
+typedef struct gl_quadform gl_quadform;
+int gl_quadform_create(gl_quadform **out, const void *A_dev, int K, int n, int dtype, double diag_add,
+                       void *stream);
+int gl_quadform_destroy(gl_quadform *q);
+int64_t gl_quadform_nnz(const gl_quadform *q);
+int gl_quadform_apply(gl_quadform *q, const void *X_dev, int64_t m, int64_t ldx, const void *shift_dev,
+                      const void *U_dev, void *Q_out_dev, void *D_out_dev, int32_t *labels_out_dev,
+                      void *stream);
 
 #ifdef __cplusplus
 }

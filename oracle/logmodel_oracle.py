@@ -44,6 +44,8 @@ __all__ = [
     "to_packed",
     "laplacian_from_packed",
     "laplacian_adjoint",
+    "smoothness",
+    "glmm_log_prob",
     "SolveInfo",
 ]
 
@@ -403,3 +405,34 @@ def laplacian_adjoint(lap: np.ndarray) -> np.ndarray:
     dg = np.diagonal(lap, axis1=-2, axis2=-1)
     full = dg[..., :, None] + dg[..., None, :] - lap - np.swapaxes(lap, -1, -2)
     return to_packed(full)
+
+
+# --------------------------------------------------------------------------------------
+# assignment step of the batched callers
+# --------------------------------------------------------------------------------------
+def smoothness(x: np.ndarray, laplacians: np.ndarray, means: np.ndarray | None = None) -> np.ndarray:
+    """(m, n) signals x (K, n, n) matrices -> (m, K) quadratic forms y^T L_k y with y = x (k-Graphs,
+    kgraphs.py:87-88) or y = x - means[k] (k-Graphs V2, kgraphs.py:203-205).  Dense contraction."""
+    x = np.asarray(x, dtype=np.float64)
+    out = np.empty((x.shape[0], laplacians.shape[0]))
+    for k, lap in enumerate(np.asarray(laplacians, dtype=np.float64)):
+        y = x if means is None else x - means[k]
+        out[:, k] = np.sum((y @ lap) * y, axis=1)
+    return out
+
+
+def glmm_log_prob(x: np.ndarray, laplacians: np.ndarray, means: np.ndarray, regul: float) -> np.ndarray:
+    """GLMM E-step log-probabilities (glmm.py:238-279): eigendecompose each Laplacian, add ``regul``
+    to the spectrum, drop the first eigenpair, Gaussian log-density in the remaining n - 1 directions.
+    ``log(prod(.))`` is kept as written there (it overflows for large n exactly like the reference)."""
+    x = np.asarray(x, dtype=np.float64)
+    n = x.shape[1]
+    eigval, eigvec = np.linalg.eigh(np.asarray(laplacians, dtype=np.float64))
+    eigval = eigval + regul
+    out = np.empty((x.shape[0], laplacians.shape[0]))
+    for k in range(laplacians.shape[0]):
+        proj = (x - means[k]) @ eigvec[k][:, 1:]
+        with np.errstate(over="ignore", divide="ignore"):
+            logdet = np.log(np.prod(eigval[k, 1:]))
+        out[:, k] = (-(n - 1) * np.log(2 * np.pi) + logdet - np.sum(proj * proj * eigval[k, 1:], axis=1)) / 2
+    return out

@@ -216,7 +216,38 @@ def clustering():
     )
 
 
+def assignment():
+    """Assignment-step quantities of the unmodified reference on the clustering
+    data and fitted parameters above: kgraphs.py:87-88, kgraphs.py:203-205, glmm.py:238-279."""
+    g = np.load(os.path.join(HERE, "clustering_n25.npz"))
+    x = g["x"]
+    kg = KGraphs(n_clusters=3, avg_degree=3)
+    kg.laplacians_ = g["kgraphs_laplacians"]
+    smooth = kg._smoothness(x)
+    kg2 = KGraphsV2(n_clusters=3, avg_degree=3)
+    kg2.laplacians_, kg2.means_ = g["kgraphs2_laplacians"], g["kgraphs2_means"]
+    csmooth = kg2._centered_smoothness(x)
+    glmm = GLMMShim(n_components=3, avg_degree=3)
+    glmm.laplacians_, glmm.means_, glmm.weights_ = g["glmm_laplacians"].copy(), g["glmm_means"], g["glmm_weights"]
+    glmm.n_nodes_ = x.shape[1]
+    log_prob = glmm._estimate_log_prob(x)
+    # a dense, non-symmetric, non-Laplacian stack: the einsum is defined for any square matrices
+    rng = np.random.default_rng(5)
+    dense = rng.standard_normal((2, 25, 25))
+    kg.laplacians_ = dense
+    smooth_dense = kg._smoothness(x)
+    save("assign_n25", x=x, kgraphs_laplacians=g["kgraphs_laplacians"], smoothness=smooth,
+         labels=np.argmin(smooth, axis=1), kgraphs2_laplacians=g["kgraphs2_laplacians"],
+         kgraphs2_means=g["kgraphs2_means"], centered_smoothness=csmooth,
+         glmm_laplacians=g["glmm_laplacians"], glmm_means=g["glmm_means"], regul=np.float64(glmm.regul),
+         log_prob=log_prob, dense=dense, smoothness_dense=smooth_dense)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1:          # regenerate only the named sets
+        for name in sys.argv[1:]:
+            globals()[name]()
+        sys.exit(0)
     solver_states()
     logmodel_fit()
     theta_cases()
@@ -224,3 +255,4 @@ if __name__ == "__main__":
     batched()
     window_model()
     clustering()
+    assignment()

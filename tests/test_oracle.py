@@ -155,3 +155,15 @@ def test_knn_support_symmetric():
     deg = np.bincount(ei, minlength=50) + np.bincount(ej, minlength=50)
     assert deg.min() >= 4
     assert np.all(np.diff(ei * 50 + ej) > 0)
+
+
+def test_assignment_step(golden):
+    """N2 / N1 restatements against the unmodified reference (kgraphs.py:87-88, :203-205, glmm.py:238-279)."""
+    g = golden("assign_n25")
+    sm = orc.smoothness(g["x"], g["kgraphs_laplacians"])
+    assert rel(sm, g["smoothness"]) < 1e-13
+    assert np.array_equal(np.argmin(sm, axis=1), g["labels"])
+    assert rel(orc.smoothness(g["x"], g["kgraphs2_laplacians"], g["kgraphs2_means"]), g["centered_smoothness"]) < 1e-13
+    assert rel(orc.smoothness(g["x"], g["dense"]), g["smoothness_dense"]) < 1e-13
+    lp = orc.glmm_log_prob(g["x"], g["glmm_laplacians"], g["glmm_means"], float(g["regul"]))
+    assert rel(lp, g["log_prob"]) < 1e-12
