@@ -228,8 +228,10 @@ class GLMM(BaseMixture):
             quad, dot = qf.apply(xd, shift=self.means_, vectors=first)
         lam0 = torch.as_tensor(eigval[:, 0], device=quad.device, dtype=torch.float64)
         data = quad.double() - lam0[None, :] * dot.double() ** 2                      # :267-274
-        with np.errstate(over="ignore", divide="ignore"):
-            logdet = np.log(np.prod(eigval[:, 1:], axis=1))                          # :272 (overflows like the reference)
+        # :272 is log(prod(.)); the sum of logs is the same number wherever that product is finite and
+        # stays finite where it overflows (n >~ 400), which config 4 (n = 1,000) needs
+        with np.errstate(divide="ignore", invalid="ignore"):
+            logdet = np.sum(np.log(eigval[:, 1:]), axis=1)
         const = -(self.n_nodes_ - 1) * np.log(2 * np.pi)
         return (const + logdet[None, :] - data.cpu().numpy()) / 2
 

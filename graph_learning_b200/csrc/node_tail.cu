@@ -368,23 +368,36 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   // rel_primal >= s_lo, so the stop rule is RULED OUT exactly whenever s_lo >= tol (or the dual
   // ratio, exact here, is >= tol).  Otherwise FLAG_NEED hands the decision to gram_edges_kernel +
   // batch_decide_kernel, which evaluate the exact norms: the decisions are those of the full rule.
+  // The dual ratio is bounded the same way from the node-side Grams (exact and cheap, but their 26
+  // squarings are not): the spectral norms are evaluated only when BOTH bounds fall below tol.
   const bool lazy = A.K > 1;
-  __shared__ double s_lo;
-  __shared__ int s_nan;
+  __shared__ double s_lo, s_lo_dual;
+  __shared__ int s_skip;
   if (!A.init && it >= 1) {
-    const double *G[4] = {lazy ? g_rb : g_r, lazy ? A.gprev + KK : A.gprev, g_rb, A.gprev + KK};
-    lambda_max4(G, A.K, A.eig, s_lam);
+    if (tid == 0) s_skip = 0;
     if (lazy && tid == 0) {
-      double mx = 0.0, tr = 0.0;
+      double mx = 0.0, tr = 0.0, mxd = 0.0, trd = 0.0;
       int bad = 0;
       for (int k = 0; k < A.K; ++k) {
         const double v = __ldcg(g_r + k * A.K + k), u = A.gprev[k * A.K + k];
-        bad |= (v != v) || (u != u);
+        const double vd = g_rb[k * A.K + k], ud = A.gprev[KK + k * A.K + k];
+        bad |= (v != v) || (u != u) || (vd != vd) || (ud != ud);
         mx = v > mx ? v : mx;
+        mxd = vd > mxd ? vd : mxd;
         tr += u;
+        trd += ud;
       }
       s_lo = sqrt(mx) / sqrt(tr);
-      s_nan = bad || (s_lo != s_lo);
+      s_lo_dual = sqrt(mxd) / sqrt(trd);
+      bad |= (s_lo != s_lo) || (s_lo_dual != s_lo_dual);
+      // 1e-3 slack covers the rounding of the float32 partial sums behind the primal bound
+      const bool out = !bad && (s_lo * (1.0 - 1e-3) >= A.tol || s_lo_dual * (1.0 - 1e-3) >= A.tol);
+      s_skip = out && it + 1 < A.maxit;   // the last iteration reports exact residuals
+    }
+    __syncthreads();
+    if (!s_skip) {
+      const double *G[4] = {lazy ? g_rb : g_r, lazy ? A.gprev + KK : A.gprev, g_rb, A.gprev + KK};
+      lambda_max4(G, A.K, A.eig, s_lam);
     }
   }
   __syncthreads();
@@ -410,7 +423,10 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
       A.resid[1] = CUDART_INF;
     } else {
       bool conv = false, need = false;
-      if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+      if (it >= 1 && s_skip) {   // K > 1: ruled out by the bounds (reported as such)
+        A.resid[0] = s_lo;
+        A.resid[1] = s_lo_dual;
+      } else if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
         const double rd = sqrt(s_lam[2]) / sqrt(s_lam[3]);
         A.resid[1] = rd;
         if (!lazy) {
@@ -418,9 +434,8 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
           A.resid[0] = rp;
           conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
         } else {
-          // 1e-3 slack covers the rounding of the float32 partial sums behind the bound
-          const bool ruled_out = !(rd < A.tol) || (!s_nan && s_lo * (1.0 - 1e-3) >= A.tol);
-          need = !ruled_out || it + 1 >= A.maxit;   // the last iteration reports exact residuals
+          // the dual ratio is exact here: it alone can still rule the stop out
+          need = (rd < A.tol) || it + 1 >= A.maxit;
           if (!need) A.resid[0] = s_lo;              // a lower bound; exact on the deciding iterations
         }
       }
