@@ -11,12 +11,15 @@
 //
 //   gl_quadform_create : compacts K dense matrices into entry lists (i, j, value), deterministic order
 //                        (row-major; warp-ballot ordered compaction, one cub scan).
-//   gl_quadform_apply  : one CTA per block of S samples.  The block's signals are staged transposed in
-//                        shared memory (node-major, padded: lane = sample reads are conflict-free), each
-//                        warp walks a strided share of the entry list (entry loads are warp-uniform
-//                        broadcasts), partial sums are combined across warps in a fixed order, and the
-//                        argmin over k is fused into the tail.  X is read exactly once: the kernel is
-//                        bound by the shared-memory gathers, 2 per entry per 32 samples.
+//   gl_quadform_apply  : one CTA (1024 threads) per block of S samples.  The block's signals are staged
+//                        transposed in shared memory (node-major, padded: lane = sample reads are
+//                        conflict-free).  Entries are stored row by row, the diagonal first and flagged,
+//                        so a warp streams a contiguous, entry-balanced range of rows as
+//                            q += y_i * (A_ii y_i + sum_j (A_ij + A_ji) y_j)
+//                        with ONE 8-byte warp-uniform entry load and ONE gather per entry (y_i is gathered
+//                        once per row).  Partial sums are combined across warps in a fixed order and the
+//                        argmin over k is fused into the tail.  X is read exactly once; the kernel is
+//                        bound by the L1/shared-memory pipe (about 2 wavefronts per entry per 32 samples).
 #include <cub/device/device_scan.cuh>
 
 #include "common.cuh"
@@ -25,18 +28,52 @@ struct gl_quadform {
   int K, n, dtype;
   int64_t nnz;
   int32_t *rowoff;   // (K*n + 1) entry offsets; graph k owns [rowoff[k*n], rowoff[(k+1)*n])
-  int2 *idx;         // (nnz) node pairs, i <= j
-  void *val;         // (nnz) values of dtype
+  void *ent;         // (nnz) packed entries {column | row-start flag, value}, row-major, diagonal first
+  int32_t *bounds;   // (K, QF_MAX_SLOTS + 1) entry offsets of row-aligned, entry-balanced stream shares
 };
 
 namespace gl {
 
-constexpr int QF_THREADS = 512;
+constexpr int QF_THREADS = 1024;
 constexpr int QF_WARPS = QF_THREADS / 32;
 constexpr int QF_UNROLL = 4;
 constexpr int QF_STAGE = 8;                   // row loads in flight per lane while staging
-constexpr size_t QF_SMEM_CAP = 200 * 1024;   // one CTA per SM
-constexpr size_t QF_SMEM_PAIR = 100 * 1024;  // two CTAs per SM: one stages while the other computes
+constexpr size_t QF_SMEM_CAP = 224 * 1024;   // one CTA per SM (227 KB is the hardware limit)
+constexpr unsigned QF_ROW_START = 0x80000000u;
+constexpr int QF_MAX_SLOTS = QF_WARPS * 8;    // S = 4: 8 slots per warp; coarser S uses every (8/R)-th bound
+
+// packed entry: column index (bit 31 = first entry of its row, i.e. the diagonal) and value
+template <typename F> struct QfEntry;
+template <> struct __align__(8) QfEntry<float> {
+  unsigned j;
+  float v;
+};
+template <> struct __align__(16) QfEntry<double> {
+  unsigned j, pad;
+  double v;
+};
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ QfEntry<float> qf_load(const QfEntry<float> *p) {
+  const int2 t = __ldg(reinterpret_cast<const int2 *>(p));
+  QfEntry<float> e;
+  e.j = (unsigned)t.x;
+  e.v = __int_as_float(t.y);
+  return e;
+}
+__device__ __forceinline__ QfEntry<double> qf_load(const QfEntry<double> *p) {
+  const int4 t = __ldg(reinterpret_cast<const int4 *>(p));
+  QfEntry<double> e;
+  e.j = (unsigned)t.x;
+  e.pad = 0;
+  e.v = __hiloint2double(t.w, t.z);
+  return e;
+}
 
 // ---- compaction -------------------------------------------------------------------------------------
 // one warp per (k, i) row: 1 (the diagonal, always kept) + #{j > i : A_ij + A_ji != 0}
@@ -54,15 +91,17 @@ __global__ void qf_count_kernel(const F *__restrict__ A, int K, int n, int32_t *
 
 template <typename F>
 __global__ void qf_fill_kernel(const F *__restrict__ A, int K, int n, F diag_add, const int32_t *__restrict__ rowoff,
-                               int2 *__restrict__ idx, F *__restrict__ val) {
+                               QfEntry<F> *__restrict__ ent) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= K * n) return;
   const int k = row / n, i = row % n;
   const F *Ak = A + (size_t)k * n * n;
   int pos = rowoff[row];
   if (lane == 0) {
-    idx[pos] = make_int2(i, i);
-    val[pos] = Ak[(size_t)i * n + i] + diag_add;
+    QfEntry<F> e{};
+    e.j = (unsigned)i | QF_ROW_START;
+    e.v = Ak[(size_t)i * n + i] + diag_add;
+    ent[pos] = e;
   }
   ++pos;
   for (int j0 = i + 1; j0 < n; j0 += 32) {
@@ -72,11 +111,29 @@ __global__ void qf_fill_kernel(const F *__restrict__ A, int K, int n, F diag_add
     const unsigned keep = __ballot_sync(0xffffffffu, v != F(0));
     if (v != F(0)) {
       const int p = pos + __popc(keep & ((1u << lane) - 1u));
-      idx[p] = make_int2(i, j);
-      val[p] = v;
+      QfEntry<F> e{};
+      e.j = (unsigned)j;
+      e.v = v;
+      ent[p] = e;
     }
     pos += __popc(keep);
   }
+}
+
+// share t of graph k starts at the first row whose offset reaches t/QF_MAX_SLOTS of the graph's entries
+__global__ void qf_bounds_kernel(const int32_t *__restrict__ rowoff, int K, int n, int32_t *__restrict__ bounds) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= K * (QF_MAX_SLOTS + 1)) return;
+  const int k = x / (QF_MAX_SLOTS + 1), t = x % (QF_MAX_SLOTS + 1);
+  const int32_t *ro = rowoff + (size_t)k * n;
+  const int e0 = ro[0], len = ro[n] - e0;
+  const int target = (int)((int64_t)len * t / QF_MAX_SLOTS);
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (ro[mid] - e0 < target) lo = mid + 1; else hi = mid;
+  }
+  bounds[x] = t == QF_MAX_SLOTS ? ro[n] : ro[lo];
 }
 
 // ---- evaluation ---------------------------------------------------------------------------------------
@@ -84,9 +141,8 @@ struct QfArgs {
   const void *X;
   int64_t m, ldx;
   int n, K;
-  const int32_t *rowoff;
-  const int2 *idx;
-  const void *val;
+  const int32_t *bounds;
+  const void *ent;
   const void *shift;   // (K, n) or null
   const void *U;       // (K, n) or null
   void *Q;             // (m, K)
@@ -94,9 +150,9 @@ struct QfArgs {
   int32_t *labels;     // (m) or null
 };
 
-// S samples per CTA; a warp holds R = 32 / S entry sub-slots of S samples each.
+// S samples per CTA; a warp holds R = 32 / S slots of S samples each, every slot streams its own rows.
 template <typename F, int S, bool SHIFT>
-__global__ void __launch_bounds__(QF_THREADS, 2) quadform_kernel(QfArgs a) {
+__global__ void __launch_bounds__(QF_THREADS, 1) quadform_kernel(QfArgs a) {
   constexpr int R = 32 / S;
   constexpr int SP = S + 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -104,12 +160,17 @@ __global__ void __launch_bounds__(QF_THREADS, 2) quadform_kernel(QfArgs a) {
   F *mus = xs + (size_t)a.n * SP;                          // [n]
   F *us = mus + a.n;                                       // [n]
   double *red = reinterpret_cast<double *>(us + a.n + (a.n & 1));   // [2][QF_WARPS * R][S]
+  constexpr int EPP = 16 / (int)sizeof(QfEntry<F>);   // entries per 16-byte piece
+  constexpr int RING = S * EPP;                       // entries per ring buffer (one piece per lane)
+  QfEntry<F> *ring_base = reinterpret_cast<QfEntry<F> *>(                              // [slots][2][RING], 16-byte aligned
+      (reinterpret_cast<uintptr_t>(red + 2 * QF_WARPS * R * S) + 15) & ~uintptr_t(15));
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int s = lane % S, sub = lane / S;
+  const unsigned slot_mask = S == 32 ? 0xffffffffu : (((1u << (S & 31)) - 1u) << (sub * S));
   const int n = a.n, K = a.K;
   const int64_t s0 = (int64_t)blockIdx.x * S;
   const F *X = static_cast<const F *>(a.X);
-  const F *val = static_cast<const F *>(a.val);
+  const QfEntry<F> *ent = static_cast<const QfEntry<F> *>(a.ent);
 
   // staging: a warp takes whole sample rows, QF_STAGE coalesced 128-byte loads in flight per lane;
   // the transposed stores have stride SP = S + 1 words (odd): conflict-free
@@ -135,6 +196,8 @@ __global__ void __launch_bounds__(QF_THREADS, 2) quadform_kernel(QfArgs a) {
   double best = 0.0;
   int best_k = 0;
   const int slot = warp * R + sub, nslots = QF_WARPS * R;
+  constexpr int BSTEP = QF_MAX_SLOTS / (QF_WARPS * R);
+  int nb0 = __ldg(a.bounds + slot * BSTEP), nb1 = __ldg(a.bounds + (slot + 1) * BSTEP);
   for (int k = 0; k < K; ++k) {
     __syncthreads();   // xs ready (k = 0); previous graph's mus / us / red consumed
     if (SHIFT) {
@@ -146,41 +209,71 @@ __global__ void __launch_bounds__(QF_THREADS, 2) quadform_kernel(QfArgs a) {
       for (int i = tid; i < n; i += QF_THREADS) us[i] = u[i];
     }
     __syncthreads();
-    const int e0 = a.rowoff[(size_t)k * n], e1 = a.rowoff[(size_t)(k + 1) * n];
-    F acc[QF_UNROLL];
-#pragma unroll
-    for (int u = 0; u < QF_UNROLL; ++u) acc[u] = F(0);
-    int e = e0 + slot;
-    for (; e + (QF_UNROLL - 1) * nslots < e1; e += QF_UNROLL * nslots) {
-      int2 ij[QF_UNROLL];
-      F v[QF_UNROLL];
-#pragma unroll
-      for (int u = 0; u < QF_UNROLL; ++u) {
-        ij[u] = __ldg(a.idx + e + u * nslots);
-        v[u] = __ldg(val + e + u * nslots);
-      }
-#pragma unroll
-      for (int u = 0; u < QF_UNROLL; ++u) {
-        F yi = xs[(size_t)ij[u].x * SP + s], yj = xs[(size_t)ij[u].y * SP + s];
-        if (SHIFT) {
-          yi -= mus[ij[u].x];
-          yj -= mus[ij[u].y];
-        }
-        acc[u] += v[u] * yi * yj;
-      }
+    // this slot's contiguous, row-aligned share of graph k's entry stream (precomputed bounds; the
+    // next graph's pair is fetched now so that its latency is hidden)
+    const int ebeg = nb0, eend = nb1;
+    if (k + 1 < K) {
+      nb0 = __ldg(a.bounds + (size_t)(k + 1) * (QF_MAX_SLOTS + 1) + slot * BSTEP);
+      nb1 = __ldg(a.bounds + (size_t)(k + 1) * (QF_MAX_SLOTS + 1) + (slot + 1) * BSTEP);
     }
-    for (; e < e1; e += nslots) {
-      const int2 ij = __ldg(a.idx + e);
-      F yi = xs[(size_t)ij.x * SP + s], yj = xs[(size_t)ij.y * SP + s];
-      if (SHIFT) {
-        yi -= mus[ij.x];
-        yj -= mus[ij.y];
-      }
-      acc[0] += __ldg(val + e) * yi * yj;
-    }
+    const int abeg = ebeg & ~(EPP - 1);                       // 16-byte aligned start
+    const int nbuf = eend > abeg ? (eend - abeg + RING - 1) / RING : 0;
+    QfEntry<F> *ring = ring_base + (size_t)slot * 2 * RING;
+    auto issue = [&](int bfr) {
+      const int pe = abeg + bfr * RING + s * EPP;             // first entry of this lane's piece
+      if (bfr < nbuf && pe < eend) cp_async16(ring + (bfr & 1) * RING + s * EPP, ent + pe);
+      cp_async_commit();
+    };
     double q = 0.0;
+    F yi = F(0), accr = F(0);
+    issue(0);
+    for (int bfr = 0; bfr < nbuf; ++bfr) {
+      issue(bfr + 1);
+      cp_async_wait1();
+      __syncwarp(slot_mask);
+      const QfEntry<F> *buf = ring + (bfr & 1) * RING;
+      const int base = abeg + bfr * RING;
+      int e = ebeg > base ? ebeg : base;
+      const int hi = eend < base + RING ? eend : base + RING;
+      for (; e + QF_UNROLL <= hi; e += QF_UNROLL) {
+        QfEntry<F> en[QF_UNROLL];
+        F g[QF_UNROLL];
 #pragma unroll
-    for (int u = 0; u < QF_UNROLL; ++u) q += (double)acc[u];
+        for (int u = 0; u < QF_UNROLL; ++u) en[u] = buf[e - base + u];
+#pragma unroll
+        for (int u = 0; u < QF_UNROLL; ++u) {
+          const unsigned j = en[u].j & ~QF_ROW_START;
+          g[u] = xs[(size_t)j * SP + s];
+          if (SHIFT) g[u] -= mus[j];
+        }
+#pragma unroll
+        for (int u = 0; u < QF_UNROLL; ++u) {
+          if (en[u].j & QF_ROW_START) {       // diagonal entry: close the previous row, open this one
+            q += (double)yi * (double)accr;
+            yi = g[u];
+            accr = en[u].v * g[u];
+          } else {
+            accr += en[u].v * g[u];
+          }
+        }
+      }
+      for (; e < hi; ++e) {
+        const QfEntry<F> en = buf[e - base];
+        const unsigned j = en.j & ~QF_ROW_START;
+        F g = xs[(size_t)j * SP + s];
+        if (SHIFT) g -= mus[j];
+        if (en.j & QF_ROW_START) {
+          q += (double)yi * (double)accr;
+          yi = g;
+          accr = en.v * g;
+        } else {
+          accr += en.v * g;
+        }
+      }
+      __syncwarp(slot_mask);   // the buffer is refilled two steps from now
+    }
+    cp_async_wait0();
+    q += (double)yi * (double)accr;
     red[(size_t)slot * S + s] = q;
     if (dots) {
       F d = F(0);
@@ -210,7 +303,8 @@ __global__ void __launch_bounds__(QF_THREADS, 2) quadform_kernel(QfArgs a) {
 
 template <typename F, int S> static size_t qf_smem(int n) {
   constexpr int R = 32 / S;
-  return sizeof(F) * ((size_t)n * (S + 1) + 2 * (size_t)n + (n & 1)) + sizeof(double) * 2 * QF_WARPS * R * S;
+  return sizeof(F) * ((size_t)n * (S + 1) + 2 * (size_t)n + (n & 1)) + sizeof(double) * 2 * QF_WARPS * R * S +
+         (size_t)QF_WARPS * R * 2 * S * 16 + 16;   // + the entry rings (aligned up)
 }
 
 template <typename F, int S> static int qf_launch(const QfArgs &a, cudaStream_t st) {
@@ -228,11 +322,7 @@ template <typename F, int S> static int qf_launch(const QfArgs &a, cudaStream_t 
 }
 
 template <typename F> static int qf_apply_t(const QfArgs &a, cudaStream_t st) {
-  // widest block that still lets two CTAs share an SM (staging of one overlaps the gathers of the
-  // other); else the widest block that fits at all
-  if (qf_smem<F, 32>(a.n) <= QF_SMEM_PAIR) return qf_launch<F, 32>(a, st);
-  if (qf_smem<F, 16>(a.n) <= QF_SMEM_PAIR) return qf_launch<F, 16>(a, st);
-  if (qf_smem<F, 8>(a.n) <= QF_SMEM_PAIR) return qf_launch<F, 8>(a, st);
+  // widest block of samples that fits (S = 32: one slot per warp, conflict-free gathers)
   if (qf_smem<F, 32>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 32>(a, st);
   if (qf_smem<F, 16>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 16>(a, st);
   if (qf_smem<F, 8>(a.n) <= QF_SMEM_CAP) return qf_launch<F, 8>(a, st);
@@ -262,10 +352,13 @@ template <typename F> static int qf_create_t(gl_quadform *q, const void *A, doub
   cudaFree(tmp);
   if (e != cudaSuccess) return fail(GL_E_CUDA, "quadform compaction failed: %s", cudaGetErrorString(e));
   q->nnz = total;
-  GL_CUDA(cudaMalloc(&q->idx, sizeof(int2) * (size_t)total));
-  GL_CUDA(cudaMalloc(&q->val, sizeof(F) * (size_t)total));
-  qf_fill_kernel<F><<<grid, wpb * 32, 0, st>>>(static_cast<const F *>(A), q->K, q->n, (F)diag_add, q->rowoff, q->idx,
-                                              static_cast<F *>(q->val));
+  GL_CUDA(cudaMalloc(&q->ent, sizeof(QfEntry<F>) * ((size_t)total + 2)));   // + slack for the last 16-byte piece
+  qf_fill_kernel<F><<<grid, wpb * 32, 0, st>>>(static_cast<const F *>(A), q->K, q->n, (F)diag_add, q->rowoff,
+                                              static_cast<QfEntry<F> *>(q->ent));
+  GL_LAUNCH_CHECK();
+  const int nb = q->K * (QF_MAX_SLOTS + 1);
+  GL_CUDA(cudaMalloc(&q->bounds, sizeof(int32_t) * (size_t)nb));
+  qf_bounds_kernel<<<(nb + 255) / 256, 256, 0, st>>>(q->rowoff, q->K, q->n, q->bounds);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }
@@ -295,8 +388,8 @@ extern "C" int gl_quadform_create(gl_quadform **out, const void *A_dev, int K, i
 extern "C" int gl_quadform_destroy(gl_quadform *q) {
   if (q == nullptr) return GL_OK;
   cudaFree(q->rowoff);
-  cudaFree(q->idx);
-  cudaFree(q->val);
+  cudaFree(q->ent);
+  cudaFree(q->bounds);
   delete q;
   return GL_OK;
 }
@@ -311,6 +404,6 @@ extern "C" int gl_quadform_apply(gl_quadform *q, const void *X_dev, int64_t m, i
   if (m == 0) return GL_OK;
   if (Q_dev == nullptr) return fail(GL_E_ARG, "Q_out is null");
   if ((U_dev == nullptr) != (D_dev == nullptr)) return fail(GL_E_ARG, "U and D_out go together");
-  QfArgs a{X_dev, m, ldx, q->n, q->K, q->rowoff, q->idx, q->val, shift_dev, U_dev, Q_dev, D_dev, labels_dev};
+  QfArgs a{X_dev, m, ldx, q->n, q->K, q->bounds, q->ent, shift_dev, U_dev, Q_dev, D_dev, labels_dev};
   return q->dtype == GL_F32 ? qf_apply_t<float>(a, as_stream(stream)) : qf_apply_t<double>(a, as_stream(stream));
 }

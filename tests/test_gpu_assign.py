@@ -83,7 +83,7 @@ def test_glmm_log_prob_device_eigh_matches_oracle():
 
 @pytest.mark.parametrize("dtype,tol", [("float64", 1e-12), ("float32", 2e-5)])
 @pytest.mark.parametrize("K,n,m", [(1, 2, 1), (3, 33, 100), (8, 300, 1000), (2, 1000, 257), (2, 1800, 40),
-                                   (2, 3100, 70), (1, 3500, 9)])
+                                   (2, 3100, 70), (1, 3002, 9)])
 def test_matches_oracle(asg, dtype, tol, K, n, m):
     """Sizes walk the samples-per-CTA ladder (32 / 16 / 8 / 4 by shared-memory footprint) and ragged
     last blocks; shift and dot vectors on."""
