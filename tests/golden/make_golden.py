@@ -109,6 +109,15 @@ def logmodel_fit():
         )
 
 
+def config1():
+    """BASELINE.json configs[0]: LogModel on synthetic smooth signals, n = 100 nodes, m = 1,000 signals,
+    fp64, with the unmodified reference.  The signals are rounded to float32 values first so that the
+    float32 path sees the very same inputs (and the fixture compresses)."""
+    x = rgg_signals_exact(100, 1000, seed=0).astype(np.float32).astype(np.float64)
+    mdl = LogModel(avg_degree=8).fit(x)
+    save("config1_n100", x=x.astype(np.float32), avg_degree=8, theta=mdl.theta_, weights=mdl.weights_)
+
+
 def theta_cases():
     rng = np.random.default_rng(3)
     n = 40

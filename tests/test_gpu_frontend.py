@@ -166,6 +166,30 @@ def test_logmodel_fit_golden(golden, sl, tag):
     assert rel(m32.weights_, g["weights"]) < 1e-4
 
 
+def test_config1_logmodel_fit(golden, sl):
+    """BASELINE.json configs[0]: n = 100 nodes, m = 1,000 signals against the unmodified reference:
+    fp64 within 1e-9 on the weights with the reference's iteration count (683, pinned through the
+    oracle in tests/test_oracle.py), fp32 within 1e-4 with identical support outside a 1e-5 band
+    around edge_tol (north_star tolerances)."""
+    g = golden("config1_n100")
+    x = g["x"].astype(np.float64)
+    ref = g["weights"]
+    mdl = sl.LogModel(avg_degree=int(g["avg_degree"])).fit(x)
+    assert abs(mdl.theta_ - float(g["theta"])) < 1e-12 * float(g["theta"])
+    assert rel(mdl.weights_, ref) < 1e-9
+    assert np.array_equal(mdl.weights_ > 0, ref > 0)
+    z = sl.pdist_sq(x) * mdl.theta_
+    _, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, return_info=True)
+    assert info.converged and info.n_iter == 683
+    for method in ("gram", "direct"):
+        z32 = sl.pdist_sq(g["x"], dtype="float32", method=method)
+        th32 = sl._theta_packed(z32, 100, int(g["avg_degree"]))
+        w32 = sl.gsp_learn_graph_log_degrees(z32 * th32, 1, 1, dtype="float32").cpu().numpy()
+        assert rel(w32, ref) < 1e-4
+        band = np.abs(ref - 1e-3) > 1e-5
+        assert np.array_equal((w32 > 0)[band], (ref > 0)[band])
+
+
 def test_logmodel_sklearn_protocol(sl):
     from sklearn.base import clone
     mdl = sl.LogModel(avg_degree=4, maxit=10)

@@ -167,3 +167,16 @@ def test_assignment_step(golden):
     assert rel(orc.smoothness(g["x"], g["dense"]), g["smoothness_dense"]) < 1e-13
     lp = orc.glmm_log_prob(g["x"], g["glmm_laplacians"], g["glmm_means"], float(g["regul"]))
     assert rel(lp, g["log_prob"]) < 1e-12
+
+
+def test_config1_logmodel(golden):
+    """BASELINE.json configs[0] (n = 100, m = 1,000, fp64) against the unmodified reference's fit."""
+    g = golden("config1_n100")
+    x = g["x"].astype(np.float64)
+    z = orc.pdist_sq(x)
+    theta = orc.theta_for_degree(orc.to_square(z), int(g["avg_degree"]))
+    assert abs(theta - float(g["theta"])) < 1e-13 * theta
+    for solve in (orc.solve_two_pass, orc.solve_one_pass):
+        w, info = solve(z * theta)
+        assert info.converged and info.n_iter == 683
+        assert rel(orc.to_square(w), g["weights"]) < 1e-11
