@@ -20,8 +20,9 @@
 
 namespace gl {
 
-// One-shot solve = the stepwise solver on a single shard [0, npad) with the stop rule fused into the
-// node kernel: 2 launches per iteration, replayed from a CUDA graph, stop flag polled between replays.
+// One-shot solve = the stepwise solver on a single shard [0, npad) in its one-launch form (slot sweep,
+// node update and stop rule in knn_fused_kernel), replayed from a CUDA graph, stop flag polled between
+// replays.
 static int knn_solve(const int32_t *ei, const int32_t *ej, const void *z, int64_t nnz, int n, int dtype, double alpha,
                      double beta, int maxit, double tol, double step_size, double edge_tol, void *w, int *n_iter,
                      double *rel_primal, double *rel_dual, cudaStream_t st) {
@@ -30,7 +31,13 @@ static int knn_solve(const int32_t *ei, const int32_t *ej, const void *z, int64_
   gl_knn_solver *k = nullptr;
   const int npad = tiles_per_side(n) * T;
   GL_TRY(gl_knn_create(&k, ei, ej, z, w, nnz, n, dtype, 0, npad, npad, st));
-  gl_knn_set_fused(k, 1);
+  {
+    const int frc = gl_knn_set_fused(k, 2);   // whole iteration in one launch
+    if (frc != GL_OK) {
+      gl_knn_destroy(k);
+      return frc;
+    }
+  }
   int *h_flags = nullptr;
   cudaGraphExec_t gexec = nullptr;
   cudaStream_t cs = nullptr;

@@ -199,6 +199,162 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_sell_kernel(const int32_t *__
   }
 }
 
+// Whole iteration in ONE launch (single shard).  Because a lane owns ALL slots of its row, the row's
+// degree sums S p and S w' are complete inside that lane when its slice ends, so the node update of
+// smooth_learning.py:148-164 for that node follows at once: no (S p, S w') round trip through memory, no
+// node kernel, no second launch.  The other rows still gather the OLD (gamma d, gamma pb) pairs during
+// this sweep, so the pairs are double-buffered (ab_in / ab_out swap every iteration).  Residual sums:
+// per-CTA partials, combined in a fixed order by the last CTA (ticket), which applies the stop rule.
+template <typename F> struct KnnFusedArgs {
+  const int32_t *dst;
+  const F *z;
+  F *w;
+  const long long *slice_off;
+  int nslices, n, maxit;
+  const typename Vec2<F>::type *ab_in;
+  typename Vec2<F>::type *ab_out;
+  double *d, *yb, *pb;
+  double *part;          // [gridDim.x][4]
+  double *gprev, *resid;
+  int *flags;
+  F c, tgz;
+  double gamma, four_ag, tol;
+};
+
+template <typename F>
+__global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused_kernel(const KnnFusedArgs<F> A) {
+  if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
+  __shared__ double s_red[KNN_THREADS / 32][4];
+  __shared__ int s_last;
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  const int32_t *__restrict__ dst = A.dst;
+  const F *__restrict__ z = A.z;
+  F *__restrict__ w = A.w;
+  const typename Vec2<F>::type *__restrict__ ab = A.ab_in;
+  const F c = A.c, tgz = A.tgz;
+  double res = 0.0, wsq = 0.0, rb2 = 0.0, d2 = 0.0;
+  const int warps = gridDim.x * (KNN_THREADS / 32);
+  for (int s = blockIdx.x * (KNN_THREADS / 32) + wp; s < A.nslices; s += warps) {
+    const long long base = A.slice_off[s] + lane, end = A.slice_off[s + 1];
+    const int me = s * 32 + lane;
+    const typename Vec2<F>::type abi = ab[me];
+    const bool live = me < A.n;
+    // node state of this row: issued now, consumed after the slice
+    const double dv = live ? A.d[me] : 0.0, ybv = live ? A.yb[me] : 0.0, pbv = live ? A.pb[me] : 0.0;
+    double acc_p = 0.0, acc_w = 0.0;
+    int j[KNN_UNROLL], jn[KNN_UNROLL];
+    F wo[KNN_UNROLL], zz[KNN_UNROLL], won[KNN_UNROLL], zzn[KNN_UNROLL];
+    auto fetch = [&](long long p0, int *jj, F *ww, F *zv) {
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u) {
+        const long long p = p0 + 32LL * u;
+        const bool in = p < end;
+        jj[u] = in ? dst[p] : -1;
+        ww[u] = in ? w[p] : F(0);
+        zv[u] = in ? z[p] : F(0);
+      }
+    };
+    fetch(base, j, wo, zz);
+    for (long long p0 = base; p0 < end; p0 += 32LL * KNN_UNROLL) {
+      typename Vec2<F>::type abj[KNN_UNROLL];
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u) abj[u] = ab[j[u] < 0 ? me : j[u]];   // far end: one gather
+      fetch(p0 + 32LL * KNN_UNROLL, jn, won, zzn);
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u)
+        if (j[u] >= 0) {
+          const F y = c * wo[u] - (abi.x + abj[u].x);
+          F pv = y - tgz * zz[u];
+          pv = pv > F(0) ? pv : F(0);
+          const F q = c * pv - (abi.y + abj[u].y);
+          const F r = q - y;
+          const F wn = (wo[u] - y) + q;
+          w[p0 + 32LL * u] = wn;
+          acc_p += (double)pv;
+          acc_w += (double)wn;
+          res += (double)r * (double)r;
+          wsq += (double)wn * (double)wn;
+        }
+#pragma unroll
+      for (int u = 0; u < KNN_UNROLL; ++u) {
+        j[u] = jn[u];
+        wo[u] = won[u];
+        zz[u] = zzn[u];
+      }
+    }
+    // ---- node update of row `me` (the arithmetic of knn_node_kernel) -----------------------------------
+    typename Vec2<F>::type pr;
+    pr.x = pr.y = F(0);
+    if (live) {
+      const double qb = pbv + A.gamma * acc_p;                    //                      :154
+      const double rbv = qb - ybv;
+      const double dn = (dv - ybv) + qb;                          //                      :164
+      const double ybn = dn + A.gamma * acc_w;                    //                      :148
+      const double pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;   //                  :151
+      rb2 += rbv * rbv;
+      d2 += dn * dn;
+      A.d[me] = dn;
+      A.yb[me] = ybn;
+      A.pb[me] = pbn;
+      pr.x = (F)(A.gamma * dn);
+      pr.y = (F)(A.gamma * pbn);
+    }
+    A.ab_out[me] = pr;
+  }
+  res = warp_sum(res);
+  wsq = warp_sum(wsq);
+  rb2 = warp_sum(rb2);
+  d2 = warp_sum(d2);
+  if (lane == 0) {
+    s_red[wp][0] = res;
+    s_red[wp][1] = wsq;
+    s_red[wp][2] = rb2;
+    s_red[wp][3] = d2;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int q = 0; q < KNN_THREADS / 32; ++q)
+      for (int i = 0; i < 4; ++i) t[i] += s_red[q][i];
+    for (int i = 0; i < 4; ++i) A.part[4 * blockIdx.x + i] = t[i];
+    __threadfence();
+    const int ticket = atomicAdd(A.flags + FLAG_EDGE_TICKET, 1);
+    s_last = (ticket == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // ---- last CTA: fixed-order sums over the CTAs, stop rule (smooth_learning.py:156-166) --------------
+  double t[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += KNN_THREADS)
+    for (int q = 0; q < 4; ++q) t[q] += __ldcg(A.part + 4 * i + q);
+  for (int q = 0; q < 4; ++q) t[q] = warp_sum(t[q]);
+  __syncthreads();
+  if (lane == 0)
+    for (int q = 0; q < 4; ++q) s_red[wp][q] = t[q];
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  for (int q = 0; q < 4; ++q) t[q] = 0.0;
+  for (int v = 0; v < KNN_THREADS / 32; ++v)
+    for (int q = 0; q < 4; ++q) t[q] += s_red[v][q];
+  const double g_r = 0.5 * t[0], g_w = 0.5 * t[1];   // every undirected edge appears in two slots
+  A.flags[FLAG_EDGE_TICKET] = 0;
+  const int it = A.flags[FLAG_IT];
+  bool conv = false;
+  if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+    const double rp = sqrt(g_r) / sqrt(A.gprev[0]);
+    const double rd = sqrt(t[2]) / sqrt(A.gprev[1]);
+    A.resid[0] = rp;
+    A.resid[1] = rd;
+    conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
+  }
+  A.flags[FLAG_IT] = it + 1;
+  if (conv) A.flags[FLAG_CONVERGED] = 1;
+  if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
+  A.gprev[0] = g_w;   // denominators of the next check: the iterate before the update (:157-159)
+  A.gprev[1] = t[3];
+}
+
 // Node phase of the kNN path (single graph, single GPU): the arithmetic of node_tail.cu for K == 1
 // (smooth_learning.py:148-166) as a grid-stride kernel -- a few hundred CTAs however large n is,
 // several independent nodes in flight per thread -- because one CTA per 256 nodes (3,907 CTAs at

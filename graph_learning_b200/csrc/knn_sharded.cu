@@ -25,6 +25,10 @@ struct gl_knn_solver {
   int nslices = 0;
   long long total = 0;              // entries incl. padding
   int fused = 0;                    // 1: single shard, the node kernel applies the stop rule itself
+                                    // 2: single shard, whole iteration in one launch (knn_fused_kernel)
+  void *ab2 = nullptr;              // fused == 2: second (a, b) buffer, roles swap every iteration
+  double *part = nullptr;           // fused == 2: [CTAs][4] residual partials
+  int parity = 0;                   // fused == 2: which buffer the next iteration READS
   double *scal = nullptr;      // [4] partial sums for the exchange
 };
 
@@ -163,6 +167,38 @@ template <typename F> static int knn_slot_launch(gl_knn_solver *k, bool init, cu
   return GL_OK;
 }
 
+constexpr int KNN_FUSED_MAX_GRID = 148 * 8;
+
+template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t st) {
+  gl_solver *s = k->s;
+  using V = typename Vec2<F>::type;
+  KnnFusedArgs<F> A;
+  A.dst = k->dst;
+  A.z = (const F *)k->zs;
+  A.w = (F *)k->ws;
+  A.slice_off = k->slice_off;
+  A.nslices = k->nslices;
+  A.n = s->n;
+  A.maxit = s->maxit;
+  A.ab_in = (const V *)(k->parity ? k->ab2 : s->ab);
+  A.ab_out = (V *)(k->parity ? s->ab : k->ab2);
+  A.d = s->d; A.yb = s->yb; A.pb = s->pb;
+  A.part = k->part;
+  A.gprev = s->gprev;
+  A.resid = s->resid;
+  A.flags = s->flags;
+  A.c = (F)s->c;
+  A.tgz = (F)(2.0 * s->gamma);
+  A.gamma = s->gamma;
+  A.four_ag = 4.0 * s->alpha * s->gamma;
+  A.tol = s->tol;
+  const int grid = std::max(1, std::min((k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32), KNN_FUSED_MAX_GRID));
+  knn_fused_kernel<F><<<grid, KNN_THREADS, 0, st>>>(A);
+  GL_LAUNCH_CHECK();
+  k->parity ^= 1;
+  return GL_OK;
+}
+
 template <typename F> static int knn_node_launch(gl_knn_solver *k, bool init, cudaStream_t st) {
   gl_solver *s = k->s;
   KnnNodeArgs A;
@@ -247,7 +283,8 @@ extern "C" int gl_knn_create(gl_knn_solver **out, const int32_t *ei, const int32
 
 extern "C" int gl_knn_destroy(gl_knn_solver *k) {
   if (!k) return GL_OK;
-  for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal})
+  for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal, k->ab2,
+                  (void *)k->part})
     if (q) cudaFree(q);
   if (k->s) gl_solver_destroy(k->s);
   delete k;
@@ -274,17 +311,22 @@ extern "C" int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double 
     GL_TRY(knn_node_launch<double>(k, true, st));
   }
   s->begun = true;
+  k->parity = 0;  // the init node step wrote buffer 0
   return GL_OK;   // caller: exchange ab / scalars, then gl_knn_decide(k, 1, stream)
 }
 
 extern "C" int gl_knn_edge_step(gl_knn_solver *k, void *stream) {
   if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
+  if (k->fused == 2)
+    return k->dtype == GL_F32 ? knn_fused_launch<float>(k, as_stream(stream))
+                              : knn_fused_launch<double>(k, as_stream(stream));
   return k->dtype == GL_F32 ? knn_slot_launch<float>(k, false, as_stream(stream))
                             : knn_slot_launch<double>(k, false, as_stream(stream));
 }
 
 extern "C" int gl_knn_node_step(gl_knn_solver *k, void *stream) {
   if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
+  if (k->fused == 2) return GL_OK;   // the node update ran inside the edge step
   return k->dtype == GL_F32 ? knn_node_launch<float>(k, false, as_stream(stream))
                             : knn_node_launch<double>(k, false, as_stream(stream));
 }
@@ -330,6 +372,18 @@ extern "C" int gl_knn_store(gl_knn_solver *k, void *w_out, double edge_tol, void
 // single shard with the stop rule fused into the node kernel (what the one-shot solve uses)
 extern "C" int gl_knn_set_fused(gl_knn_solver *k, int fused) {
   if (!k) return fail(GL_E_ARG, "null solver");
-  k->fused = fused ? 1 : 0;
+  if (fused < 0 || fused > 2) return fail(GL_E_ARG, "fused must be 0, 1 or 2");
+  if (fused == 2) {
+    if (k->row_begin != 0 || k->row_end != k->s->npad)
+      return fail(GL_E_STATE, "the one-launch iteration needs a single shard owning all rows");
+    if (k->s->begun) return fail(GL_E_STATE, "choose the mode before gl_knn_begin");
+    const size_t esz = k->dtype == GL_F32 ? 4 : 8;
+    if (!k->ab2) {
+      GL_CUDA(cudaMalloc(&k->ab2, 2 * esz * (size_t)k->ab_len));
+      GL_CUDA(cudaMemset(k->ab2, 0, 2 * esz * (size_t)k->ab_len));
+    }
+    if (!k->part) GL_CUDA(cudaMalloc((void **)&k->part, sizeof(double) * 4 * KNN_FUSED_MAX_GRID));
+  }
+  k->fused = fused;
   return GL_OK;
 }

@@ -241,7 +241,9 @@ int gl_knn_create(gl_knn_solver **out, const int32_t *ei_dev, const int32_t *ej_
                   int row_end, int64_t ab_len, void *stream);
 int gl_knn_destroy(gl_knn_solver *k);
 int64_t gl_knn_local_slots(gl_knn_solver *k);
-/* Single shard only: let the node step apply the stop rule itself (gl_knn_decide becomes a no-op). */
+/* Single shard only.  1: the node step applies the stop rule itself (gl_knn_decide becomes a no-op).
+ * 2: the whole iteration -- slot sweep, node update, stop rule -- runs inside gl_knn_edge_step as ONE
+ * launch (gl_knn_node_step and gl_knn_decide become no-ops); choose before gl_knn_begin. */
 int gl_knn_set_fused(gl_knn_solver *k, int fused);
 int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
                  int dmax, void *stream);
