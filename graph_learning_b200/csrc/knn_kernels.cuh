@@ -37,11 +37,13 @@ static __global__ void knn_max_kernel(const int *cnt, int n, int *out) {
 // undirected list -> unsorted directed slots (key = source node, value = undirected edge id)
 // Slots whose source lies outside [row_begin, row_end) (another shard's rows) get the sentinel key n,
 // sort to the end and are dropped; *count receives the number of local slots.
+// lab (nullable): node relabelling old -> new (single full-range shard: rows sorted by degree).
 static __global__ void knn_expand_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, int32_t *key, int32_t *val,
-                                  int row_begin, int row_end, int n, unsigned long long *count) {
+                                  int row_begin, int row_end, int n, unsigned long long *count,
+                                  const int32_t *lab) {
   unsigned long long mine = 0;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
-    const int i = ei[e], j = ej[e];
+    const int i = lab ? lab[ei[e]] : ei[e], j = lab ? lab[ej[e]] : ej[e];
     const bool oi = i >= row_begin && i < row_end, oj = j >= row_begin && j < row_end;
     key[2 * e] = oi ? i : n;
     val[2 * e] = (int32_t)e;
@@ -52,6 +54,16 @@ static __global__ void knn_expand_kernel(const int32_t *ei, const int32_t *ej, i
   mine = warp_sum(mine);
   if ((threadIdx.x & 31) == 0 && mine) atomicAdd(count, mine);
 }
+// Degree-sorted relabelling (single full-range shard only).  A slice is as wide as its longest row, so
+// rows of similar degree should share a slice: the nodes are renumbered in order of decreasing degree.
+// The caller only ever sees per-EDGE results, so the renumbering stays internal (node vectors, dst).
+static __global__ void knn_iota_kernel(int32_t *v, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) v[i] = i;
+}
+static __global__ void knn_invert_kernel(const int32_t *order, int n, int32_t *lab) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) lab[order[i]] = i;
+}
+
 // ---- sliced-ELL layout of the directed slots (SELL-32) ----------------------------------------------
 // Rows (= source nodes, local index r = node - row_begin) are grouped into slices of 32 consecutive
 // rows; slice s stores width[s] = max degree of its rows "columns" of 32 entries each, column-major:
@@ -79,9 +91,11 @@ static __global__ void knn_slice_size_kernel(const int *cnt, int rows, int nslic
 template <typename F>
 __global__ void knn_sell_fill_kernel(const int32_t *ei, const int32_t *ej, const F *z, const F *w, int64_t nslots,
                                      const int32_t *src, const int32_t *eid, int row_begin, const int *row_ptr,
-                                     const long long *slice_off, int32_t *dst_s, F *z_s, F *w_s, int32_t *eid_canon) {
+                                     const long long *slice_off, int32_t *dst_s, F *z_s, F *w_s, int32_t *eid_canon,
+                                     const int32_t *lab) {
   for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nslots; s += (int64_t)gridDim.x * blockDim.x) {
-    const int32_t e = eid[s], i = ei[e], j = ej[e], me = src[s];
+    const int32_t e = eid[s], me = src[s];
+    const int32_t i = lab ? lab[ei[e]] : ei[e], j = lab ? lab[ej[e]] : ej[e];
     const int r = me - row_begin;
     const int t = (int)(s - row_ptr[r]);
     const long long pos = slice_off[r >> 5] + 32LL * t + (r & 31);

@@ -41,12 +41,14 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
   const int n = k->s->n;
   if (nnz == 0) return GL_OK;
   int32_t *key_in = nullptr, *val_in = nullptr, *src_all = nullptr, *eid_all = nullptr;
+  int32_t *lab = nullptr, *deg = nullptr, *deg_sorted = nullptr, *ids = nullptr, *order = nullptr;
   unsigned long long *count = nullptr;
-  void *tmp = nullptr;
+  void *tmp = nullptr, *tmp0 = nullptr;
   F *w_zero = nullptr;
   int rc = GL_OK;
   auto cleanup = [&]() {
-    for (void *q : {(void *)key_in, (void *)val_in, (void *)src_all, (void *)eid_all, (void *)count, tmp, (void *)w_zero})
+    for (void *q : {(void *)key_in, (void *)val_in, (void *)src_all, (void *)eid_all, (void *)count, tmp, (void *)w_zero,
+                    (void *)lab, (void *)deg, (void *)deg_sorted, (void *)ids, (void *)order, tmp0})
       if (q) cudaFree(q);
   };
 #define KS_CUDA(expr)                                                                                      \
@@ -65,7 +67,27 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
   KS_CUDA(cudaMalloc((void **)&count, sizeof(unsigned long long)));
   KS_CUDA(cudaMemsetAsync(count, 0, sizeof(unsigned long long), st));
   const int grid = (int)std::min<int64_t>((nnz + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
-  knn_expand_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, key_in, val_in, k->row_begin, k->row_end, n, count);
+  if (k->row_begin == 0 && k->row_end >= k->s->npad) {
+    // single shard owning every row: renumber the nodes by decreasing degree (SELL padding -> ~0)
+    const size_t nb = sizeof(int32_t) * ((size_t)n + 1);
+    KS_CUDA(cudaMalloc((void **)&lab, nb));
+    KS_CUDA(cudaMalloc((void **)&deg, nb));
+    KS_CUDA(cudaMalloc((void **)&deg_sorted, nb));
+    KS_CUDA(cudaMalloc((void **)&ids, nb));
+    KS_CUDA(cudaMalloc((void **)&order, nb));
+    KS_CUDA(cudaMemsetAsync(deg, 0, nb, st));
+    const int ngrid = std::min((n + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+    knn_degree_count_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, deg);
+    knn_iota_kernel<<<ngrid, KNN_THREADS, 0, st>>>(ids, n);
+    size_t t0b = 0;
+    KS_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, t0b, deg, deg_sorted, ids, order, n, 0, 32, st));
+    KS_CUDA(cudaMalloc(&tmp0, t0b ? t0b : 16));
+    KS_CUDA(cub::DeviceRadixSort::SortPairsDescending(tmp0, t0b, deg, deg_sorted, ids, order, n, 0, 32, st));
+    knn_invert_kernel<<<ngrid, KNN_THREADS, 0, st>>>(order, n, lab);
+    g_launches.fetch_add(3);
+    KS_CUDA(cudaGetLastError());
+  }
+  knn_expand_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, key_in, val_in, k->row_begin, k->row_end, n, count, lab);
   g_launches.fetch_add(1);
   int bits = 1;
   while (bits < 31 && ((int64_t)1 << bits) <= (int64_t)n) ++bits;   // the sentinel key n must fit
@@ -138,7 +160,7 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
     const int sgrid = (int)std::min<int64_t>((k->nslots + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
     knn_sell_fill_kernel<F><<<sgrid, KNN_THREADS, 0, st>>>(ei, ej, z, w_init, k->nslots, src_all, eid_all, k->row_begin,
                                                            row_ptr, k->slice_off, k->dst, (F *)k->zs, (F *)k->ws,
-                                                           k->eid_canon);
+                                                           k->eid_canon, lab);
     g_launches.fetch_add(1);
     KS2_CUDA(cudaGetLastError());
   }

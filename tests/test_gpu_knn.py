@@ -45,6 +45,45 @@ def test_knn_support_vs_oracle(n, k):
     assert w32.dtype == np.float32 and rel(w32, wo) < 1e-4
 
 
+@pytest.mark.parametrize("maxit", [1, 2, 15, 16, 17, 33, 100])
+def test_one_launch_iteration_any_iteration_count(maxit):
+    """The one-shot solve runs the whole iteration in one launch with double-buffered (a, b) pairs whose
+    roles are baked into a 16-iteration graph: odd counts, counts around the graph length and stops in
+    the middle of a replay must leave the same iterate as the oracle (raw weights, no threshold)."""
+    from graph_learning_b200.knn import gsp_learn_graph_log_degrees_knn as knn
+    n, k = 300, 6
+    rng = np.random.default_rng(7)
+    pts = rng.uniform(size=(n, 3))
+    zsq = ((pts[:, None] - pts[None]) ** 2).sum(-1)
+    ei, ej = orc.knn_support(zsq, k)
+    z = zsq[ei, ej] * (n ** (2 / 3))
+    wo, io = orc.solve_knn(ei, ej, z, n, maxit=maxit, tol=0.0, threshold=False)
+    w, info = knn(ei, ej, z, n, maxit=maxit, tol=0.0, edge_tol=-np.inf, return_info=True)
+    assert info.n_iter == io.n_iter == maxit
+    assert rel(w, wo) < 1e-12
+    if maxit > 1:
+        assert abs(info.rel_primal - io.rel_primal) < 1e-9 * io.rel_primal
+        assert abs(info.rel_dual - io.rel_dual) < 1e-9 * io.rel_dual
+
+
+def test_one_launch_mode_needs_a_single_shard():
+    import ctypes
+    import torch
+    from graph_learning_b200 import _native as nat
+    ei = torch.tensor([0, 1], dtype=torch.int32, device="cuda")
+    ej = torch.tensor([1, 2], dtype=torch.int32, device="cuda")
+    z = torch.ones(2, dtype=torch.float32, device="cuda")
+    h = ctypes.c_void_p()
+    nat.check(nat.lib().gl_knn_create(ctypes.byref(h), ei.data_ptr(), ej.data_ptr(), z.data_ptr(), None, 2, 300,
+                                      nat.GL_F32, 0, 128, 384, None))
+    try:
+        assert nat.lib().gl_knn_set_fused(h, 2) == nat.GL_E_STATE      # rows [0, 128) of 384
+        assert nat.lib().gl_knn_set_fused(h, 3) == nat.GL_E_ARG
+        assert nat.lib().gl_knn_set_fused(h, 1) == nat.GL_OK
+    finally:
+        nat.lib().gl_knn_destroy(h)
+
+
 def test_knn_warm_start_and_empty():
     from graph_learning_b200.knn import gsp_learn_graph_log_degrees_knn as knn
     rng = np.random.default_rng(5)
