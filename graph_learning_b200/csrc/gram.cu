@@ -317,6 +317,7 @@ struct GramArgs {
   const double *norms;    // (n_pad,)
   float *Z;
   int layout, n, nt, tile_begin, tile_end;
+  int debug;              // diagnostics only (GL_GRAM_DEBUG): 1 = skip the TMEM folds, 2 = skip the MMAs, 4 = 1 pair
 };
 
 template <int TERMS, int BN, int BK, bool SPLIT>
@@ -405,6 +406,7 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             uint32_t acc_main = kb > c * kb_per_chunk, acc_small = acc_main;
 #pragma unroll
             for (int p = 0; p < C::PAIRS; ++p) {
+              if ((args.debug & 2) || ((args.debug & 4) && p > 0)) continue;   // timing diagnostics (wrong results)
               const uint64_t da = smem_desc_kmajor<C::ROW_BYTES>(sa + pa[p] * C::A_PLANE);
               const uint64_t db = smem_desc_kmajor<C::ROW_BYTES>(sb + pb[p] * C::B_PLANE);
               const bool to_small = SPLIT && p > 0;
@@ -451,7 +453,9 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         mbar_wait(&acc_full[ab], aph);
         tc_fence_after();
         const uint32_t taddr = tmem_base + lane_sel + (uint32_t)(ab * BN + cb * CPW);
-        if (SPLIT) {
+        if (args.debug & 1) {
+          // timing diagnostic: hand the buffer back without reading it (wrong results)
+        } else if (SPLIT) {
 #pragma unroll
           for (int g = 0; g < CPW / 8; ++g) {
             float v[8], vs[8];
@@ -757,6 +761,10 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   a.nt = nt;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
+  {
+    const char *dbg = getenv("GL_GRAM_DEBUG");   // timing diagnostics of the pipeline stages; results are wrong
+    a.debug = dbg ? atoi(dbg) : 0;
+  }
   // variant: 0 = split accumulators (precise, default), 128-wide units, 32-sample k-blocks (SWIZZLE_64B)
   //          1 = same with 64-sample k-blocks (SWIZZLE_128B)
   //          2 / 3 = single accumulator, 256- / 128-wide units, 32-sample k-blocks
