@@ -263,8 +263,7 @@ int gl_solver_node_tail(gl_solver *s, void *stream) {
   if (!s || !s->begun) return fail(GL_E_STATE, "gl_solver_begin/begin_finish must be called first");
   cudaStream_t st = as_stream(stream);
   GL_TRY(launch_node_tail(s, false, st));
-  GL_TRY(launch_gram_edges(s, st));    // K > 1: no-ops unless the node tail asked for the exact norms
-  return launch_batch_decide(s, st);
+  return launch_gram_edges(s, st);    // K > 1: a no-op unless the node tail asked for the exact norms
 }
 
 void *gl_solver_comm_ptr(gl_solver *s, int64_t *n_bytes) {
@@ -373,7 +372,7 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   RUN_CUDA(cudaEventCreateWithFlags(&evs[0], cudaEventDisableTiming));
   RUN_CUDA(cudaEventCreateWithFlags(&evs[1], cudaEventDisableTiming));
 
-  const int per_iter = (s->ntl ? 1 : 0) + ((s->K > 1 && s->ntl) ? 2 : 0) + 1;
+  const int per_iter = (s->ntl ? 1 : 0) + ((s->K > 1 && s->ntl) ? 1 : 0) + 1;
   if (!persistent && (!s->graph_exec || s->graph_iters != poll_every)) {
     if (s->graph_exec) {
       cudaGraphExecDestroy(s->graph_exec);
@@ -386,7 +385,6 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
       rc = launch_edge_pass(s, st);
       if (rc == GL_OK) rc = launch_node_tail(s, false, st);
       if (rc == GL_OK) rc = launch_gram_edges(s, st);
-      if (rc == GL_OK) rc = launch_batch_decide(s, st);
     }
     cudaError_t ce = cudaStreamEndCapture(st, &graph);
     g_launches.store(before);  // capture records, it does not launch

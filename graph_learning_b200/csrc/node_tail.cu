@@ -366,8 +366,8 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   // Grams over the edge axis.  Only their diagonals are maintained every iteration (edge pass); with
   //   sigma_max(R)^2 >= max_k ||r_k||^2   and   sigma_max(W)^2 <= sum_k ||w_k||^2
   // rel_primal >= s_lo, so the stop rule is RULED OUT exactly whenever s_lo >= tol (or the dual
-  // ratio, exact here, is >= tol).  Otherwise FLAG_NEED hands the decision to gram_edges_kernel +
-  // batch_decide_kernel, which evaluate the exact norms: the decisions are those of the full rule.
+  // ratio, exact here, is >= tol).  Otherwise FLAG_NEED hands the decision to gram_edges_kernel, which
+  // forms the exact Grams and whose last CTA applies the rule: the decisions are those of the full rule.
   // The dual ratio is bounded the same way from the node-side Grams (exact and cheap, but their 26
   // squarings are not): the spectral norms are evaluated only when BOTH bounds fall below tol.
   const bool lazy = A.K > 1;
@@ -450,49 +450,15 @@ __global__ void __launch_bounds__(NODE_THREADS) node_tail_kernel(const NodeArgs 
   }
 }
 
-// K > 1, after gram_edges_kernel ran for real (FLAG_NEED): exact rel_primal from the spectral norms of
-// Gram(q - y) and Gram(w) of the previous iterate, then the reference's stop rule (:158-166).
+// K > 1, what the last CTA of gram_edges_kernel needs to decide (FLAG_NEED iterations): exact rel_primal
+// from the spectral norms of Gram(q - y) and Gram(w) of the previous iterate, then the reference's stop
+// rule (:158-166).
 struct DecideArgs {
   double *g_r, *g_w, *resid, *eig;
   int *flags;
   int K, maxit;
   double tol;
 };
-
-__global__ void __launch_bounds__(NODE_THREADS) batch_decide_kernel(const DecideArgs A) {
-  __shared__ double s_lam[4];
-  if (!*reinterpret_cast<volatile int *>(A.flags + FLAG_NEED)) return;
-  const int tid = threadIdx.x, KK = A.K * A.K;
-  const double *G[4] = {A.g_r, A.g_w, A.g_r, A.g_w};
-  lambda_max4(G, A.K, A.eig, s_lam);
-  __syncthreads();
-  for (int e = tid; e < 2 * KK; e += NODE_THREADS) A.g_r[e] = 0.0;   // g_w follows g_r: slots for the next pass
-  if (tid == 0) {
-    const double rp = sqrt(s_lam[0]) / sqrt(s_lam[1]), rd = A.resid[1];
-    A.resid[0] = rp;
-    const bool conv = (rp < A.tol) && (rd < A.tol);
-    A.flags[FLAG_NEED] = 0;
-    if (conv) A.flags[FLAG_CONVERGED] = 1;
-    if (conv || A.flags[FLAG_IT] >= A.maxit) A.flags[FLAG_DONE] = 1;
-  }
-}
-
-int launch_batch_decide(gl_solver *s, cudaStream_t st) {
-  if (s->K == 1 || s->ntl == 0) return GL_OK;
-  const int64_t total = (int64_t)s->K * s->npad;
-  DecideArgs A;
-  A.g_r = s->xch + 2 * total;
-  A.g_w = A.g_r + (int64_t)s->K * s->K;
-  A.resid = s->resid;
-  A.eig = s->eig_scratch;
-  A.flags = s->flags;
-  A.K = s->K;
-  A.maxit = s->maxit;
-  A.tol = s->tol;
-  batch_decide_kernel<<<1, NODE_THREADS, 0, st>>>(A);
-  GL_LAUNCH_CHECK();
-  return GL_OK;
-}
 
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
   NodeArgs A;
@@ -530,15 +496,18 @@ int launch_node_tail(gl_solver *s, bool init, cudaStream_t st) {
 // ---- batch mode: Gram matrices of R = Q - Y and of the previous iterate W = W' - R over the local edge
 // shard, only on the iterations whose stop decision needs them (FLAG_NEED, see node_tail_kernel).
 // 8 x 8 register-blocked; grid = (chunks, graph-block pairs kb <= lb, {R, W}).
-constexpr int GRAM_THREADS = 128;
+constexpr int GRAM_THREADS = NODE_THREADS;   // lambda_max4 in the deciding CTA is written for this block size
 constexpr int GB = 8;
 
 template <typename F>
 __global__ void __launch_bounds__(GRAM_THREADS) gram_edges_kernel(const F *r, const F *w, int64_t gstride,
-                                                                   int64_t len, int K, double *g_r,
-                                                                   double *g_w, const int *flags) {
+                                                                   int64_t len, int K, const DecideArgs D) {
+  int *flags = D.flags;
+  double *g_r = D.g_r, *g_w = D.g_w;
   if (!*reinterpret_cast<const volatile int *>(flags + FLAG_NEED)) return;
   __shared__ double s_acc[GRAM_THREADS / 32][GB * GB];
+  __shared__ int s_last;
+  __shared__ double s_lam[4];
   const int nb = (K + GB - 1) / GB;
   // decode pair index blockIdx.y -> (kb <= lb)
   int kb = 0, rem = blockIdx.y;
@@ -591,6 +560,30 @@ __global__ void __launch_bounds__(GRAM_THREADS) gram_edges_kernel(const F *r, co
       if (kb != lb) atomicAdd(g + (int64_t)l * K + k, v);
     }
   }
+  // ---- last CTA of the grid: the exact stop rule on the finished Grams ------------------------------
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int ctas = (int)(gridDim.x * gridDim.y * gridDim.z);
+    s_last = atomicAdd(flags + FLAG_EDGE_TICKET, 1) == ctas - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int KK = K * K;
+  const double *G[4] = {g_r, g_w, g_r, g_w};
+  lambda_max4(G, K, D.eig, s_lam);
+  __syncthreads();
+  for (int e = threadIdx.x; e < 2 * KK; e += GRAM_THREADS) g_r[e] = 0.0;   // g_w follows g_r: slots of the next pass
+  if (threadIdx.x == 0) {
+    const double rp = sqrt(s_lam[0]) / sqrt(s_lam[1]), rd = D.resid[1];
+    D.resid[0] = rp;
+    const bool conv = (rp < D.tol) && (rd < D.tol);
+    flags[FLAG_EDGE_TICKET] = 0;
+    flags[FLAG_NEED] = 0;
+    if (conv) flags[FLAG_CONVERGED] = 1;
+    if (conv || flags[FLAG_IT] >= D.maxit) flags[FLAG_DONE] = 1;
+  }
 }
 
 int launch_gram_edges(gl_solver *s, cudaStream_t st) {
@@ -604,15 +597,23 @@ int launch_gram_edges(gl_solver *s, cudaStream_t st) {
   if (chunks < 1) chunks = 1;
   dim3 grid(chunks, nb * (nb + 1) / 2, 2);
   const int64_t total = (int64_t)s->K * s->npad;
-  double *g_r = s->xch + 2 * total, *g_w = g_r + (int64_t)s->K * s->K;
+  DecideArgs D;
+  D.g_r = s->xch + 2 * total;
+  D.g_w = D.g_r + (int64_t)s->K * s->K;
+  D.resid = s->resid;
+  D.eig = s->eig_scratch;
+  D.flags = s->flags;
+  D.K = s->K;
+  D.maxit = s->maxit;
+  D.tol = s->tol;
   if (s->dtype == GL_F32)
     gram_edges_kernel<float><<<grid, GRAM_THREADS, 0, st>>>(static_cast<const float *>(s->r),
                                                            static_cast<const float *>(s->w), s->gstride,
-                                                           len, s->K, g_r, g_w, s->flags);
+                                                           len, s->K, D);
   else
     gram_edges_kernel<double><<<grid, GRAM_THREADS, 0, st>>>(static_cast<const double *>(s->r),
                                                             static_cast<const double *>(s->w), s->gstride,
-                                                            len, s->K, g_r, g_w, s->flags);
+                                                            len, s->K, D);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }

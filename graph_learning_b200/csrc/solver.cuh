@@ -77,7 +77,6 @@ int launch_edge_init(gl_solver *s, cudaStream_t st);
 int launch_signal(gl_solver *s, cudaStream_t st);
 int launch_gram_edges(gl_solver *s, cudaStream_t st);
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
-int launch_batch_decide(gl_solver *s, cudaStream_t st);
 int launch_persistent(gl_solver *s, int iters, cudaStream_t st);
 int fill_tile_table(gl_solver *s);
 }  // namespace gl
