@@ -224,8 +224,7 @@ __global__ void __launch_bounds__(QF_THREADS, 1) quadform_kernel(QfArgs a) {
       if (bfr < nbuf && pe < eend) cp_async16(ring + (bfr & 1) * RING + s * EPP, ent + pe);
       cp_async_commit();
     };
-    double q = 0.0;
-    F yi = F(0), accr = F(0);
+    F yi = F(0), acc[2] = {F(0), F(0)};
     issue(0);
     for (int bfr = 0; bfr < nbuf; ++bfr) {
       issue(bfr + 1);
@@ -248,13 +247,8 @@ __global__ void __launch_bounds__(QF_THREADS, 1) quadform_kernel(QfArgs a) {
         }
 #pragma unroll
         for (int u = 0; u < QF_UNROLL; ++u) {
-          if (en[u].j & QF_ROW_START) {       // diagonal entry: close the previous row, open this one
-            q += (double)yi * (double)accr;
-            yi = g[u];
-            accr = en[u].v * g[u];
-          } else {
-            accr += en[u].v * g[u];
-          }
+          yi = (en[u].j & QF_ROW_START) ? g[u] : yi;   // diagonal entry opens its row: y_i by select, no branch
+          acc[u & 1] += (en[u].v * g[u]) * yi;
         }
       }
       for (; e < hi; ++e) {
@@ -262,18 +256,13 @@ __global__ void __launch_bounds__(QF_THREADS, 1) quadform_kernel(QfArgs a) {
         const unsigned j = en.j & ~QF_ROW_START;
         F g = xs[(size_t)j * SP + s];
         if (SHIFT) g -= mus[j];
-        if (en.j & QF_ROW_START) {
-          q += (double)yi * (double)accr;
-          yi = g;
-          accr = en.v * g;
-        } else {
-          accr += en.v * g;
-        }
+        yi = (en.j & QF_ROW_START) ? g : yi;
+        acc[0] += (en.v * g) * yi;
       }
       __syncwarp(slot_mask);   // the buffer is refilled two steps from now
     }
     cp_async_wait0();
-    q += (double)yi * (double)accr;
+    const double q = (double)acc[0] + (double)acc[1];
     red[(size_t)slot * S + s] = q;
     if (dots) {
       F d = F(0);
