@@ -85,7 +85,6 @@ def _estimate_gauss_laplacian_parameters(
             theta_inv = torch.tensor([[_theta_packed(sq_dist[k], n_nodes, avg_degree)] for k in range(n_components)],
                                      dtype=sq_dist.dtype, device=sq_dist.device)
         else:
-            from .. import _native as nat
             iu = torch.triu_indices(n_nodes, n_nodes, 1, device=sq_dist.device)
             rows = []
             for k in range(n_components):

@@ -7,12 +7,10 @@ import json
 import os
 import sys
 
-import numpy as np
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import graph_learning_b200.smooth_learning as sl  # noqa: E402
-from graph_learning_b200 import _native as nat  # noqa: E402
 from graph_learning_b200.synthetic import rgg_signals_exact, rgg_signals_filtered  # noqa: E402
 
 
