@@ -764,6 +764,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   {
     const char *dbg = getenv("GL_GRAM_DEBUG");   // timing diagnostics of the pipeline stages; results are wrong
     a.debug = dbg ? atoi(dbg) : 0;
+    if (a.debug) fprintf(stderr, "gl_b200: GL_GRAM_DEBUG=%d -- timing diagnostics, the distances are WRONG\n", a.debug);
   }
   // variant: 0 = split accumulators (precise, default), 128-wide units, 32-sample k-blocks (SWIZZLE_64B)
   //          1 = same with 64-sample k-blocks (SWIZZLE_128B)
