@@ -63,6 +63,18 @@ static __global__ void knn_iota_kernel(int32_t *v, int n) {
 static __global__ void knn_invert_kernel(const int32_t *order, int n, int32_t *lab) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) lab[order[i]] = i;
 }
+// Windowed variant (SELL-C-sigma): `arr` lists the nodes in a locality-preserving arrangement (the
+// caller's numbering, or ascending order key); position p belongs to window p / sigma, and an
+// ascending stable sort of these keys orders every window by decreasing degree while the windows stay
+// where they are, so rows that share a slice are also close in the arrangement (their far ends fall
+// into a few KB of the (a, b) array instead of all of it).  sigma == 0: one window (global sort).
+static __global__ void knn_window_key_kernel(const int32_t *arr, const int *deg, int n, int sigma,
+                                             unsigned long long *key) {
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    const unsigned long long win = sigma > 0 ? (unsigned long long)(p / sigma) : 0ULL;
+    key[p] = (win << 32) | (unsigned long long)(0x7fffffffu - (unsigned)deg[arr[p]]);
+  }
+}
 
 // ---- sliced-ELL layout of the directed slots (SELL-32) ----------------------------------------------
 // Rows (= source nodes, local index r = node - row_begin) are grouped into slices of 32 consecutive

@@ -36,19 +36,21 @@ namespace gl {
 
 template <typename F>
 static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, const F *z, const F *w0,
-                        cudaStream_t st) {
+                        const int32_t *okey, int window, cudaStream_t st) {
   const int64_t nnz = k->nnz, all = 2 * nnz;
   const int n = k->s->n;
   if (nnz == 0) return GL_OK;
   int32_t *key_in = nullptr, *val_in = nullptr, *src_all = nullptr, *eid_all = nullptr;
   int32_t *lab = nullptr, *deg = nullptr, *deg_sorted = nullptr, *ids = nullptr, *order = nullptr;
-  unsigned long long *count = nullptr;
+  int32_t *okey_sorted = nullptr, *arr = nullptr;
+  unsigned long long *count = nullptr, *wkey = nullptr, *wkey_sorted = nullptr;
   void *tmp = nullptr, *tmp0 = nullptr;
   F *w_zero = nullptr;
   int rc = GL_OK;
   auto cleanup = [&]() {
     for (void *q : {(void *)key_in, (void *)val_in, (void *)src_all, (void *)eid_all, (void *)count, tmp, (void *)w_zero,
-                    (void *)lab, (void *)deg, (void *)deg_sorted, (void *)ids, (void *)order, tmp0})
+                    (void *)lab, (void *)deg, (void *)deg_sorted, (void *)ids, (void *)order, tmp0,
+                    (void *)okey_sorted, (void *)arr, (void *)wkey, (void *)wkey_sorted})
       if (q) cudaFree(q);
   };
 #define KS_CUDA(expr)                                                                                      \
@@ -80,9 +82,38 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
     knn_degree_count_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, deg);
     knn_iota_kernel<<<ngrid, KNN_THREADS, 0, st>>>(ids, n);
     size_t t0b = 0;
-    KS_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, t0b, deg, deg_sorted, ids, order, n, 0, 32, st));
-    KS_CUDA(cudaMalloc(&tmp0, t0b ? t0b : 16));
-    KS_CUDA(cub::DeviceRadixSort::SortPairsDescending(tmp0, t0b, deg, deg_sorted, ids, order, n, 0, 32, st));
+    if (!okey && window == 0) {
+      KS_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, t0b, deg, deg_sorted, ids, order, n, 0, 32, st));
+      KS_CUDA(cudaMalloc(&tmp0, t0b ? t0b : 16));
+      KS_CUDA(cub::DeviceRadixSort::SortPairsDescending(tmp0, t0b, deg, deg_sorted, ids, order, n, 0, 32, st));
+    } else {
+      // locality-preserving variants: arrange the nodes by the caller's order key (stable; none = the
+      // caller's numbering), then sort by decreasing degree inside windows of `window` positions
+      // (0: one window = global sort with the arrangement as tie order; < 0: arrangement only)
+      const int32_t *arrangement = ids;
+      if (okey) {
+        KS_CUDA(cudaMalloc((void **)&okey_sorted, nb));
+        KS_CUDA(cudaMalloc((void **)&arr, nb));
+        KS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, t0b, okey, okey_sorted, ids, arr, n, 0, 32, st));
+        KS_CUDA(cudaMalloc(&tmp0, t0b ? t0b : 16));
+        KS_CUDA(cub::DeviceRadixSort::SortPairs(tmp0, t0b, okey, okey_sorted, ids, arr, n, 0, 32, st));
+        KS_CUDA(cudaFree(tmp0));
+        tmp0 = nullptr;
+        arrangement = arr;
+      }
+      if (window < 0) {
+        KS_CUDA(cudaMemcpyAsync(order, arrangement, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+      } else {
+        const size_t kb = sizeof(unsigned long long) * ((size_t)n + 1);
+        KS_CUDA(cudaMalloc((void **)&wkey, kb));
+        KS_CUDA(cudaMalloc((void **)&wkey_sorted, kb));
+        knn_window_key_kernel<<<ngrid, KNN_THREADS, 0, st>>>(arrangement, deg, n, window, wkey);
+        g_launches.fetch_add(1);
+        KS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, t0b, wkey, wkey_sorted, arrangement, order, n, 0, 64, st));
+        KS_CUDA(cudaMalloc(&tmp0, t0b ? t0b : 16));
+        KS_CUDA(cub::DeviceRadixSort::SortPairs(tmp0, t0b, wkey, wkey_sorted, arrangement, order, n, 0, 64, st));
+      }
+    }
     knn_invert_kernel<<<ngrid, KNN_THREADS, 0, st>>>(order, n, lab);
     g_launches.fetch_add(3);
     KS_CUDA(cudaGetLastError());
@@ -266,6 +297,12 @@ extern "C" int gl_knn_max_degree(const int32_t *ei, const int32_t *ej, int64_t n
 
 extern "C" int gl_knn_create(gl_knn_solver **out, const int32_t *ei, const int32_t *ej, const void *z, const void *w0,
                              int64_t nnz, int n, int dtype, int row_begin, int row_end, int64_t ab_len, void *stream) {
+  return gl_knn_create_ordered(out, ei, ej, z, w0, nnz, n, dtype, row_begin, row_end, ab_len, nullptr, 0, stream);
+}
+
+extern "C" int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei, const int32_t *ej, const void *z,
+                                     const void *w0, int64_t nnz, int n, int dtype, int row_begin, int row_end,
+                                     int64_t ab_len, const int32_t *order_key, int sort_window, void *stream) {
   if (!out) return fail(GL_E_ARG, "null output");
   *out = nullptr;
   if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
@@ -293,8 +330,8 @@ extern "C" int gl_knn_create(gl_knn_solver **out, const int32_t *ei, const int32
     gl_knn_destroy(k);
     return fail(GL_E_ALLOC, "gl_knn_create: %s", cudaGetErrorString(e));
   }
-  rc = dtype == GL_F32 ? knn_create_t<float>(k, ei, ej, (const float *)z, (const float *)w0, st)
-                       : knn_create_t<double>(k, ei, ej, (const double *)z, (const double *)w0, st);
+  rc = dtype == GL_F32 ? knn_create_t<float>(k, ei, ej, (const float *)z, (const float *)w0, order_key, sort_window, st)
+                       : knn_create_t<double>(k, ei, ej, (const double *)z, (const double *)w0, order_key, sort_window, st);
   if (rc != GL_OK) {
     gl_knn_destroy(k);
     return rc;
@@ -314,6 +351,7 @@ extern "C" int gl_knn_destroy(gl_knn_solver *k) {
 }
 
 extern "C" int64_t gl_knn_local_slots(gl_knn_solver *k) { return k ? k->nslots : -1; }
+extern "C" int64_t gl_knn_padded_slots(gl_knn_solver *k) { return k ? (int64_t)k->total : -1; }
 
 extern "C" int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
                             int dmax, void *stream) {

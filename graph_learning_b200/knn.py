@@ -17,7 +17,42 @@ from sklearn.base import BaseEstimator
 
 from .smooth_learning import SolveInfo, _gl_dtype, _ptr, _stream, _theta_dense, _to_device, _torch_dtype
 
-__all__ = ["gsp_learn_graph_log_degrees_knn", "knn_search", "knn_graph", "theta_from_knn", "KNNLogModel"]
+__all__ = ["gsp_learn_graph_log_degrees_knn", "knn_search", "knn_graph", "theta_from_knn", "locality_keys",
+           "KNNLogModel"]
+
+
+def _part1by2(v: torch.Tensor) -> torch.Tensor:
+    """Spread the low 10 bits of v (int64) so that two zero bits follow each of them."""
+    v = v & 0x3FF
+    v = (v | (v << 16)) & 0x030000FF
+    v = (v | (v << 8)) & 0x0300F00F
+    v = (v | (v << 4)) & 0x030C30C3
+    v = (v | (v << 2)) & 0x09249249
+    return v
+
+
+def locality_keys(x) -> torch.Tensor:
+    """Morton (Z-order) codes of the nodes (COLUMNS of x, shape (m, n)) as non-negative int32, for the
+    ``order_key`` of :func:`gsp_learn_graph_log_degrees_knn`: nodes with close codes are close in
+    space, so rows that share a slice of the solver's layout have overlapping neighbourhoods.  The
+    three features of largest variance are quantised to 10 bits each (all of them when m <= 3); for
+    high-dimensional signals this is only a coarse arrangement.  Plain torch ops on x's device; the
+    codes steer an internal row order and never change a result."""
+    xt = x if isinstance(x, torch.Tensor) else torch.as_tensor(np.asarray(x))
+    if xt.ndim != 2:
+        raise ValueError("signals must be a (n_samples, n_nodes) matrix")
+    xt = xt.to(torch.float64)
+    m, n = xt.shape
+    if m > 3:
+        top = torch.argsort(xt.var(dim=1, unbiased=False), descending=True, stable=True)[:3]
+        xt = xt[torch.sort(top).values]
+    lo = xt.min(dim=1, keepdim=True).values
+    span = (xt.max(dim=1, keepdim=True).values - lo).clamp_min(torch.finfo(torch.float64).tiny)
+    q = torch.clamp(((xt - lo) / span * 1024.0).to(torch.int64), 0, 1023)
+    key = torch.zeros(n, dtype=torch.int64, device=xt.device)
+    for a in range(q.shape[0]):
+        key |= _part1by2(q[a]) << a
+    return key.to(torch.int32)
 
 
 def knn_search(x, k: int):
@@ -74,10 +109,16 @@ def theta_from_knn(d2_sorted: torch.Tensor, avg_degree: int) -> float:
 
 def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: float = 1.0, beta: float = 1.0,
                                     edge_init=None, maxit: int = 1000, tol: float = 1e-5, step_size: float = 0.5,
-                                    edge_tol: float = 1e-3, *, dtype=None, return_info: bool = False):
+                                    edge_tol: float = 1e-3, *, dtype=None, return_info: bool = False,
+                                    order_key=None, sort_window: int = 0):
     """Edge weights on the support {(ei[k], ej[k])}, ei < ej, from the (theta-scaled) squared
     distances of those edges.  Returns an array shaped like ``distances`` (NumPy in -> NumPy out).
-    Step size: gamma = step_size / (2 beta + sqrt(2 d_max)), d_max the largest support degree."""
+    Step size: gamma = step_size / (2 beta + sqrt(2 d_max)), d_max the largest support degree.
+
+    ``order_key`` ((n_nodes,) non-negative int32, e.g. :func:`locality_keys`) and ``sort_window``
+    choose the solver's INTERNAL row order (``gl_knn_create_ordered`` in include/gl_b200.h); the
+    defaults are the global degree sort.  They change memory locality, never the result beyond the
+    rounding of the degree sums' summation order."""
     is_np = not isinstance(distances, torch.Tensor)
     if dtype is None and getattr(distances, "dtype", None) in (np.float32, torch.float32):
         dtype = torch.float32
@@ -93,10 +134,23 @@ def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: floa
     w = torch.zeros_like(z) if edge_init is None else _to_device(edge_init, dt).clone()
     it = ctypes.c_int()
     rp, rd = ctypes.c_double(), ctypes.c_double()
-    nat.check(nat.lib().gl_knn_logmodel_solve(_ptr(i32), _ptr(j32), _ptr(z), z.numel(), int(n_nodes), _gl_dtype(dt),
-                                              float(alpha), float(beta), int(maxit), float(tol), float(step_size),
-                                              float(edge_tol), _ptr(w), ctypes.byref(it), ctypes.byref(rp),
-                                              ctypes.byref(rd), _stream()))
+    if order_key is None and int(sort_window) == 0:
+        nat.check(nat.lib().gl_knn_logmodel_solve(_ptr(i32), _ptr(j32), _ptr(z), z.numel(), int(n_nodes),
+                                                  _gl_dtype(dt), float(alpha), float(beta), int(maxit), float(tol),
+                                                  float(step_size), float(edge_tol), _ptr(w), ctypes.byref(it),
+                                                  ctypes.byref(rp), ctypes.byref(rd), _stream()))
+    else:
+        key = None
+        if order_key is not None:
+            key = torch.as_tensor(order_key, device=dev).to(torch.int32).contiguous()
+            if key.ndim != 1 or key.numel() != int(n_nodes):
+                raise ValueError("order_key must hold one key per node")
+            if key.numel() and int(key.min()) < 0:
+                raise ValueError("order_key must be non-negative")
+        nat.check(nat.lib().gl_knn_logmodel_solve_ordered(
+            _ptr(i32), _ptr(j32), _ptr(z), z.numel(), int(n_nodes), _gl_dtype(dt), float(alpha), float(beta),
+            int(maxit), float(tol), float(step_size), float(edge_tol), _ptr(w), ctypes.byref(it), ctypes.byref(rp),
+            ctypes.byref(rd), _ptr(key) if key is not None else None, int(sort_window), _stream()))
     info = SolveInfo(it.value, rp.value, rd.value, bool(rp.value < tol and rd.value < tol))
     out = w.cpu().numpy() if is_np else w
     return (out, info) if return_info else out
@@ -111,7 +165,10 @@ class KNNLogModel(BaseEstimator):
     ``n_iter_``; :meth:`to_sparse` gives the symmetric scipy CSR matrix."""
 
     def __init__(self, avg_degree: int = 10, n_neighbors: int = 20, *, maxit: int = 1000, tol: float = 1e-5,
-                 step_size: float = 0.5, edge_tol: float = 1e-3) -> None:
+                 step_size: float = 0.5, edge_tol: float = 1e-3, locality_order: bool = False,
+                 sort_window: int = 0) -> None:
+        self.locality_order = locality_order   # Morton arrangement of the rows (locality_keys)
+        self.sort_window = sort_window         # degree sort inside windows of this many rows (0: global)
         self.avg_degree = avg_degree
         self.n_neighbors = n_neighbors
         self.maxit = maxit
@@ -126,7 +183,9 @@ class KNNLogModel(BaseEstimator):
         self.theta_ = theta_from_knn(d2_lists, self.avg_degree)
         w, info = gsp_learn_graph_log_degrees_knn(ei, ej, d2 * self.theta_, self.n_nodes_, maxit=self.maxit,
                                                   tol=self.tol, step_size=self.step_size, edge_tol=self.edge_tol,
-                                                  return_info=True)
+                                                  return_info=True,
+                                                  order_key=locality_keys(x).to(d2.device) if self.locality_order
+                                                  else None, sort_window=self.sort_window)
         edges = torch.stack([ei, ej])
         self.edges_ = edges.cpu().numpy() if is_np else edges
         self.weights_ = w.cpu().numpy() if is_np else w

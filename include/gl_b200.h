@@ -239,8 +239,28 @@ int gl_knn_max_degree(const int32_t *ei_dev, const int32_t *ej_dev, int64_t nnz,
 int gl_knn_create(gl_knn_solver **out, const int32_t *ei_dev, const int32_t *ej_dev, const void *z_dev,
                   const void *w0_dev /* nullable: zeros */, int64_t nnz, int n, int dtype, int row_begin,
                   int row_end, int64_t ab_len, void *stream);
+/* Same with a choice of the INTERNAL row order of a single full-range shard (ignored otherwise; the
+ * caller never sees it: results are per edge of the caller's list).  By default the rows are sorted
+ * by decreasing degree over the whole node set (no SELL padding, but neighbouring rows are unrelated
+ * nodes, so every far-end gather of a warp touches its own sector).  order_key_dev (nullable, n
+ * int32 >= 0, e.g. Morton codes of the points the kNN lists were built from): the nodes are first
+ * arranged by ascending key (stable; null = the caller's numbering).  sort_window > 0: degree sort
+ * inside windows of that many consecutive positions of the arrangement (SELL-C-sigma: padding stays
+ * small and the far ends of a CTA's rows stay within a few KB of the (a, b) array); 0: one window
+ * (global sort, the arrangement only breaks ties); < 0: the arrangement as it is. */
+int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei_dev, const int32_t *ej_dev,
+                          const void *z_dev, const void *w0_dev, int64_t nnz, int n, int dtype,
+                          int row_begin, int row_end, int64_t ab_len, const int32_t *order_key_dev,
+                          int sort_window, void *stream);
+int gl_knn_logmodel_solve_ordered(const int32_t *ei_dev, const int32_t *ej_dev, const void *z_dev,
+                                  int64_t nnz, int n, int dtype, double alpha, double beta,
+                                  int maxit, double tol, double step_size, double edge_tol,
+                                  void *w_dev, int *n_iter, double *rel_primal, double *rel_dual,
+                                  const int32_t *order_key_dev, int sort_window, void *stream);
 int gl_knn_destroy(gl_knn_solver *k);
 int64_t gl_knn_local_slots(gl_knn_solver *k);
+/* entries of the SELL arrays including padding (gl_knn_local_slots counts the live ones) */
+int64_t gl_knn_padded_slots(gl_knn_solver *k);
 /* Single shard only.  1: the node step applies the stop rule itself (gl_knn_decide becomes a no-op).
  * 2: the whole iteration -- slot sweep, node update, stop rule -- runs inside gl_knn_edge_step as ONE
  * launch (gl_knn_node_step and gl_knn_decide become no-ops); choose before gl_knn_begin. */

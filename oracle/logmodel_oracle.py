@@ -386,6 +386,48 @@ def solve_knn(
     return w, SolveInfo(it, float(rp), float(rd), converged)
 
 
+def knn_row_order(ei, ej, n: int, order_key=None, sort_window: int = 0) -> np.ndarray:
+    """Internal row order of the kNN solver's sliced layout (include/gl_b200.h, gl_knn_create_ordered):
+    nodes arranged by ascending ``order_key`` (stable; None = their numbering), then sorted by
+    decreasing support degree inside windows of ``sort_window`` positions (0: one window; < 0: no
+    degree sort).  Returns ``order`` with order[p] = node stored in row p.  No reference code (A9)."""
+    deg = np.bincount(np.asarray(ei, dtype=np.int64), minlength=n) + np.bincount(np.asarray(ej, dtype=np.int64), minlength=n)
+    arr = np.arange(n) if order_key is None else np.argsort(np.asarray(order_key), kind="stable")
+    if sort_window < 0:
+        return arr
+    win = np.arange(n) // sort_window if sort_window > 0 else np.zeros(n, dtype=np.int64)
+    # stable: ties keep the arrangement
+    return arr[np.lexsort((np.arange(n), -deg[arr], win))]
+
+
+def knn_padded_slots(ei, ej, n: int, order: np.ndarray, slice_rows: int = 32) -> int:
+    """Entries of a sliced-ELL layout with ``slice_rows`` rows per slice in the given row order,
+    padding included: every slice is as wide as its longest row."""
+    deg = np.bincount(np.asarray(ei, dtype=np.int64), minlength=n) + np.bincount(np.asarray(ej, dtype=np.int64), minlength=n)
+    d = deg[order]
+    pad = (-len(d)) % slice_rows
+    d = np.concatenate([d, np.zeros(pad, dtype=d.dtype)]).reshape(-1, slice_rows)
+    return int(slice_rows * d.max(axis=1).sum())
+
+
+def morton_keys(x: np.ndarray) -> np.ndarray:
+    """Z-order codes of the columns of x (m, n): the (up to) three features of largest variance
+    quantised to 10 bits each, bits interleaved with feature 0 lowest -- a bit-by-bit restatement of
+    graph_learning_b200.knn.locality_keys (host-side glue, no reference code)."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.shape[0] > 3:
+        top = np.argsort(-x.var(axis=1), kind="stable")[:3]
+        x = x[np.sort(top)]
+    lo = x.min(axis=1, keepdims=True)
+    span = np.maximum(x.max(axis=1, keepdims=True) - lo, np.finfo(np.float64).tiny)
+    q = np.clip(((x - lo) / span * 1024.0).astype(np.int64), 0, 1023)
+    key = np.zeros(x.shape[1], dtype=np.int64)
+    for a in range(q.shape[0]):
+        for b in range(10):
+            key |= ((q[a] >> b) & 1) << (3 * b + a)
+    return key.astype(np.int32)
+
+
 # --------------------------------------------------------------------------------------
 # dense-Laplacian forms of the same operator pair (operators.py:44-94)
 # --------------------------------------------------------------------------------------

@@ -1,0 +1,157 @@
+"""Row ordering of the kNN solver's sliced layout (gl_knn_create_ordered / locality_keys).
+
+CPU part: the Morton keys against a bit-by-bit restatement, and the properties of the windowed
+degree sort the library implements (restated in oracle.knn_row_order).
+
+GPU part: WRITTEN AFTER THE ROUND'S GPU MINUTES WERE SPENT -- the ordered entry points have been
+compiled but never run on a device.  The default path (global degree sort) is untouched and keeps its
+own tests in test_gpu_knn.py; the tests below are skipped unless GL_RUN_UNVALIDATED=1 so that an
+unmeasured option cannot turn the GPU suite red.  First thing next round: run them, then drop the gate.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import logmodel_oracle as orc
+
+torch = pytest.importorskip("torch")
+
+unvalidated = pytest.mark.skipif(os.environ.get("GL_RUN_UNVALIDATED") != "1",
+                                 reason="ordered kNN layout not yet run on a GPU (set GL_RUN_UNVALIDATED=1)")
+
+
+def _case(n, k, dim=3, seed=0):
+    rng = np.random.default_rng(seed)
+    pts = rng.uniform(size=(n, dim))
+    zsq = ((pts[:, None] - pts[None]) ** 2).sum(-1)
+    ei, ej = orc.knn_support(zsq, k)
+    return pts, ei, ej, zsq[ei, ej] * (n ** (2 / dim))
+
+
+# ---- CPU ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("m", [1, 2, 3, 8])
+def test_locality_keys_match_bitwise_restatement(m):
+    from graph_learning_b200.knn import locality_keys
+    rng = np.random.default_rng(m)
+    x = rng.standard_normal((m, 500)) * rng.uniform(0.1, 5.0, size=(m, 1))
+    got = locality_keys(x)
+    assert got.dtype == torch.int32 and got.shape == (500,)
+    want = orc.morton_keys(x)
+    assert np.array_equal(got.numpy(), want)
+    assert int(got.min()) >= 0 and int(got.max()) < 2 ** 30
+    # tensors in, same keys
+    assert torch.equal(locality_keys(torch.as_tensor(x)), got)
+
+
+def test_locality_keys_constant_feature_and_errors():
+    from graph_learning_b200.knn import locality_keys
+    x = np.stack([np.linspace(0, 1, 64), np.full(64, 3.0)])
+    keys = locality_keys(x).numpy()
+    assert np.array_equal(keys, orc.morton_keys(x))
+    assert np.all(np.diff(keys) >= 0)            # one varying coordinate: keys follow it
+    with pytest.raises(ValueError):
+        locality_keys(np.zeros(5))
+
+
+def test_locality_keys_are_local():
+    """Points adjacent in key order are close in space: the mean distance between consecutive points of
+    the arrangement is far below that of a random order."""
+    from graph_learning_b200.knn import locality_keys
+    rng = np.random.default_rng(0)
+    pts = rng.uniform(size=(4000, 3))
+    order = np.argsort(locality_keys(pts.T).numpy(), kind="stable")
+    step = np.linalg.norm(np.diff(pts[order], axis=0), axis=1).mean()
+    base = np.linalg.norm(np.diff(pts, axis=0), axis=1).mean()
+    assert step < 0.25 * base
+
+
+@pytest.mark.parametrize("window", [-1, 0, 32, 64, 1000])
+def test_row_order_properties(window):
+    n = 700
+    pts, ei, ej, _ = _case(n, 8)
+    keys = orc.morton_keys(pts.T)
+    deg = np.bincount(ei, minlength=n) + np.bincount(ej, minlength=n)
+    for key in (None, keys):
+        order = orc.knn_row_order(ei, ej, n, key, window)
+        assert np.array_equal(np.sort(order), np.arange(n))
+        arr = np.arange(n) if key is None else np.argsort(key, kind="stable")
+        if window < 0:
+            assert np.array_equal(order, arr)
+            continue
+        w = window if window > 0 else n
+        for b in range(0, n, w):
+            blk = order[b:b + w]
+            assert np.array_equal(np.sort(blk), np.sort(arr[b:b + w]))       # windows keep their nodes
+            assert np.all(np.diff(deg[blk]) <= 0)                            # decreasing degree inside
+    glob = orc.knn_padded_slots(ei, ej, n, orc.knn_row_order(ei, ej, n, None, 0))
+    here = orc.knn_padded_slots(ei, ej, n, orc.knn_row_order(ei, ej, n, keys, window))
+    assert 2 * len(ei) <= glob <= here        # the global sort has the least padding of all orders
+
+
+# ---- GPU (gated, see the module docstring) ----------------------------------------------------------
+def _rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.mark.gpu
+@unvalidated
+@pytest.mark.parametrize("with_key", [False, True])
+@pytest.mark.parametrize("window", [-1, 0, 32, 256, 4096])
+def test_ordered_solve_equals_oracle(window, with_key):
+    from graph_learning_b200.knn import gsp_learn_graph_log_degrees_knn as knn
+    from graph_learning_b200.knn import locality_keys
+    n = 1000
+    pts, ei, ej, z = _case(n, 10, seed=3)
+    wo, io = orc.solve_knn(ei, ej, z, n, maxit=300)
+    key = locality_keys(pts.T) if with_key else None
+    w, info = knn(ei, ej, z, n, maxit=300, return_info=True, order_key=key, sort_window=window)
+    assert info.n_iter == io.n_iter
+    assert _rel(w, wo) < 1e-9
+    assert np.array_equal(w > 0, wo > 0)
+    w32 = knn(ei, ej, z.astype(np.float32), n, maxit=300, order_key=key, sort_window=window)
+    assert w32.dtype == np.float32 and _rel(w32, wo) < 1e-4
+
+
+@pytest.mark.gpu
+@unvalidated
+@pytest.mark.parametrize("with_key", [False, True])
+@pytest.mark.parametrize("window", [-1, 0, 32, 100, 4096])
+def test_padded_slots_match_row_order_restatement(window, with_key):
+    """The padding of the device layout is a fingerprint of the row order actually built."""
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    from graph_learning_b200.knn import locality_keys
+    n = 900
+    pts, ei, ej, z = _case(n, 7, seed=5)
+    key = locality_keys(pts.T).cuda() if with_key else None
+    e_i = torch.as_tensor(ei, dtype=torch.int32, device="cuda")
+    e_j = torch.as_tensor(ej, dtype=torch.int32, device="cuda")
+    zd = torch.as_tensor(z, dtype=torch.float64, device="cuda")
+    npad = -(-n // 128) * 128
+    h = ctypes.c_void_p()
+    nat.check(nat.lib().gl_knn_create_ordered(ctypes.byref(h), e_i.data_ptr(), e_j.data_ptr(), zd.data_ptr(), None,
+                                              len(ei), n, nat.GL_F64, 0, npad, npad,
+                                              key.data_ptr() if key is not None else None, window, None))
+    try:
+        torch.cuda.synchronize()
+        order = orc.knn_row_order(ei, ej, n, key.cpu().numpy() if key is not None else None, window)
+        assert nat.lib().gl_knn_local_slots(h) == 2 * len(ei)
+        assert nat.lib().gl_knn_padded_slots(h) == orc.knn_padded_slots(ei, ej, n, order)
+    finally:
+        nat.lib().gl_knn_destroy(h)
+
+
+@pytest.mark.gpu
+@unvalidated
+def test_estimator_with_locality_order_matches_default():
+    from graph_learning_b200.knn import KNNLogModel
+    rng = np.random.default_rng(11)
+    x = rng.uniform(size=(3, 2000))
+    a = KNNLogModel(avg_degree=6, n_neighbors=12, maxit=200).fit(x)
+    b = KNNLogModel(avg_degree=6, n_neighbors=12, maxit=200, locality_order=True, sort_window=512).fit(x)
+    assert np.array_equal(a.edges_, b.edges_)
+    assert a.n_iter_ == b.n_iter_
+    assert _rel(b.weights_, a.weights_) < 1e-5        # float32 solve; only the summation order differs
+    assert b.get_params()["locality_order"] is True and b.get_params()["sort_window"] == 512
