@@ -247,7 +247,11 @@ template <typename F> struct KnnFusedArgs {
   double gamma, four_ag, tol;
 };
 
-template <typename F>
+// STREAM: the slot arrays (dst, w, z: read once per iteration) are loaded / stored with the
+// cache-streaming (evict-first) policy so that they do not push the gathered (a, b) lines out of the L1;
+// only worth having together with a locality-preserving row order (gl_knn_create_ordered).  Selected
+// with GL_KNN_STREAM=1 in the environment; same arithmetic, same results.
+template <typename F, bool STREAM = false>
 __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused_kernel(const KnnFusedArgs<F> A) {
   if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][4];
@@ -275,9 +279,15 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
       for (int u = 0; u < KNN_UNROLL; ++u) {
         const long long p = p0 + 32LL * u;
         const bool in = p < end;
-        jj[u] = in ? dst[p] : -1;
-        ww[u] = in ? w[p] : F(0);
-        zv[u] = in ? z[p] : F(0);
+        if constexpr (STREAM) {
+          jj[u] = in ? __ldcs(dst + p) : -1;
+          ww[u] = in ? __ldcs(w + p) : F(0);
+          zv[u] = in ? __ldcs(z + p) : F(0);
+        } else {
+          jj[u] = in ? dst[p] : -1;
+          ww[u] = in ? w[p] : F(0);
+          zv[u] = in ? z[p] : F(0);
+        }
       }
     };
     fetch(base, j, wo, zz);
@@ -295,7 +305,8 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
           const F q = c * pv - (abi.y + abj[u].y);
           const F r = q - y;
           const F wn = (wo[u] - y) + q;
-          w[p0 + 32LL * u] = wn;
+          if constexpr (STREAM) __stcs(w + p0 + 32LL * u, wn);
+          else w[p0 + 32LL * u] = wn;
           acc_p += (double)pv;
           acc_w += (double)wn;
           res += (double)r * (double)r;

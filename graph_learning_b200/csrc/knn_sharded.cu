@@ -8,6 +8,8 @@
 // (8 B x n in fp32; by the caller: NCCL in-place all-gather, graph_learning_b200/sharded.py).
 // Per iteration:  edge_step -> node_step -> [all-gather ab | all-reduce 4 scalars] -> decide.
 // The node state (d, yb, pb) of foreign rows is never touched.
+#include <cstdlib>
+
 #include <cub/device/device_scan.cuh>
 
 #include "knn_kernels.cuh"
@@ -246,7 +248,14 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
   const int grid = std::max(1, std::min((k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32), KNN_FUSED_MAX_GRID));
-  knn_fused_kernel<F><<<grid, KNN_THREADS, 0, st>>>(A);
+  static const bool stream_loads = [] {
+    const char *e = getenv("GL_KNN_STREAM");   // evict-first slot loads (knn_kernels.cuh); off by default
+    return e && atoi(e) != 0;
+  }();
+  if (stream_loads)
+    knn_fused_kernel<F, true><<<grid, KNN_THREADS, 0, st>>>(A);
+  else
+    knn_fused_kernel<F, false><<<grid, KNN_THREADS, 0, st>>>(A);
   GL_LAUNCH_CHECK();
   k->parity ^= 1;
   return GL_OK;

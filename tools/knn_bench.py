@@ -5,7 +5,8 @@ Prints one JSON line.  Development / measurement aid.
     python tools/knn_bench.py [n] [k] [iters] [sort_window] [locality]
 sort_window / locality (0 | 1) select the solver's internal row order (gl_knn_create_ordered): the
 default 0 0 is the global degree sort; e.g. `1000000 20 200 4096 1` = Morton arrangement of the points
-with the degree sort inside windows of 4,096 rows."""
+with the degree sort inside windows of 4,096 rows.  GL_KNN_STREAM=1 in the environment selects the
+evict-first slot loads of knn_fused_kernel."""
 import json
 import os
 import sys
