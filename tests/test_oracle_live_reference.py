@@ -128,3 +128,25 @@ def test_laplacian_operator_pair(ref):
     lhs = np.sum(orc.laplacian_from_packed(w) * mats)
     rhs = np.sum(w * orc.laplacian_adjoint(mats))
     assert abs(lhs - rhs) < 1e-10 * abs(lhs)
+
+
+def test_assignment_step_forms(ref):
+    """k-Graphs smoothness (kgraphs.py:87-88) and the GLMM E-step (glmm.py:238-279), called unbound on a
+    bare namespace so that no estimator has to be fitted."""
+    from types import SimpleNamespace
+
+    sys.path.insert(0, REF)
+    try:
+        from graph_learn.clustering.glmm import GLMM
+        from graph_learn.clustering.kgraphs import KGraphs
+    finally:
+        sys.path.remove(REF)
+    rng = np.random.default_rng(601)
+    n, n_graphs, m = 14, 3, 50
+    w = rng.uniform(size=(n_graphs, n * (n - 1) // 2)) * (rng.uniform(size=(n_graphs, n * (n - 1) // 2)) < 0.4)
+    laps = orc.laplacian_from_packed(w)
+    x = rng.standard_normal((m, n))
+    means = rng.standard_normal((n_graphs, n))
+    ns = SimpleNamespace(laplacians_=laps, n_components=n_graphs, regul=0.1, means_=means, n_nodes_=n)
+    assert _rel(orc.smoothness(x, laps), KGraphs._smoothness(ns, x)) < 1e-13
+    assert _rel(orc.glmm_log_prob(x, laps, means, 0.1), GLMM._estimate_log_prob(ns, x)) < 1e-12
