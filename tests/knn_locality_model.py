@@ -10,7 +10,7 @@ gl_knn_create_ordered) and count, for every warp-wide gather of the interleaved 
   * the layout's padding.
 This is an access-pattern count, not a timing; the timing is tools/knn_bench.py on a B200.
 
-    python tools/knn_locality_model.py [n] [k]          # default 200000 20
+    python tests/knn_locality_model.py [n] [k]          # default 200000 20
 """
 import json
 import os
@@ -20,7 +20,7 @@ import numpy as np
 from scipy.spatial import cKDTree
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from oracle import logmodel_oracle as orc  # noqa: E402  (a development tool, not product code)
+from oracle import logmodel_oracle as orc  # noqa: E402  (lives under tests/: only tests may import the oracle)
 
 
 def support(pts, k):
