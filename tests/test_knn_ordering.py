@@ -155,3 +155,54 @@ def test_estimator_with_locality_order_matches_default():
     assert a.n_iter_ == b.n_iter_
     assert _rel(b.weights_, a.weights_) < 1e-5        # float32 solve; only the summation order differs
     assert b.get_params()["locality_order"] is True and b.get_params()["sort_window"] == 512
+
+
+# ---- CPU: executable specification of the planned blocked layout -----------------------
+@pytest.mark.parametrize("block,window", [(256, 256), (64, 64), (256, 0), (1024, 1024)])
+def test_blocked_layout_invariants(block, window):
+    n = 1500
+    pts, ei, ej, _ = _case(n, 8, seed=2)
+    order = orc.knn_row_order(ei, ej, n, orc.morton_keys(pts.T), window)
+    lay = orc.knn_blocked_layout(ei, ej, n, order, block)
+    lab = lay["lab"]
+    assert np.array_equal(lab[order], np.arange(n))
+    # every edge exactly once in an intra list or exactly twice among the slots
+    count = np.bincount(lay["intra_eid"], minlength=len(ei)) * 2 + np.bincount(lay["slot_eid"], minlength=len(ei))
+    assert np.all(count == 2)
+    assert np.all(np.bincount(lay["slot_eid"][lay["slot_first"]], minlength=len(ei)) + np.bincount(
+        lay["intra_eid"], minlength=len(ei)) == 1)
+    # intra edges: both ends in the list's block, local ids reproduce the rows
+    blk = np.repeat(np.arange(lay["nblocks"]), np.diff(lay["intra_ptr"]))
+    ra, rb = blk * block + lay["intra_a"], blk * block + lay["intra_b"]
+    e = lay["intra_eid"]
+    assert np.array_equal(np.sort(np.stack([ra, rb]), axis=0), np.sort(np.stack([lab[ei[e]], lab[ej[e]]]), axis=0))
+    assert lay["intra_a"].dtype == (np.uint8 if block <= 256 else np.uint16)
+    # slots: source row from slot_ptr, far end is the other end of the edge, never in the same block
+    src = np.repeat(np.arange(n), np.diff(lay["slot_ptr"]))
+    e = lay["slot_eid"]
+    assert np.array_equal(src + lay["slot_dst"], lab[ei[e]] + lab[ej[e]])
+    assert np.all(src // block != lay["slot_dst"] // block)
+    assert 14.0 <= lay["bytes_per_edge"] <= 32.0
+    if window == block == 256:
+        assert lay["intra_fraction"] > 0.35          # small n; 0.67 at n = 2e5
+
+
+@pytest.mark.parametrize("block,window,with_key", [(256, 256, True), (32, 0, True), (128, -1, False), (4096, 0, False)])
+def test_blocked_schedule_equals_knn_oracle(block, window, with_key):
+    n = 600
+    pts, ei, ej, z = _case(n, 7, seed=9)
+    order = orc.knn_row_order(ei, ej, n, orc.morton_keys(pts.T) if with_key else None, window)
+    lay = orc.knn_blocked_layout(ei, ej, n, order, block)
+    for kw in ({"maxit": 1, "tol": 0.0}, {"maxit": 40, "tol": 0.0}, {"maxit": 400}):
+        wo, io = orc.solve_knn(ei, ej, z, n, threshold=False, **kw)
+        w, info = orc.solve_knn_blocked(ei, ej, z, n, lay, threshold=False, **kw)
+        assert info.n_iter == io.n_iter and info.converged == io.converged
+        assert _rel(w, wo) < 1e-12
+        if io.n_iter > 1:
+            assert abs(info.rel_primal - io.rel_primal) < 1e-9 * io.rel_primal
+            assert abs(info.rel_dual - io.rel_dual) < 1e-9 * io.rel_dual
+    # warm start and thresholding go through the same path
+    init = np.random.default_rng(1).uniform(0, 0.2, size=len(ei))
+    wo, _ = orc.solve_knn(ei, ej, z, n, edge_init=init, maxit=30)
+    w, _ = orc.solve_knn_blocked(ei, ej, z, n, lay, edge_init=init, maxit=30)
+    assert _rel(w, wo) < 1e-12 and np.array_equal(w > 0, wo > 0)
