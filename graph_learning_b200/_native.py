@@ -78,10 +78,11 @@ SIGNATURES = {
     "gl_knn_create": (c_int, [POINTER(c_void_p), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                               c_int, c_int64, c_void_p]),
     "gl_knn_create_ordered": (c_int, [POINTER(c_void_p), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int,
-                                      c_int, c_int, c_int64, c_void_p, c_int, c_void_p]),
+                                      c_int, c_int, c_int64, c_void_p, c_int, c_int, c_void_p]),
     "gl_knn_destroy": (c_int, [c_void_p]),
     "gl_knn_local_slots": (c_int64, [c_void_p]),
     "gl_knn_padded_slots": (c_int64, [c_void_p]),
+    "gl_knn_intra_edges": (c_int64, [c_void_p]),
     "gl_knn_set_fused": (c_int, [c_void_p, c_int]),
     "gl_knn_begin": (c_int, [c_void_p, c_double, c_double, c_double, c_int, c_double, c_int, c_void_p]),
     "gl_knn_edge_step": (c_int, [c_void_p, c_void_p]),
@@ -101,7 +102,7 @@ SIGNATURES = {
                                       c_int, c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p]),
     "gl_knn_logmodel_solve_ordered": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_double, c_double,
                                               c_int, c_double, c_double, c_double, c_void_p, _pi, _pd, _pd, c_void_p,
-                                              c_int, c_void_p]),
+                                              c_int, c_int, c_void_p]),
 }
 
 

@@ -25,13 +25,13 @@ namespace gl {
 // replays.
 static int knn_solve(const int32_t *ei, const int32_t *ej, const void *z, int64_t nnz, int n, int dtype, double alpha,
                      double beta, int maxit, double tol, double step_size, double edge_tol, void *w, int *n_iter,
-                     double *rel_primal, double *rel_dual, const int32_t *order_key, int sort_window,
+                     double *rel_primal, double *rel_dual, const int32_t *order_key, int sort_window, int layout,
                      cudaStream_t st) {
   int dmax = 0;
   GL_TRY(gl_knn_max_degree(ei, ej, nnz, n, &dmax, st));
   gl_knn_solver *k = nullptr;
   const int npad = tiles_per_side(n) * T;
-  GL_TRY(gl_knn_create_ordered(&k, ei, ej, z, w, nnz, n, dtype, 0, npad, npad, order_key, sort_window, st));
+  GL_TRY(gl_knn_create_ordered(&k, ei, ej, z, w, nnz, n, dtype, 0, npad, npad, order_key, sort_window, layout, st));
   {
     const int frc = gl_knn_set_fused(k, 2);   // whole iteration in one launch
     if (frc != GL_OK) {
@@ -110,17 +110,17 @@ extern "C" int gl_knn_logmodel_solve(const int32_t *ei, const int32_t *ej, const
   if (nnz < 0) return fail(GL_E_SHAPE, "negative edge count");
   if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
   return knn_solve(ei, ej, z, nnz, n, dtype, alpha, beta, maxit, tol, step_size, edge_tol, w, n_iter, rel_primal,
-                   rel_dual, nullptr, 0, as_stream(stream));
+                   rel_dual, nullptr, 0, 0, as_stream(stream));
 }
 
 extern "C" int gl_knn_logmodel_solve_ordered(const int32_t *ei, const int32_t *ej, const void *z, int64_t nnz, int n,
                                              int dtype, double alpha, double beta, int maxit, double tol,
                                              double step_size, double edge_tol, void *w, int *n_iter,
                                              double *rel_primal, double *rel_dual, const int32_t *order_key,
-                                             int sort_window, void *stream) {
+                                             int sort_window, int layout, void *stream) {
   if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
   if (nnz < 0) return fail(GL_E_SHAPE, "negative edge count");
   if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
   return knn_solve(ei, ej, z, nnz, n, dtype, alpha, beta, maxit, tol, step_size, edge_tol, w, n_iter, rel_primal,
-                   rel_dual, order_key, sort_window, as_stream(stream));
+                   rel_dual, order_key, sort_window, layout, as_stream(stream));
 }

@@ -133,7 +133,7 @@ def test_padded_slots_match_row_order_restatement(window, with_key):
     h = ctypes.c_void_p()
     nat.check(nat.lib().gl_knn_create_ordered(ctypes.byref(h), e_i.data_ptr(), e_j.data_ptr(), zd.data_ptr(), None,
                                               len(ei), n, nat.GL_F64, 0, npad, npad,
-                                              key.data_ptr() if key is not None else None, window, None))
+                                              key.data_ptr() if key is not None else None, window, 0, None))
     try:
         torch.cuda.synchronize()
         order = orc.knn_row_order(ei, ej, n, key.cpu().numpy() if key is not None else None, window)
@@ -206,3 +206,67 @@ def test_blocked_schedule_equals_knn_oracle(block, window, with_key):
     wo, _ = orc.solve_knn(ei, ej, z, n, edge_init=init, maxit=30)
     w, _ = orc.solve_knn_blocked(ei, ej, z, n, lay, edge_init=init, maxit=30)
     assert _rel(w, wo) < 1e-12 and np.array_equal(w > 0, wo > 0)
+
+
+@pytest.mark.gpu
+@unvalidated
+@pytest.mark.parametrize("n,k,window,with_key", [(1000, 10, 256, True), (1000, 10, 0, False), (200, 5, -1, True),
+                                                 (3000, 12, 256, True), (257, 6, 256, True)])
+def test_blocked_layout_solve_equals_oracle(n, k, window, with_key):
+    """layout="blocked": intra-block edges stored once (knn_blocked_kernel).  Same iterates as the oracle;
+    the device's split into intra edges and slots matches the executable specification."""
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    from graph_learning_b200.knn import gsp_learn_graph_log_degrees_knn as knn
+    from graph_learning_b200.knn import locality_keys
+    pts, ei, ej, z = _case(n, k, seed=n)
+    key = locality_keys(pts.T) if with_key else None
+    for kw in ({"maxit": 1, "tol": 0.0}, {"maxit": 17, "tol": 0.0}, {"maxit": 300}):
+        wo, io = orc.solve_knn(ei, ej, z, n, threshold=False, **kw)
+        w, info = knn(ei, ej, z, n, edge_tol=-np.inf, return_info=True, order_key=key, sort_window=window,
+                      layout="blocked", **kw)
+        assert info.n_iter == io.n_iter
+        assert _rel(w, wo) < 1e-9
+    w32 = knn(ei, ej, z.astype(np.float32), n, maxit=300, order_key=key, sort_window=window, layout="blocked")
+    wo, _ = orc.solve_knn(ei, ej, z, n, maxit=300)
+    assert w32.dtype == np.float32 and _rel(w32, wo) < 1e-4
+    # warm start goes through both the intra lists and the slots
+    init = np.random.default_rng(1).uniform(0, 0.2, size=len(ei))
+    wo, _ = orc.solve_knn(ei, ej, z, n, edge_init=init, maxit=25)
+    w = knn(ei, ej, z, n, edge_init=init, maxit=25, order_key=key, sort_window=window, layout="blocked")
+    assert _rel(w, wo) < 1e-9
+    # the split itself
+    order = orc.knn_row_order(ei, ej, n, key.numpy() if key is not None else None, window)
+    lay = orc.knn_blocked_layout(ei, ej, n, order, 256)
+    e_i = torch.as_tensor(ei, dtype=torch.int32, device="cuda")
+    e_j = torch.as_tensor(ej, dtype=torch.int32, device="cuda")
+    zd = torch.as_tensor(z, dtype=torch.float64, device="cuda")
+    kd = key.cuda() if key is not None else None
+    npad = -(-n // 128) * 128
+    h = ctypes.c_void_p()
+    nat.check(nat.lib().gl_knn_create_ordered(ctypes.byref(h), e_i.data_ptr(), e_j.data_ptr(), zd.data_ptr(), None,
+                                              len(ei), n, nat.GL_F64, 0, npad, npad,
+                                              kd.data_ptr() if kd is not None else None, window, 1, None))
+    try:
+        torch.cuda.synchronize()
+        assert nat.lib().gl_knn_intra_edges(h) == len(lay["intra_eid"])
+        assert nat.lib().gl_knn_local_slots(h) == len(lay["slot_eid"])
+        assert nat.lib().gl_knn_set_fused(h, 1) == nat.GL_E_STATE          # one-launch form only
+    finally:
+        nat.lib().gl_knn_destroy(h)
+
+
+@pytest.mark.gpu
+@unvalidated
+def test_blocked_layout_needs_a_single_shard():
+    import ctypes
+    from graph_learning_b200 import _native as nat
+    ei = torch.tensor([0, 1], dtype=torch.int32, device="cuda")
+    ej = torch.tensor([1, 2], dtype=torch.int32, device="cuda")
+    z = torch.ones(2, dtype=torch.float32, device="cuda")
+    h = ctypes.c_void_p()
+    rc = nat.lib().gl_knn_create_ordered(ctypes.byref(h), ei.data_ptr(), ej.data_ptr(), z.data_ptr(), None, 2, 300,
+                                         nat.GL_F32, 0, 128, 384, None, 0, 1, None)
+    assert rc == nat.GL_E_STATE and not h.value
+    assert nat.lib().gl_knn_create_ordered(ctypes.byref(h), ei.data_ptr(), ej.data_ptr(), z.data_ptr(), None, 2, 300,
+                                           nat.GL_F32, 0, 384, 384, None, 0, 7, None) == nat.GL_E_ARG

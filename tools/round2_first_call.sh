@@ -6,7 +6,8 @@
 #
 # 1. the full GPU suite (must stay green: the defaults did not change)
 # 2. the gated tests of the ordered kNN layout
-# 3. tools/knn_bench.py at config 5 for each row order, with and without evict-first slot loads
+# 3. tools/knn_bench.py at config 5 for each row order (slot and blocked layouts), with and without
+#    evict-first slot loads
 # 4. one ncu --set full capture of knn_fused_kernel under the Morton order (only after 3 exited 0)
 set -u
 out=gpurun_out
@@ -17,7 +18,7 @@ GL_RUN_UNVALIDATED=1 python -m pytest tests/test_knn_ordering.py -m gpu -q > "$o
 echo "ordered-layout tests exit $?" | tee -a "$out/r2_status.txt"
 : > "$out/r2_knn_order.jsonl"
 ok=0
-for args in "0 0" "0 1" "256 1" "1024 1" "4096 1" "-1 1"; do
+for args in "0 0" "0 1" "256 1" "1024 1" "4096 1" "-1 1" "256 1 blocked" "-1 1 blocked" "0 1 blocked"; do
   # shellcheck disable=SC2086
   timeout 300 python tools/knn_bench.py 1000000 20 200 $args >> "$out/r2_knn_order.jsonl" 2>> "$out/r2_knn_order.err" || ok=1
 done
