@@ -167,7 +167,11 @@ class KNNLogModel(BaseEstimator):
     the device.  No reference estimator exists for it; the parameters mirror ``LogModel``.
 
     Attributes: ``edges_`` (2, nnz) int32 with ei < ej, ``weights_`` (nnz,), ``theta_``,
-    ``n_iter_``; :meth:`to_sparse` gives the symmetric scipy CSR matrix."""
+    ``n_iter_``; :meth:`to_sparse` gives the symmetric scipy CSR matrix.
+
+    ``locality_order`` / ``sort_window`` / ``layout`` choose the solver's internal row order and edge
+    layout (see :func:`gsp_learn_graph_log_degrees_knn`); they never change what is returned.  They were
+    added after round 1's last device run and are off by default until measured."""
 
     def __init__(self, avg_degree: int = 10, n_neighbors: int = 20, *, maxit: int = 1000, tol: float = 1e-5,
                  step_size: float = 0.5, edge_tol: float = 1e-3, locality_order: bool = False,
