@@ -12,6 +12,7 @@
 #include <cstring>
 #include <memory>
 #include <mutex>
+#include <system_error>
 #include <thread>
 #include <vector>
 
@@ -65,23 +66,36 @@ template <typename V> static inline V warp_sum(V v) {
 }
 }  // namespace gl
 
-// run `kernel(args)` for a grid of `grid` CTAs of `threads` threads, CTAs sequentially
+// run `kernel(args)` for a grid of `grid` CTAs of `threads` threads, CTAs sequentially.  Returns false when
+// the OS refuses the threads (the caller skips the test): the pool is created behind a gate, so a failed
+// creation releases the threads that already exist without running the kernel.
+static bool emu_failed = false;
 template <typename K, typename A> static void emu_launch(K kernel, const A &args, int grid, int threads) {
+  if (emu_failed) return;
   gridDim.x = (unsigned)grid;
   blockDim.x = (unsigned)threads;
   emu_warp_barrier.clear();
   for (int w = 0; w < threads / 32; ++w) emu_warp_barrier.emplace_back(new std::barrier<>(32));
-  for (int b = 0; b < grid; ++b) {
+  for (int b = 0; b < grid && !emu_failed; ++b) {
     blockIdx.x = (unsigned)b;
     std::barrier<> bar(threads);
     emu_cta_barrier = &bar;
+    std::atomic<int> gate{0};   // 0: wait, 1: run, 2: abort
     std::vector<std::thread> pool;
     pool.reserve(threads);
-    for (int t = 0; t < threads; ++t)
-      pool.emplace_back([&, t]() {
-        threadIdx.x = (unsigned)t;
-        kernel(args);
-      });
+    try {
+      for (int t = 0; t < threads; ++t)
+        pool.emplace_back([&, t]() {
+          while (gate.load(std::memory_order_acquire) == 0) std::this_thread::yield();
+          if (gate.load(std::memory_order_acquire) != 1) return;
+          threadIdx.x = (unsigned)t;
+          kernel(args);
+        });
+      gate.store(1, std::memory_order_release);
+    } catch (const std::system_error &) {
+      emu_failed = true;
+      gate.store(2, std::memory_order_release);
+    }
     for (auto &th : pool) th.join();
   }
 }
