@@ -34,6 +34,7 @@ SIGNATURES = {
     "gl_num_tiles": (c_int, [c_int]),
     "gl_tiled_elems": (c_int64, [c_int]),
     "gl_shard_tiles": (c_int, [c_int, c_int, c_int, _pi, _pi]),
+    "gl_shard_rows": (c_int, [c_int, c_int, c_int, _pi, _pi, POINTER(c_int64), POINTER(c_int64)]),
     "gl_pack_to_tiles": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "gl_tiles_to_packed": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "gl_tiles_to_square": (c_int, [c_void_p, c_void_p, c_int, c_int, c_double, c_void_p]),
@@ -47,12 +48,14 @@ SIGNATURES = {
     "gl_pdist_sq_gram": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                  c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "gl_theta": (c_int, [c_void_p, c_int, c_int, c_int, c_int, _pd, c_void_p]),
+    "gl_theta_partial": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "gl_theta_dense": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, _pd, c_void_p]),
     "gl_solver_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int]),
     "gl_solver_destroy": (c_int, [c_void_p]),
     "gl_solver_z_tiles": (c_void_p, [c_void_p, c_int]),
     "gl_solver_w_tiles": (c_void_p, [c_void_p, c_int]),
     "gl_solver_load": (c_int, [c_void_p, c_void_p, _pd, c_void_p, c_void_p]),
+    "gl_solver_load_rows": (c_int, [c_void_p, c_void_p, _pd, c_void_p, c_void_p]),
     "gl_solver_scale_z": (c_int, [c_void_p, _pd, c_void_p]),
     "gl_solver_begin": (c_int, [c_void_p, c_double, c_double, c_double, c_int, c_double, c_void_p]),
     "gl_solver_begin_finish": (c_int, [c_void_p, c_void_p]),

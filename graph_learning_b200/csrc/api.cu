@@ -122,6 +122,12 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
   if (tile_begin < 0 || tile_end > num_tiles(n) || tile_end < tile_begin)
     return fail(GL_E_ARG, "bad tile range [%d,%d) for n=%d (%d tiles)", tile_begin, tile_end, n,
                 num_tiles(n));
+  // K > 1 shares ONE stop decision through spectral norms of (E, K) matrices (smooth_learning.py:158-159);
+  // the exact rule forms K x K edge Grams from the local tiles only, so a batch cannot be tile-sharded
+  // (config 4 is 16 MB of state: it runs on one GPU, "replicas only" when more are offered).
+  if (K > 1 && (tile_begin != 0 || tile_end != num_tiles(n)))
+    return fail(GL_E_ARG, "a batch of K=%d graphs cannot be tile-sharded (shared spectral stop rule); "
+                          "use the full tile range on one GPU", K);
   gl_solver *s = new (std::nothrow) gl_solver();
   if (!s) return fail(GL_E_ALLOC, "host allocation failed");
   GL_CUDA(cudaGetDevice(&s->device));
@@ -208,6 +214,46 @@ int gl_solver_load(gl_solver *s, const void *z_packed, const double *z_scale_hos
     GL_CUDA(cudaMemsetAsync(s->w, 0, (size_t)s->K * s->gstride * s->esz, st));
   s->begun = false;
   return GL_OK;
+}
+
+int gl_shard_rows(int n, int tile_begin, int tile_end, int *row_begin, int *row_end, int64_t *edge_begin,
+                  int64_t *edge_end) {
+  if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
+  if (tile_begin < 0 || tile_end > num_tiles(n) || tile_end < tile_begin) return fail(GL_E_ARG, "bad tile range");
+  const int nt = tiles_per_side(n);
+  auto tile_row = [&](int t) {
+    int I = 0;
+    while (I < nt && t >= nt - I) {
+      t -= nt - I;
+      ++I;
+    }
+    return I;
+  };
+  int r0 = 0, r1 = 0;
+  if (tile_end > tile_begin) {
+    r0 = tile_row(tile_begin) * T;
+    r1 = (tile_row(tile_end - 1) + 1) * T;
+    if (r1 > n) r1 = n;
+  }
+  auto base = [&](int64_t i) { return i * (n - 1) - i * (i - 1) / 2; };  // packed offset of row i
+  if (row_begin) *row_begin = r0;
+  if (row_end) *row_end = r1;
+  if (edge_begin) *edge_begin = base(r0);
+  if (edge_end) *edge_end = base(r1 < n ? r1 : n - 1);
+  return GL_OK;
+}
+
+int gl_solver_load_rows(gl_solver *s, const void *z_rows, const double *z_scale_host, const void *w_rows,
+                        void *stream) {
+  if (!s) return fail(GL_E_ARG, "null solver");
+  if (!z_rows) return fail(GL_E_ARG, "null distances");
+  if (s->K != 1) return fail(GL_E_ARG, "gl_solver_load_rows serves a single graph");
+  int64_t e0 = 0;
+  GL_TRY(gl_shard_rows(s->n, s->tile_begin, s->tile_end, nullptr, nullptr, &e0, nullptr));
+  // the kernels index the packed vector from its start; only elements of the shard's rows are touched
+  const char *zb = static_cast<const char *>(z_rows) - (size_t)e0 * s->esz;
+  const char *wb = w_rows ? static_cast<const char *>(w_rows) - (size_t)e0 * s->esz : nullptr;
+  return gl_solver_load(s, zb, z_scale_host, wb, stream);
 }
 
 int gl_solver_scale_z(gl_solver *s, const double *z_scale_host, void *stream) {

@@ -16,78 +16,93 @@ namespace gl {
 constexpr int TH_THREADS = 256;
 constexpr int LAYOUT_DENSE = 2;
 
+// Row i of the (virtual) square matrix streams through shared memory in chunks of `chunk` entries; the
+// k+1 smallest seen so far are carried in front of the next chunk, so a row of any length is handled
+// (one chunk up to ~50,000 float32 entries).  Tiled layout: only entries stored in tiles [tb, te) take
+// part (a GPU shard; Z then points at the shard's first tile), the others count as +inf, and the zero
+// diagonal belongs to the shard that owns the row's diagonal tile.  cand_out != nullptr: write the
+// row's k+1 smallest (ascending, +inf padded) instead of the two statistics -- the per-shard half of
+// the sharded form, merged by a second call on the gathered candidates (gl_theta_dense).
 template <typename F>
-__global__ void __launch_bounds__(TH_THREADS) theta_rows_kernel(const F *Z, int layout, int n, int nt, int k,
-                                                                double *lo_out, double *hi_out, int64_t ld) {
+__global__ void __launch_bounds__(TH_THREADS) theta_rows_kernel(const F *Z, int layout, int n, int nt, int k, int chunk,
+                                                                int tb, int te, double *lo_out, double *hi_out,
+                                                                F *cand_out, int64_t ld) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  F *row = reinterpret_cast<F *>(smem_raw);
+  double *best_q = reinterpret_cast<double *>(smem_raw);          // [k + 1] sorted minima so far
+  F *row = reinterpret_cast<F *>(smem_raw + sizeof(double) * ((k + 2) & ~1));  // [k + 1 carried | chunk]
   __shared__ double s_val[TH_THREADS / 32];
   __shared__ int s_idx[TH_THREADS / 32];
-  __shared__ double s_sorted_prev, s_sorted_last, s_b;
   const int i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
-  for (int j = tid; j < n; j += TH_THREADS) {
-    F v = F(0);
-    if (layout == LAYOUT_DENSE) {  // general (rows, n) matrix, row i as stored (block form, :220-235)
-      v = Z[(int64_t)i * ld + j];
-    } else if (j != i) {
-      const int lo = j < i ? j : i, hi = j < i ? i : j;
-      if (layout == GL_LAYOUT_TILED) {
-        const int I = lo / T, J = hi / T;
-        v = Z[(int64_t)tile_index(I, J, nt) * TT + (lo % T) * T + (hi % T)];
+  int carried = 0;
+  for (int s0 = 0; s0 < n; s0 += chunk) {
+    const int cnt = (n - s0 < chunk) ? n - s0 : chunk;
+    for (int jj = tid; jj < cnt; jj += TH_THREADS) {
+      const int j = s0 + jj;
+      F v = (F)CUDART_INF;
+      if (layout == LAYOUT_DENSE) {  // general (rows, n) matrix, row i as stored (block form, :220-235)
+        v = Z[(int64_t)i * ld + j];
+      } else if (layout == GL_LAYOUT_PACKED) {
+        v = F(0);
+        if (j != i) v = Z[packed_index(j < i ? j : i, j < i ? i : j, n)];
       } else {
-        v = Z[packed_index(lo, hi, n)];
+        const int lo = j < i ? j : i, hi = j < i ? i : j;
+        const int t = tile_index(lo / T, hi / T, nt);
+        if (t >= tb && t < te) v = (j == i) ? F(0) : Z[(int64_t)(t - tb) * TT + (lo % T) * T + (hi % T)];
       }
+      row[carried + jj] = v;
     }
-    row[j] = v;
-  }
-  if (tid == 0) {
-    s_b = 0.0;
-    s_sorted_prev = 0.0;
-    s_sorted_last = 0.0;
-  }
-  __syncthreads();
-  // k+1 rounds of arg-min extraction: round q yields sorted[q]
-  for (int q = 0; q <= k; ++q) {
-    double best = CUDART_INF;
-    int bidx = -1;
-    for (int j = tid; j < n; j += TH_THREADS) {
-      const double v = (double)row[j];
-      if (bidx < 0 || v < best) {
-        best = v;
-        bidx = j;
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double ov = __shfl_xor_sync(0xffffffffu, best, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
-      if (oi >= 0 && (bidx < 0 || ov < best || (ov == best && oi < bidx))) {
-        best = ov;
-        bidx = oi;
-      }
-    }
-    if (lane == 0) {
-      s_val[wp] = best;
-      s_idx[wp] = bidx;
-    }
+    const int len = carried + cnt;
     __syncthreads();
-    if (tid == 0) {
-      double bv = s_val[0];
-      int bi = s_idx[0];
-      for (int w = 1; w < TH_THREADS / 32; ++w)
-        if (s_idx[w] >= 0 && (bi < 0 || s_val[w] < bv || (s_val[w] == bv && s_idx[w] < bi))) {
-          bv = s_val[w];
-          bi = s_idx[w];
+    // k+1 rounds of arg-min extraction: round q yields sorted[q]
+    for (int q = 0; q <= k; ++q) {
+      double best = CUDART_INF;
+      int bidx = -1;
+      for (int j = tid; j < len; j += TH_THREADS) {
+        const double v = (double)row[j];
+        if (bidx < 0 || v < best) {
+          best = v;
+          bidx = j;
         }
-      if (bi >= 0) row[bi] = (F)CUDART_INF;
-      if (q < k) s_b += bv;  // b = sum of sorted[0..k-1]   (:204)
-      s_sorted_prev = s_sorted_last;
-      s_sorted_last = bv;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
+        if (oi >= 0 && (bidx < 0 || ov < best || (ov == best && oi < bidx))) {
+          best = ov;
+          bidx = oi;
+        }
+      }
+      if (lane == 0) {
+        s_val[wp] = best;
+        s_idx[wp] = bidx;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        double bv = s_val[0];
+        int bi = s_idx[0];
+        for (int w = 1; w < TH_THREADS / 32; ++w)
+          if (s_idx[w] >= 0 && (bi < 0 || s_val[w] < bv || (s_val[w] == bv && s_idx[w] < bi))) {
+            bv = s_val[w];
+            bi = s_idx[w];
+          }
+        if (bi >= 0) row[bi] = (F)CUDART_INF;
+        best_q[q] = bi >= 0 ? bv : CUDART_INF;
+      }
+      __syncthreads();
     }
-    __syncthreads();
+    if (s0 + chunk < n) {  // carry the minima in front of the next chunk
+      for (int q = tid; q <= k; q += TH_THREADS) row[q] = (F)best_q[q];
+      carried = k + 1;
+      __syncthreads();
+    }
   }
-  if (tid == 0) {
-    const double kk = (double)k, b = s_b, sk = s_sorted_last, sk1 = s_sorted_prev;
+  if (cand_out) {
+    for (int q = tid; q <= k; q += TH_THREADS) cand_out[(int64_t)i * (k + 1) + q] = (F)best_q[q];
+  } else if (tid == 0) {
+    double b = 0.0;
+    for (int q = 0; q < k; ++q) b += best_q[q];          // b = sum of sorted[0..k-1]   (:204)
+    const double kk = (double)k, sk = best_q[k], sk1 = best_q[k - 1];
     lo_out[i] = 1.0 / sqrt(kk * sk * sk - b * sk);      // :205-208
     hi_out[i] = 1.0 / sqrt(kk * sk1 * sk1 - b * sk1);   // :209-212
   }
@@ -119,40 +134,51 @@ __global__ void __launch_bounds__(256) theta_mean_kernel(const double *lo, const
 }  // namespace gl
 using namespace gl;
 
+static int theta_launch(const void *Z, int layout, int rows, int n, int64_t ld, int k, int dtype, int tb, int te,
+                        double *lo, double *hi, void *cand, cudaStream_t st) {
+  const size_t esz = dtype == GL_F32 ? 4 : 8;
+  const size_t head = sizeof(double) * (size_t)((k + 2) & ~1);
+  const size_t budget = 200 * 1024;
+  if (head + esz * (size_t)(k + 2) > budget)
+    return fail(GL_E_ARG, "avg_degree %d is too large for the row-select kernel", k);
+  size_t chunk = (budget - head) / esz - (size_t)(k + 1);
+  if (chunk > (size_t)n) chunk = (size_t)n;
+  const size_t smem = head + esz * (chunk + (size_t)(k + 1));
+  const int nt = tiles_per_side(n);
+  cudaError_t e;
+  if (dtype == GL_F32) {
+    e = cudaFuncSetAttribute(theta_rows_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess)
+      theta_rows_kernel<float><<<rows, TH_THREADS, smem, st>>>((const float *)Z, layout, n, nt, k, (int)chunk, tb, te, lo, hi,
+                                                               (float *)cand, ld);
+  } else {
+    e = cudaFuncSetAttribute(theta_rows_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess)
+      theta_rows_kernel<double><<<rows, TH_THREADS, smem, st>>>((const double *)Z, layout, n, nt, k, (int)chunk, tb, te, lo, hi,
+                                                                (double *)cand, ld);
+  }
+  if (e == cudaSuccess) {
+    g_launches.fetch_add(1);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) return fail(GL_E_CUDA, "theta row select failed: %s", cudaGetErrorString(e));
+  return GL_OK;
+}
+
 static int theta_impl(const void *Z, int layout, int rows, int n, int64_t ld, int avg_degree, int dtype,
                       double *theta_host, void *stream) {
   if (n < 2 || rows < 1) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
   if (avg_degree < 1 || avg_degree >= n)
     return fail(GL_E_ARG, "avg_degree must be in [1, n-1], got %d (n=%d)", avg_degree, n);
   if (!theta_host) return fail(GL_E_ARG, "null output");
-  const size_t esz = dtype == GL_F32 ? 4 : 8;
-  const size_t smem = esz * (size_t)n;
-  if (smem > 200 * 1024)
-    return fail(GL_E_SHAPE, "gl_theta holds one row of Z in shared memory: n=%d exceeds the %d-node limit "
-                            "of this dtype; use the kNN-support path for larger graphs", n, (int)(200 * 1024 / esz));
+  if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
   cudaStream_t st = as_stream(stream);
   double *buf = nullptr;
   GL_CUDA(cudaMalloc((void **)&buf, sizeof(double) * (2 * (size_t)rows + 2)));
-  const int nt = tiles_per_side(n);
-  int rc = GL_OK;
+  int rc = theta_launch(Z, layout, rows, n, ld, avg_degree, dtype, 0, num_tiles(n), buf, buf + rows, nullptr, st);
   cudaError_t e = cudaSuccess;
-  if (dtype == GL_F32) {
-    e = cudaFuncSetAttribute(theta_rows_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess)
-      theta_rows_kernel<float><<<rows, TH_THREADS, smem, st>>>((const float *)Z, layout, n, nt, avg_degree, buf, buf + rows, ld);
-  } else if (dtype == GL_F64) {
-    e = cudaFuncSetAttribute(theta_rows_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess)
-      theta_rows_kernel<double><<<rows, TH_THREADS, smem, st>>>((const double *)Z, layout, n, nt, avg_degree, buf, buf + rows, ld);
-  } else {
-    rc = fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
-  }
-  if (rc == GL_OK && e == cudaSuccess) {
-    g_launches.fetch_add(1);
-    e = cudaGetLastError();
-  }
   double h[2] = {0, 0};
-  if (rc == GL_OK && e == cudaSuccess) {
+  if (rc == GL_OK) {
     theta_mean_kernel<<<1, 256, 0, st>>>(buf, buf + rows, rows, buf + 2 * (size_t)rows);
     g_launches.fetch_add(1);
     e = cudaGetLastError();
@@ -177,4 +203,16 @@ extern "C" int gl_theta_dense(const void *M, int rows, int cols, int64_t ld, int
                               double *theta_host, void *stream) {
   if (ld < cols) return fail(GL_E_SHAPE, "leading dimension %lld < cols %d", (long long)ld, cols);
   return theta_impl(M, LAYOUT_DENSE, rows, cols, ld, avg_degree, dtype, theta_host, stream);
+}
+
+extern "C" int gl_theta_partial(const void *Z_tiles, int n, int tile_begin, int tile_end, int avg_degree, int dtype,
+                                void *cand_out, void *stream) {
+  if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
+  if (avg_degree < 1 || avg_degree >= n)
+    return fail(GL_E_ARG, "avg_degree must be in [1, n-1], got %d (n=%d)", avg_degree, n);
+  if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
+  if (tile_begin < 0 || tile_end > num_tiles(n) || tile_end < tile_begin) return fail(GL_E_ARG, "bad tile range");
+  if (!cand_out) return fail(GL_E_ARG, "null output");
+  return theta_launch(Z_tiles, GL_LAYOUT_TILED, n, n, 0, avg_degree, dtype, tile_begin, tile_end, nullptr, nullptr,
+                      cand_out, as_stream(stream));
 }

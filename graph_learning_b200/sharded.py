@@ -18,7 +18,8 @@ import torch.distributed as dist
 
 from . import _native as nat
 
-__all__ = ["shard_tiles", "ShardBackend", "sharded_schedule", "ShardedLogModelSolver", "shard_rows", "KnnShardBackend",
+__all__ = ["shard_tiles", "ShardBackend", "sharded_schedule", "ShardedLogModelSolver", "sharded_workspace",
+           "solve_distributed", "release_workspaces", "shard_rows", "KnnShardBackend",
            "knn_exchange", "knn_sharded_schedule", "ShardedKNNSolver"]
 
 
@@ -68,6 +69,9 @@ class ShardedLogModelSolver:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.n = n
+        if n_graphs > 1 and self.world > 1:
+            # the shared stop rule of a batch needs spectral norms over ALL edges (smooth_learning.py:158-159)
+            raise ValueError("a (K, E) batch is not tile-sharded: solve it on one GPU (replicas only)")
         self.tile_range = shard_tiles(n, self.rank, self.world)
         self.solver = Solver(n, n_graphs, dtype, tile_range=self.tile_range)
         self._xch = self.solver.exchange()
@@ -153,6 +157,51 @@ class ShardedLogModelSolver:
     def status(self):
         return self.solver.status()
 
+    def gather_square(self, edge_tol: float = 1e-3, result_on: str = "all") -> Optional[torch.Tensor]:
+        """The reference's return value of the 1-D call (:171-172): the dense symmetric (n, n) matrix,
+        on every rank ("all") or on rank 0 only ("root": the others return None).  Tile shards are
+        contiguous slices of one tiled buffer, so the gather is one NCCL transfer per rank (straight
+        into the root's buffer, or an all-reduce of disjoint slices); the square form is written by
+        ``gl_tiles_to_square`` with the edge_tol threshold (:169)."""
+        if result_on not in ("all", "root"):
+            raise ValueError("result_on must be 'all' or 'root'")
+        lib = nat.lib()
+        s = self.solver
+        tt = nat.TILE * nat.TILE
+        if self.world == 1:
+            return s.square(edge_tol)
+        total = lib.gl_num_tiles(self.n)
+        mine = s.w_view(0)
+        b, e = self.tile_range
+        full = None
+        if result_on == "all":
+            full = torch.zeros(total * tt, dtype=s.dtype, device=s.device)
+            full[b * tt:e * tt].copy_(mine)
+            dist.all_reduce(full, group=self.group)
+        else:
+            root = dist.get_global_rank(self.group, 0) if self.group is not None else 0
+            if self.rank == 0:
+                full = torch.empty(total * tt, dtype=s.dtype, device=s.device)
+                full[b * tt:e * tt].copy_(mine)
+                ops = []
+                for r in range(1, self.world):
+                    rb, re = shard_tiles(self.n, r, self.world)
+                    if re > rb:
+                        peer = dist.get_global_rank(self.group, r) if self.group is not None else r
+                        ops.append(dist.P2POp(dist.irecv, full[rb * tt:re * tt], peer, group=self.group))
+            else:
+                ops = [dist.P2POp(dist.isend, mine, root, group=self.group)] if e > b else []
+            if ops:
+                for req in dist.batch_isend_irecv(ops):
+                    req.wait()
+        if full is None:
+            return None
+        out = torch.empty((self.n, self.n), dtype=s.dtype, device=s.device)
+        nat.check(lib.gl_tiles_to_square(ctypes.c_void_p(full.data_ptr()), ctypes.c_void_p(out.data_ptr()), self.n,
+                                         nat.GL_F32 if s.dtype == torch.float32 else nat.GL_F64, float(edge_tol),
+                                         ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return out
+
     def gather_packed(self, edge_tol: float = 1e-3) -> torch.Tensor:
         """All shards' weights as one packed (K, E) tensor on every rank (sum of disjoint stores)."""
         out = self.solver.store(edge_tol)
@@ -166,6 +215,74 @@ class ShardedLogModelSolver:
             torch.cuda.synchronize()
             dist.barrier(group=self.group)  # nobody unmaps memory a peer may still read
         self.solver.close()
+
+
+# ----------------------------------------------------------------------------------------------------
+# the reference-facing distributed call (gsp_learn_graph_log_degrees(..., distributed=...))
+# ----------------------------------------------------------------------------------------------------
+_workspaces: dict = {}
+
+
+def sharded_workspace(n: int, dtype, group=None) -> ShardedLogModelSolver:
+    """One cached :class:`ShardedLogModelSolver` per (n, dtype, group): creating one costs device
+    allocations plus, in peer mode, a CUDA IPC handle exchange and a barrier, which a caller in a loop
+    (bench, GLMM-style outer iterations) should not pay per solve.  Collective: every rank of the group
+    must ask for the same workspace in the same order."""
+    key = (int(n), dtype, id(group) if group is not None else None)
+    ws = _workspaces.get(key)
+    if ws is None:
+        for old in list(_workspaces):          # one resident workspace at a time (they are n^2-sized)
+            _workspaces.pop(old).close()
+        ws = ShardedLogModelSolver(n, dtype, group=group)
+        _workspaces[key] = ws
+    return ws
+
+
+def release_workspaces() -> None:
+    """Free the cached distributed workspace (collective in peer mode: ends with a barrier)."""
+    for key in list(_workspaces):
+        _workspaces.pop(key).close()
+
+
+def solve_distributed(distances, alpha, beta, edge_init, maxit, tol, step_size, edge_tol, dtype, group,
+                      result_on, out, return_info, z_scale=None):
+    """1-D ``gsp_learn_graph_log_degrees`` over all ranks of ``group`` (see its docstring).  Every rank
+    passes the same packed (E,) distances (host array, CPU tensor -- copied asynchronously when pinned --
+    or CUDA tensor) and moves only the rows of its own tile shard to its device."""
+    from .smooth_learning import _n_from_edges, _to_device
+    if not dist.is_initialized():
+        raise RuntimeError("distributed=True needs an initialised torch.distributed process group "
+                           "(one process per GPU, e.g. under torchrun)")
+    is_np = not isinstance(distances, torch.Tensor)
+    is_host_tensor = isinstance(distances, torch.Tensor) and not distances.is_cuda
+    n = _n_from_edges(int(distances.shape[0]))
+    ws = sharded_workspace(n, dtype, group)
+    _, _, e0, e1 = ws.solver.shard_rows()
+    z_rows = _to_device(distances[e0:e1], dtype)
+    w_rows = None
+    if edge_init is not None:
+        if tuple(edge_init.shape) != tuple(distances.shape):
+            raise ValueError(f"edge_init has shape {tuple(edge_init.shape)}, expected {tuple(distances.shape)}")
+        w_rows = _to_device(edge_init[e0:e1], dtype)
+    if z_scale is not None:
+        z_scale = float(np.asarray(z_scale, dtype=np.float64).ravel()[0])
+    ws.solver.load_rows(z_rows, z_scale, w_rows)
+    ws.begin(alpha, beta, step_size, maxit, tol)
+    ws.run()
+    info = ws.status()
+    result = ws.gather_square(edge_tol, result_on)
+    res = result
+    if result is not None:
+        if out is not None:
+            out_t = torch.from_numpy(out) if isinstance(out, np.ndarray) else out
+            out_t.copy_(result, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            res = out
+        elif is_np:
+            res = result.cpu().numpy()
+        elif is_host_tensor:
+            res = result.cpu()
+    return (res, info) if return_info else res
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -218,18 +335,24 @@ def knn_sharded_schedule(backend: KnnShardBackend, maxit: int, rank: int, world:
             break
 
 
+KNN_EXCHANGES = ("nccl",)
+
+
 class ShardedKNNSolver:
     """CUDA backend of the row-sharded kNN-support solve (``gl_knn_*``): one process per GPU, each
     rank builds the directed slots of its own rows from the edges touching them; iterations
     (slot sweep, node step, NCCL all-gather + all-reduce, decision) are captured in a CUDA graph."""
 
     def __init__(self, ei, ej, z, n_nodes: int, dtype=torch.float32, edge_init=None, group=None, rank=None,
-                 world=None):
+                 world=None, exchange: str = "nccl"):
         """``rank`` / ``world`` override the process group's (single-process emulation of several
         shards in the tests; the caller then performs the exchange itself)."""
         from .smooth_learning import _device, _gl_dtype, _to_device
         self.lib = nat.lib()
         self.group = group
+        if exchange not in KNN_EXCHANGES:
+            raise ValueError(f"exchange must be one of {KNN_EXCHANGES}")
+        self.exchange = exchange
         self.emulated = world is not None
         self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.rank = rank if rank is not None else (dist.get_rank(group) if dist.is_initialized() else 0)

@@ -148,6 +148,42 @@ class Solver:
             sc = (ctypes.c_double * self.K)(*[float(v) for v in np.broadcast_to(np.asarray(z_scale, dtype=np.float64).ravel(), (self.K,))])
         nat.check(self.lib.gl_solver_load(self._h, _ptr(z_packed), sc, _ptr(w_packed), _stream()))
 
+    def load_rows(self, z_rows: torch.Tensor, z_scale=None, w_rows: Optional[torch.Tensor] = None):
+        """:meth:`load` for a tile shard from the shard's slice of the packed vector only
+        (``gl_shard_rows`` gives the slice; single graph)."""
+        assert z_rows.is_cuda and z_rows.dtype == self.dtype and z_rows.is_contiguous()
+        sc = None
+        if z_scale is not None:
+            sc = (ctypes.c_double * 1)(float(z_scale))
+        nat.check(self.lib.gl_solver_load_rows(self._h, _ptr(z_rows), sc, _ptr(w_rows), _stream()))
+
+    def shard_rows(self):
+        """(row_begin, row_end, edge_begin, edge_end) of this workspace's tile range."""
+        r0, r1 = ctypes.c_int(), ctypes.c_int()
+        e0, e1 = ctypes.c_int64(), ctypes.c_int64()
+        nat.check(self.lib.gl_shard_rows(self.n, self.tile_begin, self.tile_end, ctypes.byref(r0), ctypes.byref(r1),
+                                         ctypes.byref(e0), ctypes.byref(e1)))
+        return r0.value, r1.value, e0.value, e1.value
+
+    def z_view(self, k: int = 0) -> torch.Tensor:
+        """Zero-copy view of graph k's resident tiled distances (this shard's tiles)."""
+        return _wrap_device_memory(self.z_tiles_ptr(k), (self.tile_end - self.tile_begin) * nat.TILE * nat.TILE,
+                                   self.dtype, self.device, owner=self)
+
+    def w_view(self, k: int = 0) -> torch.Tensor:
+        return _wrap_device_memory(self.w_tiles_ptr(k), (self.tile_end - self.tile_begin) * nat.TILE * nat.TILE,
+                                   self.dtype, self.device, owner=self)
+
+    def load_w_packed(self, w_packed: Optional[torch.Tensor]):
+        """Initial weights from a full packed (K, E) array into the resident tiles (zeros if None)."""
+        if w_packed is None:
+            for k in range(self.K):
+                self.w_view(k).zero_()
+            return
+        assert w_packed.is_cuda and w_packed.dtype == self.dtype and w_packed.is_contiguous()
+        nat.check(self.lib.gl_pack_to_tiles(_ptr(w_packed), ctypes.c_void_p(self.w_tiles_ptr(0)), self.n, self.K,
+                                            _gl_dtype(self.dtype), self.tile_begin, self.tile_end, _stream()))
+
     def z_tiles_ptr(self, k: int = 0) -> int:
         return self.lib.gl_solver_z_tiles(self._h, k)
 
@@ -389,6 +425,29 @@ def _theta_packed(z_packed: torch.Tensor, n: int, avg_degree: int) -> float:
     return th.value
 
 
+def _theta_tiles(z_tiles: torch.Tensor, n: int, avg_degree: int, tile_range=None, group=None) -> float:
+    """theta from the resident tiled distances.  With a tile shard per rank (``tile_range``, a process
+    ``group``) every rank extracts the avg_degree + 1 smallest entries of each row among its own tiles
+    (``gl_theta_partial``); the candidate lists are all-gathered (n x world x (k + 1) values) and merged
+    by the same row statistic -- identical on every rank, equal to the single-GPU value."""
+    lib = nat.lib()
+    if tile_range is None:
+        th = ctypes.c_double()
+        nat.check(lib.gl_theta(_ptr(z_tiles), nat.LAYOUT_TILED, n, int(avg_degree), _gl_dtype(z_tiles.dtype),
+                               ctypes.byref(th), _stream()))
+        return th.value
+    import torch.distributed as dist
+    k1 = int(avg_degree) + 1
+    cand = torch.empty((n, k1), dtype=z_tiles.dtype, device=z_tiles.device)
+    nat.check(lib.gl_theta_partial(_ptr(z_tiles), n, int(tile_range[0]), int(tile_range[1]), int(avg_degree),
+                                   _gl_dtype(z_tiles.dtype), _ptr(cand), _stream()))
+    world = dist.get_world_size(group)
+    allc = torch.empty((world, n, k1), dtype=cand.dtype, device=cand.device)
+    dist.all_gather_into_tensor(allc, cand, group=group)
+    merged = allc.permute(1, 0, 2).reshape(n, world * k1).contiguous()
+    return _theta_dense(merged, avg_degree)
+
+
 def get_theta(sq_pdists, avg_degree, blocks=None):
     """Theta giving the requested average degree (Kalofolias & Perraudin 2019).
 
@@ -433,6 +492,9 @@ def gsp_learn_graph_log_degrees(
     dtype=None,
     return_info: bool = False,
     out=None,
+    z_scale=None,
+    distributed=False,
+    result_on: str = "all",
 ):
     r"""Weighted adjacency from squared pairwise distances under the smoothness prior
     (Kalofolias 2016): minimise :math:`\sum_{ij} w_{ij} z_{ij} - \alpha \sum_i \log(\sum_j w_{ij})
@@ -449,6 +511,13 @@ def gsp_learn_graph_log_degrees(
     ``out`` (extra): preallocated result (e.g. a pinned CPU tensor) to copy the result into.
     A CPU torch tensor as input is treated like a NumPy array (host in, host out) and is copied
     asynchronously when pinned.
+    ``z_scale`` (extra): scalar or K values multiplied into the distances while they are loaded (the
+    ``theta`` of :289, ``glmm.py:79``, ``kgraphs.py:102``) -- saves the caller a full pass over Z.
+    ``distributed`` (extra): ``True`` (default process group) or a ``torch.distributed`` group: one
+    process per GPU, every rank calls with the SAME arguments; a single graph's triangle tiles are
+    sharded over the ranks (each rank uploads only its slice of ``distances``), the result arrives on
+    every rank (``result_on="all"``) or on rank 0 only (``"root"``; the other ranks get ``None``).  A
+    (K, E) batch is not sharded: every rank solves it (replicas).
     """
     is_np = not isinstance(distances, torch.Tensor)
     is_host_tensor = isinstance(distances, torch.Tensor) and not distances.is_cuda
@@ -460,6 +529,11 @@ def gsp_learn_graph_log_degrees(
     if dtype is None and getattr(distances, "dtype", None) in (np.float32, torch.float32):
         dtype = torch.float32
     dt = _torch_dtype(dtype)
+    if distributed is not False and distributed is not None and n_dim == 1:
+        from .sharded import solve_distributed
+        return solve_distributed(distances, alpha, beta, edge_init, maxit, tol, step_size, edge_tol, dt,
+                                 None if distributed is True else distributed, result_on, out, return_info,
+                                 z_scale)
     z = _to_device(distances, dt)
     zk = z[None, :] if n_dim == 1 else z
     n_graphs, n_edges = zk.shape
@@ -475,7 +549,7 @@ def gsp_learn_graph_log_degrees(
 
     solver = Solver(n, n_graphs, dt)
     try:
-        solver.load(zk.contiguous(), None, w0)
+        solver.load(zk.contiguous(), z_scale, w0)
         solver.begin(alpha, beta, step_size, maxit, tol)
         solver.run()
         info = solver.status()
@@ -510,6 +584,13 @@ class LogModel(BaseEstimator):
         step_size (float): Optimisation step size. Defaults to 0.5.
         edge_tol (float): Tolerance to keep positive edges. Defaults to 1e-3.
         dtype (extra, keyword-only): "float64" (reference arithmetic, default) or "float32".
+        distributed (extra, keyword-only): ``False`` (one GPU), ``True`` (the default
+            ``torch.distributed`` process group) or a process group: one process per GPU, every rank
+            calls ``fit`` with the same signals; each rank builds the distance tiles of its own shard of
+            the triangle, theta comes from per-rank row candidates merged after one
+            all-gather, the solve exchanges its degree partials over NVLink peer memory.
+        weights_on (extra, keyword-only): "all" (every rank gets ``weights_``) or "root" (rank 0 only;
+            ``None`` elsewhere) for distributed fits.
 
     Attributes:
         theta_ (float): Sparsity parameter rescaling the pairwise distances.
@@ -527,6 +608,8 @@ class LogModel(BaseEstimator):
         step_size: float = 0.5,
         edge_tol: float = 1e-3,
         dtype="float64",
+        distributed=False,
+        weights_on: str = "all",
     ) -> None:
         self.avg_degree = avg_degree
         self.edge_init = edge_init
@@ -535,9 +618,13 @@ class LogModel(BaseEstimator):
         self.step_size = step_size
         self.edge_tol = edge_tol
         self.dtype = dtype
+        self.distributed = distributed
+        self.weights_on = weights_on
 
     def _initialize(self, x):
-        """Squared pairwise distances (packed, on the device) and ``theta_`` (:277-284)."""
+        """Squared pairwise distances (packed, on the device) and ``theta_`` (:277-284).  Subclasses
+        override this (``WindowLogModel``); :meth:`fit` itself takes the resident route below when it
+        is not overridden."""
         sq_pdists = pdist_sq(x, dtype=self.dtype)
         if self.avg_degree is None:
             self.theta_ = 1
@@ -546,28 +633,104 @@ class LogModel(BaseEstimator):
             self.theta_ = _theta_packed(sq_pdists, n, self.avg_degree)
         return sq_pdists
 
-    def fit(self, x):
-        """x: (n_samples, n_nodes) signals, nodes are COLUMNS (:286-300)."""
+    def _group(self):
+        d = getattr(self, "distributed", False)
+        if d is False or d is None:
+            return False
+        return None if d is True else d
+
+    def _fit_resident(self, x, out=None):
+        """X -> Z tiles written straight into the solver's resident buffer (this rank's shard) ->
+        theta -> in-place scaling -> solve -> (n, n).  No packed Z, no eager elementwise pass, no
+        re-tiling (:277-300)."""
+        dt = _torch_dtype(self.dtype)
+        xd = _to_device(x, dt)
+        if xd.ndim != 2:
+            raise ValueError("signals must be a (n_samples, n_nodes) matrix")
+        m, n = xd.shape
+        group = self._group()
+        sharded = None
+        if group is False:
+            solver = Solver(n, 1, dt)
+            tile_range = None
+        else:
+            from .sharded import sharded_workspace
+            sharded = sharded_workspace(n, dt, group)
+            solver = sharded.solver
+            tile_range = sharded.tile_range if sharded.world > 1 else None
+        try:
+            method = _resolve_method("auto", dt, m)
+            _pdist_into(xd, None, None, solver.z_view(0), nat.LAYOUT_TILED, solver.tile_begin, solver.tile_end, method)
+            if self.avg_degree is None:
+                self.theta_ = 1
+            else:
+                self.theta_ = _theta_tiles(solver.z_view(0), n, self.avg_degree, tile_range,
+                                           None if group is False else group)
+                solver.scale_z(self.theta_)
+            w0 = None
+            if self.edge_init is not None:
+                w0 = _to_device(self.edge_init, dt).reshape(1, -1).contiguous()
+                if w0.shape[1] != n * (n - 1) // 2:
+                    raise ValueError(f"edge_init has shape {tuple(np.shape(self.edge_init))}, expected {(n * (n - 1) // 2,)}")
+            solver.load_w_packed(w0)
+            if sharded is None:
+                solver.begin(1, 1, self.step_size, self.maxit, self.tol)
+                solver.run()
+                info = solver.status()
+                result = solver.square(self.edge_tol)
+            else:
+                sharded.begin(1, 1, self.step_size, self.maxit, self.tol)
+                sharded.run()
+                info = sharded.status()
+                result = sharded.gather_square(self.edge_tol, self.weights_on)
+        finally:
+            if sharded is None:
+                solver.close()
+        return result, info
+
+    def fit(self, x, out=None):
+        """x: (n_samples, n_nodes) signals, nodes are COLUMNS (:286-300).  ``out`` (extra): a
+        preallocated (n, n) host array / pinned tensor that receives ``weights_``."""
         is_np = not isinstance(x, torch.Tensor)
-        sq_pdists = self._initialize(x)
-        if not isinstance(sq_pdists, torch.Tensor):
-            sq_pdists = _to_device(sq_pdists, _torch_dtype(self.dtype))
-        theta = self.theta_
-        if isinstance(theta, np.ndarray):
-            theta = _to_device(theta, sq_pdists.dtype)
-        weights, info = gsp_learn_graph_log_degrees(
-            sq_pdists * theta,
-            1,
-            1,
-            edge_init=self.edge_init,
-            maxit=self.maxit,
-            tol=self.tol,
-            step_size=self.step_size,
-            edge_tol=self.edge_tol,
-            dtype=self.dtype,
-            return_info=True,
-        )
-        self.weights_ = weights.cpu().numpy() if is_np else weights
+        if type(self)._initialize is LogModel._initialize:
+            weights, info = self._fit_resident(x)
+        else:
+            sq_pdists = self._initialize(x)
+            if not isinstance(sq_pdists, torch.Tensor):
+                sq_pdists = _to_device(sq_pdists, _torch_dtype(self.dtype))
+            theta = self.theta_
+            z_scale = None
+            if isinstance(theta, (np.ndarray, torch.Tensor)) and np.size(theta) == (sq_pdists.shape[0] if sq_pdists.ndim == 2 else 1):
+                z_scale = np.asarray(theta.cpu() if isinstance(theta, torch.Tensor) else theta, dtype=np.float64).ravel()
+            elif isinstance(theta, (np.ndarray, torch.Tensor)):
+                sq_pdists = sq_pdists * _to_device(theta, sq_pdists.dtype)   # per-edge theta (block form, :220-235)
+            else:
+                z_scale = float(theta)
+            group = self._group()
+            weights, info = gsp_learn_graph_log_degrees(
+                sq_pdists,
+                1,
+                1,
+                edge_init=self.edge_init,
+                maxit=self.maxit,
+                tol=self.tol,
+                step_size=self.step_size,
+                edge_tol=self.edge_tol,
+                dtype=self.dtype,
+                return_info=True,
+                z_scale=z_scale,
+                distributed=False if group is False else (True if group is None else group),
+                result_on=self.weights_on,
+            )
+        if weights is None:
+            self.weights_ = None
+        elif out is not None:
+            out_t = torch.from_numpy(out) if isinstance(out, np.ndarray) else out
+            out_t.copy_(weights, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            self.weights_ = out
+        else:
+            self.weights_ = weights.cpu().numpy() if (is_np and isinstance(weights, torch.Tensor)) else weights
         self.n_iter_, self.rel_primal_, self.rel_dual_ = info.n_iter, info.rel_primal, info.rel_dual
         self.converged_ = info.converged
         return self

@@ -66,6 +66,13 @@ int64_t gl_tiled_elems(int n);      /* gl_num_tiles(n) * 128 * 128 */
  * half).  SURVEY 8(e): each GPU owns a contiguous edge shard. */
 int gl_shard_tiles(int n, int rank, int world, int *tile_begin, int *tile_end);
 
+/* Node rows [row_begin, row_end) touched by tiles [tile_begin, tile_end), and the range
+ * [edge_begin, edge_end) of the packed vector that holds those rows (contiguous: the packed order is
+ * row-major).  A rank of a sharded solve needs only that slice of Z on its device
+ * (gl_solver_load_rows). */
+int gl_shard_rows(int n, int tile_begin, int tile_end, int *row_begin, int *row_end,
+                  int64_t *edge_begin, int64_t *edge_end);
+
 /* packed <-> tiled for K graphs stored (K, E) / (K, tiled_elems).  Tiles [tile_begin,tile_end)
  * only; `tiled_dev` points at the first tile of the shard. */
 int gl_pack_to_tiles(const void *packed_dev, void *tiled_dev, int n, int K, int dtype,
@@ -126,9 +133,18 @@ int gl_pdist_sq_gram(const void *X_dev, int64_t m, int n, int64_t ldx, const voi
                      void *stream);
 
 /* ---- theta heuristic (smooth_learning.py:201-219, get_theta without blocks) --------------- */
-/* Z in either layout (full triangle).  Writes theta to *theta_host (synchronises). */
+/* Z in either layout (full triangle).  Writes theta to *theta_host (synchronises).  Rows of any
+ * length stream through shared memory in chunks (one chunk up to ~50,000 float32 entries). */
 int gl_theta(const void *Z_dev, int layout, int n, int avg_degree, int dtype, double *theta_host,
              void *stream);
+/* Sharded form: Z_tiles_dev points at the first tile of the range [tile_begin, tile_end) a rank holds
+ * (e.g. gl_solver_z_tiles); cand_out_dev (n, avg_degree + 1) of `dtype` receives, per node, the
+ * avg_degree + 1 smallest entries of its row found in those tiles (ascending, +inf padded; the zero
+ * diagonal counts in the shard owning the row's diagonal tile).  The ranks gather their candidate
+ * lists side by side, (n, world * (avg_degree + 1)), and gl_theta_dense on that matrix returns the
+ * theta of the full matrix (the statistic only reads the avg_degree + 1 smallest entries of a row). */
+int gl_theta_partial(const void *Z_tiles_dev, int n, int tile_begin, int tile_end, int avg_degree,
+                     int dtype, void *cand_out_dev, void *stream);
 /* Same statistic on a general dense (rows, cols) matrix with leading dimension ld, rows used as
  * stored (no implicit diagonal): the per-block-pair call of the block form
  * (smooth_learning.py:220-235, get_theta(sq_pdists[slice1, slice2], ...)). */
@@ -137,7 +153,9 @@ int gl_theta_dense(const void *M_dev, int rows, int cols, int64_t ld, int avg_de
 
 /* ---- the solver (smooth_learning.py:47-174, gsp_learn_graph_log_degrees) ----------------- */
 /* Workspace for K graphs on n nodes owning tiles [tile_begin, tile_end) of the triangle
- * (0, gl_num_tiles(n) for a single GPU).  Allocates w, z (tiled) and all node vectors. */
+ * (0, gl_num_tiles(n) for a single GPU).  Allocates w, z (tiled) and all node vectors.  A batch
+ * (K > 1) must own the full range: its shared stop rule needs spectral norms over all edges
+ * (smooth_learning.py:158-159), so it is not tile-sharded (GL_E_ARG). */
 int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, int tile_end);
 int gl_solver_destroy(gl_solver *s);
 /* Device pointers of the resident tiled state of graph k (for zero-copy producers/consumers). */
@@ -149,6 +167,10 @@ void *gl_solver_w_tiles(gl_solver *s, int k);
  * (smooth_learning.py:140-143). */
 int gl_solver_load(gl_solver *s, const void *z_packed_dev, const double *z_scale_host,
                    const void *w_packed_dev, void *stream);
+/* gl_solver_load for a tile shard when only the shard's slice of the packed vector is on the device
+ * (single graph): z_rows_dev / w_rows_dev point at packed element edge_begin of gl_shard_rows. */
+int gl_solver_load_rows(gl_solver *s, const void *z_rows_dev, const double *z_scale_host,
+                        const void *w_rows_dev, void *stream);
 /* Same, when Z already sits in the solver's tiled buffer (gl_pdist_sq wrote it there). */
 int gl_solver_scale_z(gl_solver *s, const double *z_scale_host, void *stream);
 /* Set parameters and initialise the dual state d = S w (smooth_learning.py:135-144).

@@ -80,7 +80,8 @@ def test_product_never_imports_the_oracle():
 
 def test_estimators_keep_the_reference_constructor_surface(sl):
     """Same parameter names and defaults as the reference classes (smooth_learning.py:257-275,
-    kgraphs.py:20-60, glmm.py:88-135, temporal/smooth.py:12-40); ``dtype`` is the one extra."""
+    kgraphs.py:20-60, glmm.py:88-135, temporal/smooth.py:12-40); the extras (``dtype``, and for LogModel
+    ``distributed`` / ``weights_on``) are keyword-only and default to the reference behaviour."""
     from sklearn.base import BaseEstimator, clone
     from sklearn.mixture._base import BaseMixture
 
@@ -91,7 +92,11 @@ def test_estimators_keep_the_reference_constructor_surface(sl):
         return {k: v.default for k, v in inspect.signature(cls.__init__).parameters.items() if k != "self"}
 
     p = params(sl.LogModel)
-    assert [k for k in p if k != "dtype"] == ["avg_degree", "edge_init", "maxit", "tol", "step_size", "edge_tol"]
+    extras = {"dtype": "float64", "distributed": False, "weights_on": "all"}
+    assert [k for k in p if k not in extras] == ["avg_degree", "edge_init", "maxit", "tol", "step_size", "edge_tol"]
+    assert {k: p[k] for k in extras} == extras
+    sig = inspect.signature(sl.LogModel.__init__).parameters
+    assert all(sig[k].kind is inspect.Parameter.KEYWORD_ONLY for k in extras)
     assert (p["maxit"], p["tol"], p["step_size"], p["edge_tol"]) == (1000, 1e-5, 0.5, 1e-3)
     p = params(KGraphs)
     assert [k for k in p if k != "dtype"] == ["n_clusters", "avg_degree", "max_iter", "n_init", "init_params", "delta",
