@@ -42,7 +42,7 @@ def _shards(nat, n, world):
 
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
-@pytest.mark.parametrize("n,world,k", [(300, 3, 6), (129, 2, 1), (700, 8, 10), (50, 4, 3)])
+@pytest.mark.parametrize("n,world,k", [(300, 3, 6), (129, 2, 2), (700, 8, 10), (50, 4, 3)])
 def test_theta_partial_merge_equals_full(sl, nat, n, world, k, dtype):
     lib = nat.lib()
     rng = np.random.default_rng(n + k)
