@@ -91,8 +91,8 @@ def main():
     assert rel(w_all, w_one) <= 1e-12 and rel(w_all, orc.to_square(wo)) <= 1e-11
     w_root = sl.gsp_learn_graph_log_degrees(zs, 1, 1, maxit=60, distributed=True, result_on="root")
     assert (w_root is None) == (rank != 0)
-    if rank == 0:
-        assert np.array_equal(w_root, w_all)
+    if rank == 0:   # two runs differ in the last bits (float64 atomics sum the degree partials in run order)
+        assert rel(w_root, w_all) <= 1e-13
     # warm start + z_scale + pinned tensor in + out= on the root
     w0 = np.abs(np.random.default_rng(1).standard_normal(z_np.size)) * 0.01
     zt = torch.from_numpy(z_np / 3.0).pin_memory()
@@ -106,7 +106,7 @@ def main():
     zb = np.stack([z_np, z_np * 1.3])
     wb = sl.gsp_learn_graph_log_degrees(zb, 1, 1, maxit=20, distributed=True)
     wb1 = sl.gsp_learn_graph_log_degrees(zb, 1, 1, maxit=20)
-    assert np.array_equal(wb, wb1)
+    assert rel(wb, wb1) <= 1e-13
     report["function_distributed"] = "ok"
 
     # ---- 3. LogModel.fit distributed: Z tiles per rank, theta from merged candidates -------------------------
