@@ -40,13 +40,11 @@ static __global__ void knn_max_kernel(const int *cnt, int n, int *out) {
 // lab (nullable): node relabelling old -> new (single full-range shard: rows sorted by degree).
 static __global__ void knn_expand_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, int32_t *key, int32_t *val,
                                   int row_begin, int row_end, int n, unsigned long long *count,
-                                  const int32_t *lab, int block_rows) {
+                                  const int32_t *lab) {
   unsigned long long mine = 0;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
     const int i = lab ? lab[ei[e]] : ei[e], j = lab ? lab[ej[e]] : ej[e];
-    // blocked layout (block_rows > 0): an edge inside one block lives in that block's intra list, not here
-    const bool keep = block_rows <= 0 || (i / block_rows) != (j / block_rows);
-    const bool oi = keep && i >= row_begin && i < row_end, oj = keep && j >= row_begin && j < row_end;
+    const bool oi = i >= row_begin && i < row_end, oj = j >= row_begin && j < row_end;
     key[2 * e] = oi ? i : n;
     val[2 * e] = (int32_t)e;
     key[2 * e + 1] = oj ? j : n;
@@ -249,11 +247,9 @@ template <typename F> struct KnnFusedArgs {
   double gamma, four_ag, tol;
 };
 
-// STREAM: the slot arrays (dst, w, z: read once per iteration) are loaded / stored with the
-// cache-streaming (evict-first) policy so that they do not push the gathered (a, b) lines out of the L1;
-// only worth having together with a locality-preserving row order (gl_knn_create_ordered).  Selected
-// with GL_KNN_STREAM=1 in the environment; same arithmetic, same results.
-template <typename F, bool STREAM = false>
+// (Evict-first __ldcs/__stcs slot accesses were measured on B200 in round 2 and lost: 0.154 against
+// 0.085 ms per iteration at n = 1e6 under the Morton order, profiles/r2_knn_row_order_stream.jsonl.)
+template <typename F>
 __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused_kernel(const KnnFusedArgs<F> A) {
   if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][4];
@@ -281,15 +277,9 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
       for (int u = 0; u < KNN_UNROLL; ++u) {
         const long long p = p0 + 32LL * u;
         const bool in = p < end;
-        if constexpr (STREAM) {
-          jj[u] = in ? __ldcs(dst + p) : -1;
-          ww[u] = in ? __ldcs(w + p) : F(0);
-          zv[u] = in ? __ldcs(z + p) : F(0);
-        } else {
-          jj[u] = in ? dst[p] : -1;
-          ww[u] = in ? w[p] : F(0);
-          zv[u] = in ? z[p] : F(0);
-        }
+        jj[u] = in ? dst[p] : -1;
+        ww[u] = in ? w[p] : F(0);
+        zv[u] = in ? z[p] : F(0);
       }
     };
     fetch(base, j, wo, zz);
@@ -307,8 +297,7 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
           const F q = c * pv - (abi.y + abj[u].y);
           const F r = q - y;
           const F wn = (wo[u] - y) + q;
-          if constexpr (STREAM) __stcs(w + p0 + 32LL * u, wn);
-          else w[p0 + 32LL * u] = wn;
+          w[p0 + 32LL * u] = wn;
           acc_p += (double)pv;
           acc_w += (double)wn;
           res += (double)r * (double)r;
@@ -377,275 +366,6 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
   for (int v = 0; v < KNN_THREADS / 32; ++v)
     for (int q = 0; q < 4; ++q) t[q] += s_red[v][q];
   const double g_r = 0.5 * t[0], g_w = 0.5 * t[1];   // every undirected edge appears in two slots
-  A.flags[FLAG_EDGE_TICKET] = 0;
-  const int it = A.flags[FLAG_IT];
-  bool conv = false;
-  if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
-    const double rp = sqrt(g_r) / sqrt(A.gprev[0]);
-    const double rd = sqrt(t[2]) / sqrt(A.gprev[1]);
-    A.resid[0] = rp;
-    A.resid[1] = rd;
-    conv = (rp < A.tol) && (rd < A.tol);  // NaN / inf compare false, like NumPy
-  }
-  A.flags[FLAG_IT] = it + 1;
-  if (conv) A.flags[FLAG_CONVERGED] = 1;
-  if (conv || it + 1 >= A.maxit) A.flags[FLAG_DONE] = 1;
-  A.gprev[0] = g_w;   // denominators of the next check: the iterate before the update (:157-159)
-  A.gprev[1] = t[3];
-}
-
-// ---- blocked layout (single shard; built at the end of round 1, NOT yet run on a device) -------------
-// With a locality-preserving row order most undirected edges have both ends inside one block of
-// KNN_BLOCK_ROWS consecutive rows (oracle.knn_blocked_layout is the executable specification).  Such an
-// edge is stored ONCE in its block's intra list with two 8-bit local row ids (14 B per edge and
-// iteration in fp32 instead of the 32 B of its two slots); the CTA that sweeps the block keeps the
-// block's (gamma d, gamma pb) pairs and both degree accumulators in shared memory and adds the edge's p
-// and w' to both ends there.  All other edges keep the duplicated-slot SELL form.  One CTA trip = one
-// block = KNN_THREADS rows = one slice per warp, so the block's degree sums are complete when its own
-// sweep ends and the node update follows at once, exactly as in knn_fused_kernel.
-// The shared-memory float64 atomics make the summation order of the intra part run-dependent (last-bit
-// differences between runs), unlike the slot form.
-constexpr int KNN_BLOCK_ROWS = KNN_THREADS;   // 256: local ids fit 8 bits, one slice per warp
-constexpr int KNN_INTRA_UNROLL = 4;
-
-// key = block of an intra edge, else the sentinel nblocks; *count receives the number of intra edges
-static __global__ void knn_intra_key_kernel(const int32_t *ei, const int32_t *ej, int64_t nnz, const int32_t *lab,
-                                            int nblocks, int32_t *key, int32_t *val, unsigned long long *count) {
-  unsigned long long mine = 0;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
-    const int bi = lab[ei[e]] / KNN_BLOCK_ROWS, bj = lab[ej[e]] / KNN_BLOCK_ROWS;
-    const bool intra = bi == bj;
-    key[e] = intra ? bi : nblocks;
-    val[e] = (int32_t)e;
-    mine += intra ? 1 : 0;
-  }
-  mine = warp_sum(mine);
-  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(count, mine);
-}
-static __global__ void knn_intra_count_kernel(const int32_t *key_sorted, int64_t n_intra, int *cnt) {
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_intra; t += (int64_t)gridDim.x * blockDim.x)
-    atomicAdd(cnt + key_sorted[t], 1);
-}
-template <typename F>
-__global__ void knn_intra_fill_kernel(const int32_t *ei, const int32_t *ej, const F *z, const F *w, const int32_t *lab,
-                                      const int32_t *eid_sorted, int64_t n_intra, uchar2 *ab_ids, F *z_i, F *w_i,
-                                      int32_t *eid_i) {
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_intra; t += (int64_t)gridDim.x * blockDim.x) {
-    const int32_t e = eid_sorted[t];
-    ab_ids[t] = make_uchar2((unsigned char)(lab[ei[e]] % KNN_BLOCK_ROWS), (unsigned char)(lab[ej[e]] % KNN_BLOCK_ROWS));
-    z_i[t] = z[e];
-    w_i[t] = w[e];
-    eid_i[t] = e;
-  }
-}
-template <typename F>
-__global__ void knn_intra_writeback_kernel(const int32_t *eid_i, const F *w_i, int64_t n_intra, double edge_tol, F *w) {
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_intra; t += (int64_t)gridDim.x * blockDim.x) {
-    const F v = w_i[t];
-    w[eid_i[t]] = (double)v < edge_tol ? F(0) : v;
-  }
-}
-// initial degrees: adds the intra edges' w0 to S w0 (after knn_sell_kernel<F, 1> stored the slot part)
-// and their full ||w0||^2 to gsum[1] (the slot kernel adds half per slot)
-template <typename F>
-__global__ void knn_intra_init_kernel(const int *intra_ptr, const uchar2 *ab_ids, const F *w_i, int nblocks, double *sw,
-                                      double *gsum) {
-  double wsq = 0.0;
-  for (int b = blockIdx.x; b < nblocks; b += gridDim.x) {
-    const int lo = intra_ptr[b], hi = intra_ptr[b + 1];
-    for (int t = lo + threadIdx.x; t < hi; t += blockDim.x) {
-      const uchar2 id = ab_ids[t];
-      const double v = (double)w_i[t];
-      atomicAdd(sw + (int64_t)b * KNN_BLOCK_ROWS + id.x, v);
-      atomicAdd(sw + (int64_t)b * KNN_BLOCK_ROWS + id.y, v);
-      wsq += v * v;
-    }
-  }
-  wsq = warp_sum(wsq);
-  if ((threadIdx.x & 31) == 0 && wsq != 0.0) atomicAdd(gsum + 1, wsq);
-}
-
-template <typename F> struct KnnBlockedArgs {
-  KnnFusedArgs<F> f;
-  const int *intra_ptr;      // [nblocks + 1]
-  const uchar2 *intra_ids;   // local row ids of the two ends
-  const F *intra_z;
-  F *intra_w;
-  int nblocks;
-};
-
-template <typename F>
-__global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_blocked_kernel(const KnnBlockedArgs<F> B) {
-  const KnnFusedArgs<F> &A = B.f;
-  if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
-  using V = typename Vec2<F>::type;
-  __shared__ double s_red[KNN_THREADS / 32][4];
-  __shared__ int s_last;
-  __shared__ V s_ab[KNN_BLOCK_ROWS];
-  __shared__ double s_acc[2][KNN_BLOCK_ROWS];
-  const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
-  const int32_t *__restrict__ dst = A.dst;
-  const F *__restrict__ z = A.z;
-  F *__restrict__ w = A.w;
-  const V *__restrict__ ab = A.ab_in;
-  const F c = A.c, tgz = A.tgz;
-  const int nrows = A.nslices * 32;
-  double res = 0.0, wsq = 0.0, rb2 = 0.0, d2 = 0.0;
-  for (int blk = blockIdx.x; blk < B.nblocks; blk += gridDim.x) {
-    const int me = blk * KNN_BLOCK_ROWS + tid;
-    const bool row_in = me < nrows;
-    V abi;
-    abi.x = abi.y = F(0);
-    if (row_in) abi = ab[me];
-    s_ab[tid] = abi;
-    s_acc[0][tid] = 0.0;
-    s_acc[1][tid] = 0.0;
-    const bool live = me < A.n;
-    // node state of this row: issued now, consumed after the sweeps
-    const double dv = live ? A.d[me] : 0.0, ybv = live ? A.yb[me] : 0.0, pbv = live ? A.pb[me] : 0.0;
-    __syncthreads();
-    // ---- intra edges of the block: stored once, both ends in shared memory -------------------------------
-    {
-      const int lo = B.intra_ptr[blk], hi = B.intra_ptr[blk + 1];
-      for (int t0 = lo + tid; t0 < hi; t0 += KNN_THREADS * KNN_INTRA_UNROLL) {
-        uchar2 id[KNN_INTRA_UNROLL];
-        F wo[KNN_INTRA_UNROLL], zz[KNN_INTRA_UNROLL];
-#pragma unroll
-        for (int u = 0; u < KNN_INTRA_UNROLL; ++u) {
-          const int t = t0 + u * KNN_THREADS;
-          const bool in = t < hi;
-          id[u] = in ? __ldcs(B.intra_ids + t) : make_uchar2(0, 0);
-          wo[u] = in ? __ldcs(B.intra_w + t) : F(0);
-          zz[u] = in ? __ldcs(B.intra_z + t) : F(0);
-        }
-#pragma unroll
-        for (int u = 0; u < KNN_INTRA_UNROLL; ++u) {
-          const int t = t0 + u * KNN_THREADS;
-          if (t < hi) {
-            const V pa = s_ab[id[u].x], pe = s_ab[id[u].y];
-            const F y = c * wo[u] - (pa.x + pe.x);
-            F pv = y - tgz * zz[u];
-            pv = pv > F(0) ? pv : F(0);
-            const F q = c * pv - (pa.y + pe.y);
-            const F r = q - y;
-            const F wn = (wo[u] - y) + q;
-            __stcs(B.intra_w + t, wn);
-            atomicAdd(&s_acc[0][id[u].x], (double)pv);
-            atomicAdd(&s_acc[0][id[u].y], (double)pv);
-            atomicAdd(&s_acc[1][id[u].x], (double)wn);
-            atomicAdd(&s_acc[1][id[u].y], (double)wn);
-            res += 2.0 * (double)r * (double)r;     // the slot sums below are halved at the end
-            wsq += 2.0 * (double)wn * (double)wn;
-          }
-        }
-      }
-    }
-    // ---- inter slots of this warp's slice (the sweep of knn_fused_kernel) --------------------------------
-    double acc_p = 0.0, acc_w = 0.0;
-    const int s = blk * (KNN_BLOCK_ROWS / 32) + wp;
-    if (s < A.nslices) {
-      const long long base = A.slice_off[s] + lane, end = A.slice_off[s + 1];
-      int j[KNN_UNROLL], jn[KNN_UNROLL];
-      F wo[KNN_UNROLL], zz[KNN_UNROLL], won[KNN_UNROLL], zzn[KNN_UNROLL];
-      auto fetch = [&](long long p0, int *jj, F *ww, F *zv) {
-#pragma unroll
-        for (int u = 0; u < KNN_UNROLL; ++u) {
-          const long long p = p0 + 32LL * u;
-          const bool in = p < end;
-          jj[u] = in ? __ldcs(dst + p) : -1;
-          ww[u] = in ? __ldcs(w + p) : F(0);
-          zv[u] = in ? __ldcs(z + p) : F(0);
-        }
-      };
-      fetch(base, j, wo, zz);
-      for (long long p0 = base; p0 < end; p0 += 32LL * KNN_UNROLL) {
-        V abj[KNN_UNROLL];
-#pragma unroll
-        for (int u = 0; u < KNN_UNROLL; ++u) abj[u] = ab[j[u] < 0 ? me : j[u]];   // far end: one gather
-        fetch(p0 + 32LL * KNN_UNROLL, jn, won, zzn);
-#pragma unroll
-        for (int u = 0; u < KNN_UNROLL; ++u)
-          if (j[u] >= 0) {
-            const F y = c * wo[u] - (abi.x + abj[u].x);
-            F pv = y - tgz * zz[u];
-            pv = pv > F(0) ? pv : F(0);
-            const F q = c * pv - (abi.y + abj[u].y);
-            const F r = q - y;
-            const F wn = (wo[u] - y) + q;
-            __stcs(w + p0 + 32LL * u, wn);
-            acc_p += (double)pv;
-            acc_w += (double)wn;
-            res += (double)r * (double)r;
-            wsq += (double)wn * (double)wn;
-          }
-#pragma unroll
-        for (int u = 0; u < KNN_UNROLL; ++u) {
-          j[u] = jn[u];
-          wo[u] = won[u];
-          zz[u] = zzn[u];
-        }
-      }
-    }
-    __syncthreads();   // every intra contribution of the block has landed
-    acc_p += s_acc[0][tid];
-    acc_w += s_acc[1][tid];
-    // ---- node update of row `me` (the arithmetic of knn_node_kernel) -------------------------------------
-    V pr;
-    pr.x = pr.y = F(0);
-    if (live) {
-      const double qb = pbv + A.gamma * acc_p;                    //                      :154
-      const double rbv = qb - ybv;
-      const double dn = (dv - ybv) + qb;                          //                      :164
-      const double ybn = dn + A.gamma * acc_w;                    //                      :148
-      const double pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;   //                  :151
-      rb2 += rbv * rbv;
-      d2 += dn * dn;
-      A.d[me] = dn;
-      A.yb[me] = ybn;
-      A.pb[me] = pbn;
-      pr.x = (F)(A.gamma * dn);
-      pr.y = (F)(A.gamma * pbn);
-    }
-    if (row_in) A.ab_out[me] = pr;
-    __syncthreads();   // the next trip rewrites s_ab / s_acc
-  }
-  res = warp_sum(res);
-  wsq = warp_sum(wsq);
-  rb2 = warp_sum(rb2);
-  d2 = warp_sum(d2);
-  if (lane == 0) {
-    s_red[wp][0] = res;
-    s_red[wp][1] = wsq;
-    s_red[wp][2] = rb2;
-    s_red[wp][3] = d2;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double t[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int q = 0; q < KNN_THREADS / 32; ++q)
-      for (int i = 0; i < 4; ++i) t[i] += s_red[q][i];
-    for (int i = 0; i < 4; ++i) A.part[4 * blockIdx.x + i] = t[i];
-    __threadfence();
-    const int ticket = atomicAdd(A.flags + FLAG_EDGE_TICKET, 1);
-    s_last = (ticket == (int)gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  // ---- last CTA: sums over the CTAs in a fixed order, stop rule (smooth_learning.py:156-166) -----------
-  double t[4] = {0.0, 0.0, 0.0, 0.0};
-  for (int i = threadIdx.x; i < (int)gridDim.x; i += KNN_THREADS)
-    for (int q = 0; q < 4; ++q) t[q] += __ldcg(A.part + 4 * i + q);
-  for (int q = 0; q < 4; ++q) t[q] = warp_sum(t[q]);
-  __syncthreads();
-  if (lane == 0)
-    for (int q = 0; q < 4; ++q) s_red[wp][q] = t[q];
-  __syncthreads();
-  if (threadIdx.x != 0) return;
-  for (int q = 0; q < 4; ++q) t[q] = 0.0;
-  for (int v = 0; v < KNN_THREADS / 32; ++v)
-    for (int q = 0; q < 4; ++q) t[q] += s_red[v][q];
-  const double g_r = 0.5 * t[0], g_w = 0.5 * t[1];   // slots count every edge twice, intra edges were doubled
   A.flags[FLAG_EDGE_TICKET] = 0;
   const int it = A.flags[FLAG_IT];
   bool conv = false;

@@ -32,13 +32,6 @@ struct gl_knn_solver {
   double *part = nullptr;           // fused == 2: [CTAs][4] residual partials
   int parity = 0;                   // fused == 2: which buffer the next iteration READS
   double *scal = nullptr;      // [4] partial sums for the exchange
-  // blocked layout (knn_kernels.cuh, single full-range shard, one-launch iteration only)
-  int blocked = 0, nblocks = 0;
-  int64_t n_intra = 0;
-  int *intra_ptr = nullptr;         // [nblocks + 1]
-  uchar2 *intra_ids = nullptr;
-  void *intra_z = nullptr, *intra_w = nullptr;
-  int32_t *intra_eid = nullptr;
 };
 
 namespace gl {
@@ -127,86 +120,7 @@ static int knn_create_t(gl_knn_solver *k, const int32_t *ei, const int32_t *ej, 
     g_launches.fetch_add(3);
     KS_CUDA(cudaGetLastError());
   }
-  if (k->blocked) {
-    // ---- intra lists: edges with both ends in one block of KNN_BLOCK_ROWS rows, stored once ------------
-    if (!lab) {
-      cleanup();
-      return fail(GL_E_STATE, "the blocked layout needs a single shard owning all rows");
-    }
-    k->nblocks = (k->s->npad + KNN_BLOCK_ROWS - 1) / KNN_BLOCK_ROWS;
-    int32_t *ikey = nullptr, *ival = nullptr, *ikey_s = nullptr, *ival_s = nullptr;
-    int *icnt = nullptr;
-    void *itmp = nullptr;
-    auto icleanup = [&]() {
-      for (void *q : {(void *)ikey, (void *)ival, (void *)ikey_s, (void *)ival_s, (void *)icnt, itmp})
-        if (q) cudaFree(q);
-    };
-#define KI_CUDA(expr)                                                                                      \
-  do {                                                                                                     \
-    cudaError_t _e = (expr);                                                                               \
-    if (_e != cudaSuccess) {                                                                               \
-      icleanup();                                                                                          \
-      cleanup();                                                                                           \
-      return fail(GL_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
-    }                                                                                                      \
-  } while (0)
-    const size_t eb = sizeof(int32_t) * (size_t)nnz;
-    KI_CUDA(cudaMalloc((void **)&ikey, eb));
-    KI_CUDA(cudaMalloc((void **)&ival, eb));
-    KI_CUDA(cudaMalloc((void **)&ikey_s, eb));
-    KI_CUDA(cudaMalloc((void **)&ival_s, eb));
-    KI_CUDA(cudaMalloc((void **)&icnt, sizeof(int) * (size_t)(k->nblocks + 1)));
-    KI_CUDA(cudaMalloc((void **)&k->intra_ptr, sizeof(int) * (size_t)(k->nblocks + 1)));
-    KI_CUDA(cudaMemsetAsync(icnt, 0, sizeof(int) * (size_t)(k->nblocks + 1), st));
-    knn_intra_key_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, lab, k->nblocks, ikey, ival, count);
-    g_launches.fetch_add(1);
-    int ibits = 1;
-    while (ibits < 31 && ((int64_t)1 << ibits) <= (int64_t)k->nblocks) ++ibits;   // the sentinel nblocks must fit
-    size_t ib2 = 0;
-    KI_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, ib2, ikey, ikey_s, ival, ival_s, (int)nnz, 0, ibits, st));
-    KI_CUDA(cudaMalloc(&itmp, ib2 ? ib2 : 16));
-    KI_CUDA(cub::DeviceRadixSort::SortPairs(itmp, ib2, ikey, ikey_s, ival, ival_s, (int)nnz, 0, ibits, st));
-    unsigned long long h_intra = 0;
-    KI_CUDA(cudaMemcpyAsync(&h_intra, count, sizeof(h_intra), cudaMemcpyDeviceToHost, st));
-    KI_CUDA(cudaStreamSynchronize(st));
-    KI_CUDA(cudaMemsetAsync(count, 0, sizeof(unsigned long long), st));   // reused by the slot expansion below
-    k->n_intra = (int64_t)h_intra;
-    if (k->n_intra > 0) {
-      const int igrid = (int)std::min<int64_t>((k->n_intra + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
-      knn_intra_count_kernel<<<igrid, KNN_THREADS, 0, st>>>(ikey_s, k->n_intra, icnt);
-      g_launches.fetch_add(1);
-    }
-    {
-      size_t sb = 0;
-      KI_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sb, icnt, k->intra_ptr, k->nblocks + 1, st));
-      KI_CUDA(cudaFree(itmp));
-      itmp = nullptr;
-      KI_CUDA(cudaMalloc(&itmp, sb ? sb : 16));
-      KI_CUDA(cub::DeviceScan::ExclusiveSum(itmp, sb, icnt, k->intra_ptr, k->nblocks + 1, st));
-    }
-    if (k->n_intra > 0) {
-      const size_t cnt_i = (size_t)k->n_intra;
-      KI_CUDA(cudaMalloc((void **)&k->intra_ids, sizeof(uchar2) * cnt_i));
-      KI_CUDA(cudaMalloc(&k->intra_z, sizeof(F) * cnt_i));
-      KI_CUDA(cudaMalloc(&k->intra_w, sizeof(F) * cnt_i));
-      KI_CUDA(cudaMalloc((void **)&k->intra_eid, sizeof(int32_t) * cnt_i));
-      const F *w_init = w0;
-      if (!w_init) {
-        KI_CUDA(cudaMalloc((void **)&w_zero, sizeof(F) * (size_t)nnz));
-        KI_CUDA(cudaMemsetAsync(w_zero, 0, sizeof(F) * (size_t)nnz, st));
-        w_init = w_zero;
-      }
-      const int igrid = (int)std::min<int64_t>((k->n_intra + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
-      knn_intra_fill_kernel<F><<<igrid, KNN_THREADS, 0, st>>>(ei, ej, z, w_init, lab, ival_s, k->n_intra, k->intra_ids,
-                                                              (F *)k->intra_z, (F *)k->intra_w, k->intra_eid);
-      g_launches.fetch_add(1);
-    }
-    KI_CUDA(cudaStreamSynchronize(st));
-    icleanup();
-#undef KI_CUDA
-  }
-  knn_expand_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, key_in, val_in, k->row_begin, k->row_end, n, count, lab,
-                                                  k->blocked ? KNN_BLOCK_ROWS : 0);
+  knn_expand_kernel<<<grid, KNN_THREADS, 0, st>>>(ei, ej, nnz, key_in, val_in, k->row_begin, k->row_end, n, count, lab);
   g_launches.fetch_add(1);
   int bits = 1;
   while (bits < 31 && ((int64_t)1 << bits) <= (int64_t)n) ++bits;   // the sentinel key n must fit
@@ -336,27 +250,7 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
   const int grid = std::max(1, std::min((k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32), KNN_FUSED_MAX_GRID));
-  if (k->blocked) {
-    KnnBlockedArgs<F> B;
-    B.f = A;
-    B.intra_ptr = k->intra_ptr;
-    B.intra_ids = k->intra_ids;
-    B.intra_z = (const F *)k->intra_z;
-    B.intra_w = (F *)k->intra_w;
-    B.nblocks = k->nblocks;
-    knn_blocked_kernel<F><<<std::max(1, std::min(k->nblocks, KNN_FUSED_MAX_GRID)), KNN_THREADS, 0, st>>>(B);
-    GL_LAUNCH_CHECK();
-    k->parity ^= 1;
-    return GL_OK;
-  }
-  static const bool stream_loads = [] {
-    const char *e = getenv("GL_KNN_STREAM");   // evict-first slot loads (knn_kernels.cuh); off by default
-    return e && atoi(e) != 0;
-  }();
-  if (stream_loads)
-    knn_fused_kernel<F, true><<<grid, KNN_THREADS, 0, st>>>(A);
-  else
-    knn_fused_kernel<F, false><<<grid, KNN_THREADS, 0, st>>>(A);
+  knn_fused_kernel<F><<<grid, KNN_THREADS, 0, st>>>(A);
   GL_LAUNCH_CHECK();
   k->parity ^= 1;
   return GL_OK;
@@ -415,7 +309,9 @@ extern "C" int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei, con
                                      int64_t ab_len, const int32_t *order_key, int sort_window, int layout,
                                      void *stream) {
   if (!out) return fail(GL_E_ARG, "null output");
-  if (layout != 0 && layout != 1) return fail(GL_E_ARG, "layout must be 0 (slots) or 1 (blocked)");
+  if (layout != 0)
+    return fail(GL_E_ARG, "layout must be 0 (directed slots); the blocked single-copy layout of round 1 measured slower "
+                          "on B200 (profiles/r2_knn_row_order.jsonl) and was removed");
   *out = nullptr;
   if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
   if (nnz < 0 || 2 * nnz >= ((int64_t)1 << 31)) return fail(GL_E_SHAPE, "bad edge count %lld", (long long)nnz);
@@ -432,13 +328,6 @@ extern "C" int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei, con
   k->row_begin = row_begin;
   k->row_end = std::min(row_end, k->s->npad);
   k->ab_len = std::max<int64_t>(ab_len, k->s->npad);
-  if (layout == 1) {
-    if (k->row_begin != 0 || k->row_end < k->s->npad) {
-      gl_knn_destroy(k);
-      return fail(GL_E_STATE, "the blocked layout needs a single shard owning all rows");
-    }
-    k->blocked = 1;
-  }
   const size_t esz = dtype == GL_F32 ? 4 : 8;
   cudaStream_t st = as_stream(stream);
   cudaError_t e = cudaMalloc(&k->s->ab, 2 * esz * (size_t)k->ab_len);
@@ -462,8 +351,7 @@ extern "C" int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei, con
 extern "C" int gl_knn_destroy(gl_knn_solver *k) {
   if (!k) return GL_OK;
   for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal, k->ab2,
-                  (void *)k->part, (void *)k->intra_ptr, (void *)k->intra_ids, k->intra_z, k->intra_w,
-                  (void *)k->intra_eid})
+                  (void *)k->part})
     if (q) cudaFree(q);
   if (k->s) gl_solver_destroy(k->s);
   delete k;
@@ -472,7 +360,6 @@ extern "C" int gl_knn_destroy(gl_knn_solver *k) {
 
 extern "C" int64_t gl_knn_local_slots(gl_knn_solver *k) { return k ? k->nslots : -1; }
 extern "C" int64_t gl_knn_padded_slots(gl_knn_solver *k) { return k ? (int64_t)k->total : -1; }
-extern "C" int64_t gl_knn_intra_edges(gl_knn_solver *k) { return k ? k->n_intra : -1; }
 
 extern "C" int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
                             int dmax, void *stream) {
@@ -484,27 +371,11 @@ extern "C" int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double 
   s->c = 1.0 - 2.0 * s->gamma * beta;
   GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
   GL_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
-  if (k->blocked && k->fused != 2) return fail(GL_E_STATE, "the blocked layout runs only as gl_knn_set_fused(k, 2)");
-  auto intra_init = [&]() -> int {
-    if (!k->blocked || k->n_intra == 0) return GL_OK;
-    double *sw = s->xch + s->npad, *gsum = s->xch + 2 * (int64_t)s->npad;
-    const int grid = std::max(1, std::min(k->nblocks, 148 * 8));
-    if (k->dtype == GL_F32)
-      knn_intra_init_kernel<float><<<grid, KNN_THREADS, 0, st>>>(k->intra_ptr, k->intra_ids, (const float *)k->intra_w,
-                                                                 k->nblocks, sw, gsum);
-    else
-      knn_intra_init_kernel<double><<<grid, KNN_THREADS, 0, st>>>(k->intra_ptr, k->intra_ids, (const double *)k->intra_w,
-                                                                  k->nblocks, sw, gsum);
-    GL_LAUNCH_CHECK();
-    return GL_OK;
-  };
   if (k->dtype == GL_F32) {
     GL_TRY(knn_slot_launch<float>(k, true, st));
-    GL_TRY(intra_init());
     GL_TRY(knn_node_launch<float>(k, true, st));
   } else {
     GL_TRY(knn_slot_launch<double>(k, true, st));
-    GL_TRY(intra_init());
     GL_TRY(knn_node_launch<double>(k, true, st));
   }
   s->begun = true;
@@ -554,16 +425,6 @@ extern "C" int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, 
 extern "C" int gl_knn_store(gl_knn_solver *k, void *w_out, double edge_tol, void *stream) {
   if (!k) return fail(GL_E_ARG, "null solver");
   cudaStream_t st = as_stream(stream);
-  if (k->blocked && k->n_intra > 0) {
-    const int igrid = (int)std::min<int64_t>((k->n_intra + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
-    if (k->dtype == GL_F32)
-      knn_intra_writeback_kernel<float><<<igrid, KNN_THREADS, 0, st>>>(k->intra_eid, (const float *)k->intra_w,
-                                                                      k->n_intra, edge_tol, (float *)w_out);
-    else
-      knn_intra_writeback_kernel<double><<<igrid, KNN_THREADS, 0, st>>>(k->intra_eid, (const double *)k->intra_w,
-                                                                       k->n_intra, edge_tol, (double *)w_out);
-    GL_LAUNCH_CHECK();
-  }
   if (k->total == 0) return GL_OK;
   const int grid = (int)std::min<long long>((k->total + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
   if (k->dtype == GL_F32)
@@ -580,7 +441,6 @@ extern "C" int gl_knn_store(gl_knn_solver *k, void *w_out, double edge_tol, void
 extern "C" int gl_knn_set_fused(gl_knn_solver *k, int fused) {
   if (!k) return fail(GL_E_ARG, "null solver");
   if (fused < 0 || fused > 2) return fail(GL_E_ARG, "fused must be 0, 1 or 2");
-  if (k->blocked && fused != 2) return fail(GL_E_STATE, "the blocked layout runs only as the one-launch iteration");
   if (fused == 2) {
     if (k->row_begin != 0 || k->row_end != k->s->npad)
       return fail(GL_E_STATE, "the one-launch iteration needs a single shard owning all rows");

@@ -110,19 +110,17 @@ def theta_from_knn(d2_sorted: torch.Tensor, avg_degree: int) -> float:
 def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: float = 1.0, beta: float = 1.0,
                                     edge_init=None, maxit: int = 1000, tol: float = 1e-5, step_size: float = 0.5,
                                     edge_tol: float = 1e-3, *, dtype=None, return_info: bool = False,
-                                    order_key=None, sort_window: int = 0, layout: str = "slots"):
+                                    order_key=None, sort_window: int = 0):
     """Edge weights on the support {(ei[k], ej[k])}, ei < ej, from the (theta-scaled) squared
     distances of those edges.  Returns an array shaped like ``distances`` (NumPy in -> NumPy out).
     Step size: gamma = step_size / (2 beta + sqrt(2 d_max)), d_max the largest support degree.
 
     ``order_key`` ((n_nodes,) non-negative int32, e.g. :func:`locality_keys`) and ``sort_window``
-    choose the solver's INTERNAL row order (``gl_knn_create_ordered`` in include/gl_b200.h); the
-    defaults are the global degree sort.  ``layout="blocked"`` stores an edge whose two ends fall into
-    the same 256-row block once instead of as two slots (meant for a locality-preserving order such
-    as ``order_key=locality_keys(x), sort_window=256``).  All of these change memory traffic and
-    locality, never the result beyond the rounding of the degree sums' summation order."""
-    if layout not in ("slots", "blocked"):
-        raise ValueError('layout must be "slots" or "blocked"')
+    choose the solver's INTERNAL row order (``gl_knn_create_ordered`` in include/gl_b200.h); without a
+    key the rows are sorted by decreasing degree over the caller's numbering.  With Morton keys the far
+    ends of a CTA's rows fall into a few KB of the node array (0.085 against 0.127 ms per iteration at
+    n = 1e6 on B200).  The order changes memory traffic and locality, never the result beyond the
+    rounding of the degree sums' summation order."""
     is_np = not isinstance(distances, torch.Tensor)
     if dtype is None and getattr(distances, "dtype", None) in (np.float32, torch.float32):
         dtype = torch.float32
@@ -138,7 +136,7 @@ def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: floa
     w = torch.zeros_like(z) if edge_init is None else _to_device(edge_init, dt).clone()
     it = ctypes.c_int()
     rp, rd = ctypes.c_double(), ctypes.c_double()
-    if order_key is None and int(sort_window) == 0 and layout == "slots":
+    if order_key is None and int(sort_window) == 0:
         nat.check(nat.lib().gl_knn_logmodel_solve(_ptr(i32), _ptr(j32), _ptr(z), z.numel(), int(n_nodes),
                                                   _gl_dtype(dt), float(alpha), float(beta), int(maxit), float(tol),
                                                   float(step_size), float(edge_tol), _ptr(w), ctypes.byref(it),
@@ -154,8 +152,7 @@ def gsp_learn_graph_log_degrees_knn(ei, ej, distances, n_nodes: int, alpha: floa
         nat.check(nat.lib().gl_knn_logmodel_solve_ordered(
             _ptr(i32), _ptr(j32), _ptr(z), z.numel(), int(n_nodes), _gl_dtype(dt), float(alpha), float(beta),
             int(maxit), float(tol), float(step_size), float(edge_tol), _ptr(w), ctypes.byref(it), ctypes.byref(rp),
-            ctypes.byref(rd), _ptr(key) if key is not None else None, int(sort_window),
-            1 if layout == "blocked" else 0, _stream()))
+            ctypes.byref(rd), _ptr(key) if key is not None else None, int(sort_window), 0, _stream()))
     info = SolveInfo(it.value, rp.value, rd.value, bool(rp.value < tol and rd.value < tol))
     out = w.cpu().numpy() if is_np else w
     return (out, info) if return_info else out
@@ -169,16 +166,15 @@ class KNNLogModel(BaseEstimator):
     Attributes: ``edges_`` (2, nnz) int32 with ei < ej, ``weights_`` (nnz,), ``theta_``,
     ``n_iter_``; :meth:`to_sparse` gives the symmetric scipy CSR matrix.
 
-    ``locality_order`` / ``sort_window`` / ``layout`` choose the solver's internal row order and edge
-    layout (see :func:`gsp_learn_graph_log_degrees_knn`); they never change what is returned.  They were
-    added after round 1's last device run and are off by default until measured."""
+    ``locality_order`` (default True: Morton arrangement of the rows from the three features of largest
+    variance, then a stable global degree sort) / ``sort_window`` choose the solver's internal row
+    order (see :func:`gsp_learn_graph_log_degrees_knn`); they never change what is returned."""
 
     def __init__(self, avg_degree: int = 10, n_neighbors: int = 20, *, maxit: int = 1000, tol: float = 1e-5,
-                 step_size: float = 0.5, edge_tol: float = 1e-3, locality_order: bool = False,
-                 sort_window: int = 0, layout: str = "slots") -> None:
+                 step_size: float = 0.5, edge_tol: float = 1e-3, locality_order: bool = True,
+                 sort_window: int = 0) -> None:
         self.locality_order = locality_order   # Morton arrangement of the rows (locality_keys)
         self.sort_window = sort_window         # degree sort inside windows of this many rows (0: global)
-        self.layout = layout                   # "slots" | "blocked" (intra-block edges stored once)
         self.avg_degree = avg_degree
         self.n_neighbors = n_neighbors
         self.maxit = maxit
@@ -195,7 +191,7 @@ class KNNLogModel(BaseEstimator):
                                                   tol=self.tol, step_size=self.step_size, edge_tol=self.edge_tol,
                                                   return_info=True,
                                                   order_key=locality_keys(x).to(d2.device) if self.locality_order
-                                                  else None, sort_window=self.sort_window, layout=self.layout)
+                                                  else None, sort_window=self.sort_window)
         edges = torch.stack([ei, ej])
         self.edges_ = edges.cpu().numpy() if is_np else edges
         self.weights_ = w.cpu().numpy() if is_np else w

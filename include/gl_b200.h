@@ -270,12 +270,8 @@ int gl_knn_create(gl_knn_solver **out, const int32_t *ei_dev, const int32_t *ej_
  * inside windows of that many consecutive positions of the arrangement (SELL-C-sigma: padding stays
  * small and the far ends of a CTA's rows stay within a few KB of the (a, b) array); 0: one window
  * (global sort, the arrangement only breaks ties); < 0: the arrangement as it is.
- * layout 0: every edge as two directed slots (the form above).  layout 1 (blocked; one-launch
- * iteration only, i.e. gl_knn_set_fused(k, 2) before gl_knn_begin): an edge whose two ends fall into
- * the same block of 256 consecutive rows is stored once with two 8-bit local row ids and updates both
- * ends in the sweeping CTA's shared memory; the other edges keep their two slots.  Pays off with a
- * locality-preserving order (two thirds of a kNN graph's edges are intra-block under a Morton key
- * with sort_window 256).  gl_knn_intra_edges reports how many edges took the single-copy form. */
+ * layout must be 0 (every edge as two directed slots, the form above); a blocked single-copy layout
+ * was built in round 1, measured slower on B200 in round 2 and removed. */
 int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei_dev, const int32_t *ej_dev,
                           const void *z_dev, const void *w0_dev, int64_t nnz, int n, int dtype,
                           int row_begin, int row_end, int64_t ab_len, const int32_t *order_key_dev,
@@ -290,7 +286,6 @@ int gl_knn_destroy(gl_knn_solver *k);
 int64_t gl_knn_local_slots(gl_knn_solver *k);
 /* entries of the SELL arrays including padding (gl_knn_local_slots counts the live ones) */
 int64_t gl_knn_padded_slots(gl_knn_solver *k);
-int64_t gl_knn_intra_edges(gl_knn_solver *k);
 /* Single shard only.  1: the node step applies the stop rule itself (gl_knn_decide becomes a no-op).
  * 2: the whole iteration -- slot sweep, node update, stop rule -- runs inside gl_knn_edge_step as ONE
  * launch (gl_knn_node_step and gl_knn_decide become no-ops); choose before gl_knn_begin. */

@@ -410,139 +410,6 @@ def knn_padded_slots(ei, ej, n: int, order: np.ndarray, slice_rows: int = 32) ->
     return int(slice_rows * d.max(axis=1).sum())
 
 
-def knn_blocked_layout(ei, ej, n: int, order: np.ndarray, block: int = 256) -> dict:
-    """Executable specification of the PLANNED blocked kNN layout ("What the arrangement
-    makes possible next"; no kernel uses it yet, no reference code, A9).  Rows are the nodes in
-    ``order``; a block is ``block`` consecutive rows.  An edge whose two ends fall into the same block is
-    stored ONCE in that block's intra list with two local row ids; every other edge keeps two directed
-    slots (source row, far-end row).  Returns row-space arrays:
-      intra_ptr (nblocks+1), intra_a / intra_b (local ids, uint8 when block <= 256), intra_eid,
-      slot_ptr (nrows+1), slot_dst (row ids), slot_eid, slot_first (True on the copy whose source is
-      the edge's first end), and bytes_per_edge = modelled fp32 traffic per undirected edge and iteration.
-    """
-    ei = np.asarray(ei, dtype=np.int64)
-    ej = np.asarray(ej, dtype=np.int64)
-    lab = np.empty(n, dtype=np.int64)
-    lab[np.asarray(order)] = np.arange(n)
-    a, b = lab[ei], lab[ej]
-    nblocks = -(-n // block)
-    intra = (a // block) == (b // block)
-    eid = np.arange(len(ei))
-    # intra lists: by block, edge order inside a block
-    ia, ib, ie = a[intra], b[intra], eid[intra]
-    o = np.lexsort((ie, ia // block))
-    ia, ib, ie = ia[o], ib[o], ie[o]
-    intra_ptr = np.searchsorted(ia // block, np.arange(nblocks + 1))
-    loc = np.uint8 if block <= 256 else np.uint16
-    # inter slots: two per edge, grouped by source row, edge order inside a row
-    xa, xb, xe = a[~intra], b[~intra], eid[~intra]
-    src = np.concatenate([xa, xb])
-    dst = np.concatenate([xb, xa])
-    se = np.concatenate([xe, xe])
-    first = np.concatenate([np.ones(len(xa), dtype=bool), np.zeros(len(xa), dtype=bool)])
-    o = np.lexsort((se, src))
-    src, dst, se, first = src[o], dst[o], se[o], first[o]
-    slot_ptr = np.searchsorted(src, np.arange(n + 1))
-    n_intra, n_inter = int(intra.sum()), int((~intra).sum())
-    bytes_per_edge = (n_intra * (2 * np.dtype(loc).itemsize + 12) + n_inter * 32) / max(1, len(ei))
-    return {"lab": lab, "block": block, "nblocks": nblocks, "intra_ptr": intra_ptr,
-            "intra_a": (ia % block).astype(loc), "intra_b": (ib % block).astype(loc), "intra_eid": ie,
-            "slot_ptr": slot_ptr, "slot_dst": dst, "slot_eid": se, "slot_first": first,
-            "intra_fraction": n_intra / max(1, len(ei)), "bytes_per_edge": bytes_per_edge}
-
-
-def solve_knn_blocked(ei, ej, z, n, layout: dict, alpha=1.0, beta=1.0, edge_init=None, maxit=1000, tol=1e-5,
-                      step_size=0.5, edge_tol=1e-3, *, threshold=True):
-    """solve_knn executed THROUGH the blocked layout, block by block, the way one CTA per block would:
-    intra edges update both of their ends in the block's local accumulators, inter slots only their
-    source row, the node update of a block follows as soon as its own sweep is done (its rows' degree
-    sums are complete), and other blocks keep reading the OLD (gamma d, gamma pb) pairs (double
-    buffer).  Same iterates as solve_knn up to the summation order of the degree sums."""
-    ei = np.asarray(ei, dtype=np.int64)
-    ej = np.asarray(ej, dtype=np.int64)
-    z = np.asarray(z, dtype=np.float64)
-    L = layout
-    block, lab = L["block"], L["lab"]
-    dmax = int(np.max(np.bincount(ei, minlength=n) + np.bincount(ej, minlength=n)))
-    g = step_size / (2.0 * beta + np.sqrt(2.0 * dmax))
-    c = 1.0 - 2.0 * g * beta
-    w_edge = np.zeros_like(z) if edge_init is None else np.asarray(edge_init, dtype=np.float64).copy()
-    w_intra = w_edge[L["intra_eid"]].copy()          # one copy per intra edge
-    w_slot = w_edge[L["slot_eid"]].copy()            # one copy per directed slot
-    z_intra, z_slot = z[L["intra_eid"]], z[L["slot_eid"]]
-    slot_src = np.repeat(np.arange(n), np.diff(L["slot_ptr"]))
-
-    def degrees(vi, vs):                              # row-space degree sums of (intra, slot) values
-        out = np.bincount(slot_src, vs, n).astype(np.float64)
-        blk = np.repeat(np.arange(L["nblocks"]), np.diff(L["intra_ptr"])) * block
-        out += np.bincount(blk + L["intra_a"], vi, n) + np.bincount(blk + L["intra_b"], vi, n)
-        return out
-
-    d = degrees(w_intra, w_slot)                      # row space throughout
-    sw = d.copy()
-    yb = d + g * sw
-    pb = (yb - np.sqrt(yb * yb + 4.0 * alpha * g)) / 2.0
-    ab = np.stack([g * d, g * pb])                    # the pairs the sweeps gather
-    rp = rd = np.inf
-    it, converged = 0, False
-    for it in range(1, maxit + 1):
-        res = wsq_old = rb2 = d2_old = 0.0
-        d_new = np.empty(n)
-        for blk in range(L["nblocks"]):
-            r0, r1 = blk * block, min(n, (blk + 1) * block)
-            acc_p, acc_w = np.zeros(r1 - r0), np.zeros(r1 - r0)
-            # --- intra edges of the block: both ends local ---
-            lo, hi = L["intra_ptr"][blk], L["intra_ptr"][blk + 1]
-            la, lb = L["intra_a"][lo:hi].astype(np.int64), L["intra_b"][lo:hi].astype(np.int64)
-            wo = w_intra[lo:hi]
-            y = c * wo - (ab[0, r0 + la] + ab[0, r0 + lb])
-            p = np.maximum(y - 2.0 * g * z_intra[lo:hi], 0.0)
-            q = c * p - (ab[1, r0 + la] + ab[1, r0 + lb])
-            wn = (wo - y) + q
-            np.add.at(acc_p, la, p); np.add.at(acc_p, lb, p)
-            np.add.at(acc_w, la, wn); np.add.at(acc_w, lb, wn)
-            res += np.sum((q - y) ** 2); wsq_old += np.sum(wo ** 2)
-            w_intra[lo:hi] = wn
-            # --- inter slots of the block's rows: source row only, far end gathered ---
-            lo, hi = L["slot_ptr"][r0], L["slot_ptr"][r1]
-            srow, drow = slot_src[lo:hi], L["slot_dst"][lo:hi]
-            wo = w_slot[lo:hi]
-            y = c * wo - (ab[0, srow] + ab[0, drow])
-            p = np.maximum(y - 2.0 * g * z_slot[lo:hi], 0.0)
-            q = c * p - (ab[1, srow] + ab[1, drow])
-            wn = (wo - y) + q
-            np.add.at(acc_p, srow - r0, p); np.add.at(acc_w, srow - r0, wn)
-            res += 0.5 * np.sum((q - y) ** 2); wsq_old += 0.5 * np.sum(wo ** 2)   # every inter edge twice
-            w_slot[lo:hi] = wn
-            # --- node update of the block (smooth_learning.py:148-164) ---
-            rows = slice(r0, r1)
-            yb_b = d[rows] + g * sw[rows]
-            pb_b = (yb_b - np.sqrt(yb_b * yb_b + 4.0 * alpha * g)) / 2.0
-            rbv = pb_b + g * acc_p - yb_b
-            d_new[rows] = d[rows] + rbv
-            rb2 += np.sum(rbv ** 2); d2_old += np.sum(d[rows] ** 2)
-            sw[rows] = acc_w
-        if it > 1:
-            with np.errstate(divide="ignore", invalid="ignore"):
-                rp = np.sqrt(res) / np.sqrt(wsq_old)
-                rd = np.sqrt(rb2) / np.sqrt(d2_old)
-        d = d_new
-        yb = d + g * sw
-        pb = (yb - np.sqrt(yb * yb + 4.0 * alpha * g)) / 2.0
-        ab = np.stack([g * d, g * pb])
-        if rp < tol and rd < tol:
-            converged = True
-            break
-    else:
-        it = maxit
-    w = np.empty_like(z)
-    w[L["intra_eid"]] = w_intra
-    w[L["slot_eid"][L["slot_first"]]] = w_slot[L["slot_first"]]
-    if threshold:
-        w = np.where(w < edge_tol, 0.0, w)
-    return w, SolveInfo(it, float(rp), float(rd), converged)
-
-
 def morton_keys(x: np.ndarray) -> np.ndarray:
     """Z-order codes of the columns of x (m, n): the (up to) three features of largest variance
     quantised to 10 bits each, bits interleaved with feature 0 lowest -- a bit-by-bit restatement of

@@ -2,12 +2,10 @@
 points uniform in the unit cube (BASELINE gives no m for config 5: m = 3 coordinates is the choice).
 Prints one JSON line.  Development / measurement aid.
 
-    python tools/knn_bench.py [n] [k] [iters] [sort_window] [locality] [layout]
-sort_window / locality (0 | 1) select the solver's internal row order (gl_knn_create_ordered): the
-default 0 0 is the global degree sort; e.g. `1000000 20 200 4096 1` = Morton arrangement of the points
-with the degree sort inside windows of 4,096 rows; layout = slots | blocked (intra-block edges
-stored once; meant for `256 1 blocked`).  GL_KNN_STREAM=1 in the environment selects the
-evict-first slot loads of knn_fused_kernel."""
+    python tools/knn_bench.py [n] [k] [iters] [sort_window] [locality]
+sort_window / locality (0 | 1) select the solver's internal row order (gl_knn_create_ordered):
+`0 0` is the global degree sort over the caller's numbering, `0 1` the Morton arrangement with a global
+stable degree sort (the estimator's default), `4096 1` the degree sort inside windows of 4,096 rows."""
 import json
 import os
 import sys
@@ -27,7 +25,6 @@ def main():
     iters = int(sys.argv[3]) if len(sys.argv) > 3 else 200
     window = int(sys.argv[4]) if len(sys.argv) > 4 else 0
     locality = bool(int(sys.argv[5])) if len(sys.argv) > 5 else False
-    layout = sys.argv[6] if len(sys.argv) > 6 else "slots"
     torch.cuda.set_device(0)
     x = torch.rand((3, n), generator=torch.Generator(device="cuda").manual_seed(0), device="cuda")
     torch.cuda.synchronize()
@@ -38,7 +35,7 @@ def main():
     theta = theta_from_knn(d2l, 10)
     z = d2 * theta
     nnz = z.numel()
-    order = dict(order_key=locality_keys(x) if locality else None, sort_window=window, layout=layout)
+    order = dict(order_key=locality_keys(x) if locality else None, sort_window=window)
     gsp_learn_graph_log_degrees_knn(ei, ej, z, n, maxit=20, tol=0.0, **order)  # warm-up
 
     def run(maxit):
@@ -55,7 +52,7 @@ def main():
     (w, info), t_solve = run(iters + 100)
     _, t_setup = run(100)          # same set-up (sort, slot fill, graph capture) + 100 iterations
     per_it = (t_solve - t_setup) / iters
-    print(json.dumps({"n": n, "k": k, "edges": nnz, "sort_window": window, "locality_keys": locality, "layout": layout, "knn_build_s": t_build, "theta": theta, "iters": info.n_iter,
+    print(json.dumps({"n": n, "k": k, "edges": nnz, "sort_window": window, "locality_keys": locality, "knn_build_s": t_build, "theta": theta, "iters": info.n_iter,
                       "solve_s": t_solve, "setup_s": t_setup, "ms_per_iteration": per_it * 1e3,
                       "edge_iters_per_s": nnz / per_it, "algorithmic_GBps_20B_per_edge": 20 * nnz / per_it / 1e9,
                       "moved_GBps_40B_per_edge": 40 * nnz / per_it / 1e9, "kept_edges": int((w > 0).sum()),
