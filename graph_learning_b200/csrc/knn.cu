@@ -18,6 +18,8 @@
 // This file holds the one-shot entry point; the stepwise / sharded solver is knn_sharded.cu.
 #include "knn_kernels.cuh"
 
+extern "C" const int *gl_knn_flags_ptr(gl_knn_solver *k);   // knn_sharded.cu (library-internal)
+
 namespace gl {
 
 // One-shot solve = the stepwise solver on a single shard [0, npad) in its one-launch form (slot sweep,
@@ -51,7 +53,10 @@ static int knn_solve(const int32_t *ei, const int32_t *ej, const void *z, int64_
   };
   int rc = gl_knn_begin(k, alpha, beta, step_size, maxit, tol, dmax, st);
   if (rc != GL_OK) return done(rc);
-  const int chunk = maxit < 16 ? (maxit > 0 ? maxit : 1) : 16;
+  // iterations per graph replay; even, because the two (a, b) buffers swap roles every launch and the
+  // captured pointers must line up again at the start of every replay (launches past maxit are no-ops)
+  int chunk = maxit < 32 ? (maxit > 0 ? maxit : 1) : 32;
+  chunk += chunk & 1;
   cudaError_t ce = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
   cudaEvent_t ev = nullptr;
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
@@ -71,21 +76,35 @@ static int knn_solve(const int32_t *ei, const int32_t *ej, const void *z, int64_
   g_launches.store(before);
   if (ce == cudaSuccess && rc == GL_OK) ce = cudaGraphInstantiate(&gexec, graph, 0);
   if (graph) cudaGraphDestroy(graph);
-  if (ce == cudaSuccess && rc == GL_OK) ce = cudaMallocHost((void **)&h_flags, sizeof(int) * FLAG_COUNT);
+  if (ce == cudaSuccess && rc == GL_OK) ce = cudaMallocHost((void **)&h_flags, sizeof(int) * 2 * FLAG_COUNT);
+  cudaEvent_t evs[2] = {nullptr, nullptr};
+  for (auto &e2 : evs)
+    if (ce == cudaSuccess && rc == GL_OK) ce = cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
   if (ce == cudaSuccess && rc == GL_OK) {
-    gl_solver *s = nullptr;
-    for (int it = 0; it < maxit; it += chunk) {
-      ce = cudaGraphLaunch(gexec, cs);
-      g_launches.fetch_add(per_chunk);
-      int cur = 0, conv = 0;
-      double rp = 0, rd = 0;
-      (void)s;
-      if (ce == cudaSuccess) ce = cudaStreamSynchronize(cs);
-      if (ce != cudaSuccess) break;
-      if (gl_knn_status(k, &cur, &rp, &rd, &conv, cs) != GL_OK) break;
-      if (conv || cur >= maxit) break;
+    // pipelined replay (as gl_solver_run): replay g + 1 is enqueued before the flags of replay g are read,
+    // so the device never idles while the host polls; iterations past the stop are device-side no-ops
+    const int max_graphs = (maxit + chunk - 1) / chunk;
+    const int *dflags = gl_knn_flags_ptr(k);
+    int launched = 0, checked = 0;
+    bool fin = maxit <= 0;
+    while (!fin && ce == cudaSuccess) {
+      while (launched < max_graphs && launched - checked < 2 && ce == cudaSuccess) {
+        ce = cudaGraphLaunch(gexec, cs);
+        g_launches.fetch_add(per_chunk);
+        if (ce == cudaSuccess)
+          ce = cudaMemcpyAsync(h_flags + (launched & 1) * FLAG_COUNT, dflags, sizeof(int) * FLAG_COUNT,
+                               cudaMemcpyDeviceToHost, cs);
+        if (ce == cudaSuccess) ce = cudaEventRecord(evs[launched & 1], cs);
+        ++launched;
+      }
+      if (checked >= launched || ce != cudaSuccess) break;
+      ce = cudaEventSynchronize(evs[checked & 1]);
+      fin = h_flags[(checked & 1) * FLAG_COUNT + FLAG_DONE] != 0;
+      ++checked;
     }
   }
+  for (auto e2 : evs)
+    if (e2) cudaEventDestroy(e2);
   if (ce == cudaSuccess && cs) ce = cudaStreamSynchronize(cs);
   if (ev) cudaEventDestroy(ev);
   if (rc != GL_OK) return done(rc);

@@ -245,15 +245,86 @@ template <typename F> struct KnnFusedArgs {
   int *flags;
   F c, tgz;
   double gamma, four_ag, tol;
+  // ---- PEER mode (row-sharded over several GPUs, one process each; see knn_fused_kernel) --------------
+  int world, rank, row_begin;
+  typename Vec2<F>::type *ab_out_peer[GL_MAX_PEERS];   // every rank's OUT buffer of this iteration (peer-mapped)
+  double *scal_peer[GL_MAX_PEERS];                     // every rank's scalar block [2][GL_MAX_PEERS][4]
+  int *hdr_peer[GL_MAX_PEERS];                         // every rank's header: sig[r] = last sequence rank r published
+  int *hdr;                                            // own header (sig[], HDR_SEQ)
+  const double *scal;                                  // own scalar block (peers write their partials here)
+  double *ring;                                        // [2][2] denominators of the previous two iterates
 };
 
 // (Evict-first __ldcs/__stcs slot accesses were measured on B200 in round 2 and lost: 0.154 against
 // 0.085 ms per iteration at n = 1e6 under the Morton order, profiles/r2_knn_row_order_stream.jsonl.)
-template <typename F>
+//
+// PEER = true: the same launch on a row shard [row_begin, row_begin + 32 nslices) of a multi-GPU solve, with
+// the exchange done by the kernel itself over NVLink peer memory instead of two NCCL collectives:
+//   * the new (gamma d, gamma pb) pair of a row is stored into EVERY rank's out buffer (8-byte remote
+//     stores, unit stride across a warp), so after the sweep every rank holds the full array;
+//   * the last CTA writes this rank's four residual partials into every rank's scalar block and then
+//     publishes a sequence flag to every rank (st after a system fence);
+//   * the next launch starts by waiting for all ranks' flags, then EVERY rank evaluates the stop rule for
+//     the iteration just completed from the partials summed in rank order (identical inputs, identical
+//     decision, no collective).  The decision therefore lags one launch, but a launch that decides "stop"
+//     returns before touching w, so the weights and the iteration count are exactly the reference's.
+// Buffer reuse is safe without further flags: a rank writes into a peer's out buffer only after that peer
+// has published the end of the previous iteration, which was the last reader of that buffer.
+template <typename F, bool PEER = false>
 __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused_kernel(const KnnFusedArgs<F> A) {
   if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][4];
   __shared__ int s_last;
+  int seq = 0, L = 0;
+  if constexpr (PEER) {
+    __shared__ int s_stop;
+    seq = ld_volatile_int(A.hdr + HDR_SEQ);
+    if ((int)threadIdx.x < A.world) {
+      const long long t0 = clock64();
+      while (ld_acquire_sys(A.hdr + threadIdx.x) < seq) {
+        if (clock64() - t0 > 6000000000LL) {
+          A.flags[FLAG_ERROR] = 1;
+          break;
+        }
+      }
+    }
+    __syncthreads();
+    L = ld_volatile_int(A.flags + FLAG_IT);   // iterations completed so far (written by the previous launch)
+    if (threadIdx.x == 0) {
+      int stop = ld_volatile_int(A.flags + FLAG_ERROR) ? 1 : 0;
+      if (L >= 1) {   // stop rule for iteration L - 1 (smooth_learning.py:156-166)
+        const double *sc = A.scal + ((L - 1) & 1) * GL_MAX_PEERS * 4;
+        double t[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int r = 0; r < A.world; ++r)
+          for (int q = 0; q < 4; ++q) t[q] += __ldcg(sc + 4 * r + q);
+        const double g_r = 0.5 * t[0], g_w = 0.5 * t[1];   // every undirected edge appears in two slots
+        bool conv = false;
+        double rp = 0.0, rd = 0.0;
+        if (L - 1 >= 1) {   // the first iteration never stops: :156-161
+          rp = sqrt(g_r) / sqrt(__ldcg(A.ring + 2 * (L & 1)));
+          rd = sqrt(t[2]) / sqrt(__ldcg(A.ring + 2 * (L & 1) + 1));
+          conv = (rp < A.tol) && (rd < A.tol);   // NaN / inf compare false, like NumPy
+        }
+        if (conv || L >= A.maxit) stop = 1;
+        if (blockIdx.x == 0) {
+          A.ring[2 * ((L + 1) & 1)] = g_w;       // denominators of the next check (:157-159)
+          A.ring[2 * ((L + 1) & 1) + 1] = t[3];
+          if (L - 1 >= 1) {
+            A.resid[0] = rp;
+            A.resid[1] = rd;
+          }
+          if (conv) A.flags[FLAG_CONVERGED] = 1;
+        }
+      }
+      if (stop && blockIdx.x == 0) {
+        __threadfence();
+        A.flags[FLAG_DONE] = 1;
+      }
+      s_stop = stop;
+    }
+    __syncthreads();
+    if (s_stop) return;
+  }
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   const int32_t *__restrict__ dst = A.dst;
   const F *__restrict__ z = A.z;
@@ -264,12 +335,14 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
   const int warps = gridDim.x * (KNN_THREADS / 32);
   for (int s = blockIdx.x * (KNN_THREADS / 32) + wp; s < A.nslices; s += warps) {
     const long long base = A.slice_off[s] + lane, end = A.slice_off[s + 1];
-    const int me = s * 32 + lane;
+    const int me = (PEER ? A.row_begin : 0) + s * 32 + lane;
     const typename Vec2<F>::type abi = ab[me];
     const bool live = me < A.n;
     // node state of this row: issued now, consumed after the slice
     const double dv = live ? A.d[me] : 0.0, ybv = live ? A.yb[me] : 0.0, pbv = live ? A.pb[me] : 0.0;
-    double acc_p = 0.0, acc_w = 0.0;
+    // per-row partial sums in the edge dtype (a row holds a few dozen slots), folded into float64 when
+    // the row ends -- the dense tile routine does the same over 64 edges (edge_tile.cuh)
+    F acc_p = F(0), acc_w = F(0), row_r = F(0), row_w = F(0);
     int j[KNN_UNROLL], jn[KNN_UNROLL];
     F wo[KNN_UNROLL], zz[KNN_UNROLL], won[KNN_UNROLL], zzn[KNN_UNROLL];
     auto fetch = [&](long long p0, int *jj, F *ww, F *zv) {
@@ -298,10 +371,10 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
           const F r = q - y;
           const F wn = (wo[u] - y) + q;
           w[p0 + 32LL * u] = wn;
-          acc_p += (double)pv;
-          acc_w += (double)wn;
-          res += (double)r * (double)r;
-          wsq += (double)wn * (double)wn;
+          acc_p += pv;
+          acc_w += wn;
+          row_r += r * r;
+          row_w += wn * wn;
         }
 #pragma unroll
       for (int u = 0; u < KNN_UNROLL; ++u) {
@@ -310,14 +383,16 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
         zz[u] = zzn[u];
       }
     }
+    res += (double)row_r;
+    wsq += (double)row_w;
     // ---- node update of row `me` (the arithmetic of knn_node_kernel) -----------------------------------
     typename Vec2<F>::type pr;
     pr.x = pr.y = F(0);
     if (live) {
-      const double qb = pbv + A.gamma * acc_p;                    //                      :154
+      const double qb = pbv + A.gamma * (double)acc_p;            //                      :154
       const double rbv = qb - ybv;
       const double dn = (dv - ybv) + qb;                          //                      :164
-      const double ybn = dn + A.gamma * acc_w;                    //                      :148
+      const double ybn = dn + A.gamma * (double)acc_w;            //                      :148
       const double pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;   //                  :151
       rb2 += rbv * rbv;
       d2 += dn * dn;
@@ -328,6 +403,11 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
       pr.y = (F)(A.gamma * pbn);
     }
     A.ab_out[me] = pr;
+    if constexpr (PEER) {
+#pragma unroll
+      for (int r = 0; r < GL_MAX_PEERS; ++r)
+        if (r < A.world && r != A.rank) A.ab_out_peer[r][me] = pr;
+    }
   }
   res = warp_sum(res);
   wsq = warp_sum(wsq);
@@ -345,7 +425,8 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
     for (int q = 0; q < KNN_THREADS / 32; ++q)
       for (int i = 0; i < 4; ++i) t[i] += s_red[q][i];
     for (int i = 0; i < 4; ++i) A.part[4 * blockIdx.x + i] = t[i];
-    __threadfence();
+    if constexpr (PEER) __threadfence_system();   // this CTA's remote pair stores before its ticket
+    else __threadfence();
     const int ticket = atomicAdd(A.flags + FLAG_EDGE_TICKET, 1);
     s_last = (ticket == (int)gridDim.x - 1);
   }
@@ -365,6 +446,17 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
   for (int q = 0; q < 4; ++q) t[q] = 0.0;
   for (int v = 0; v < KNN_THREADS / 32; ++v)
     for (int q = 0; q < 4; ++q) t[q] += s_red[v][q];
+  if constexpr (PEER) {
+    // this rank's partials into every rank's scalar block, then the sequence flag (release at system scope)
+    for (int r = 0; r < A.world; ++r)
+      for (int q = 0; q < 4; ++q) A.scal_peer[r][((L & 1) * GL_MAX_PEERS + A.rank) * 4 + q] = t[q];
+    A.flags[FLAG_EDGE_TICKET] = 0;
+    A.flags[FLAG_IT] = L + 1;
+    A.hdr[HDR_SEQ] = seq + 1;
+    __threadfence_system();
+    for (int r = 0; r < A.world; ++r) st_relaxed_sys(A.hdr_peer[r] + A.rank, seq + 1);
+    return;
+  }
   const double g_r = 0.5 * t[0], g_w = 0.5 * t[1];   // every undirected edge appears in two slots
   A.flags[FLAG_EDGE_TICKET] = 0;
   const int it = A.flags[FLAG_IT];

@@ -9,6 +9,7 @@
 // Per iteration:  edge_step -> node_step -> [all-gather ab | all-reduce 4 scalars] -> decide.
 // The node state (d, yb, pb) of foreign rows is never touched.
 #include <cstdlib>
+#include <cstring>
 
 #include <cub/device/device_scan.cuh>
 
@@ -28,7 +29,16 @@ struct gl_knn_solver {
   long long total = 0;              // entries incl. padding
   int fused = 0;                    // 1: single shard, the node kernel applies the stop rule itself
                                     // 2: single shard, whole iteration in one launch (knn_fused_kernel)
-  void *ab2 = nullptr;              // fused == 2: second (a, b) buffer, roles swap every iteration
+                                    // 3: row shard in PEER mode: one launch per iteration, exchange over peer memory
+  // comm block (one allocation, CUDA-IPC exportable): [header 512 B | scalar block 2 x 8 x 4 doubles |
+  // (a, b) buffer 0 | (a, b) buffer 1]; s->ab = buffer 0, ab2 = buffer 1
+  char *comm = nullptr;
+  size_t ab_bytes = 0;
+  int world = 1, rank = 0;
+  char *peer_comm[GL_MAX_PEERS] = {};
+  void *ipc_opened[GL_MAX_PEERS] = {};
+  double *ring = nullptr;           // fused == 3: [2][2] denominators of the previous two iterates
+  void *ab2 = nullptr;              // second (a, b) buffer, roles swap every iteration (fused >= 2)
   double *part = nullptr;           // fused == 2: [CTAs][4] residual partials
   int parity = 0;                   // fused == 2: which buffer the next iteration READS
   double *scal = nullptr;      // [4] partial sums for the exchange
@@ -225,6 +235,7 @@ template <typename F> static int knn_slot_launch(gl_knn_solver *k, bool init, cu
 }
 
 constexpr int KNN_FUSED_MAX_GRID = 148 * 8;
+constexpr size_t KNN_COMM_HDR = 512, KNN_COMM_SCAL = sizeof(double) * 2 * GL_MAX_PEERS * 4;
 
 template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t st) {
   gl_solver *s = k->s;
@@ -250,7 +261,22 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
   const int grid = std::max(1, std::min((k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32), KNN_FUSED_MAX_GRID));
-  knn_fused_kernel<F><<<grid, KNN_THREADS, 0, st>>>(A);
+  A.world = k->world;
+  A.rank = k->rank;
+  A.row_begin = k->row_begin;
+  A.hdr = reinterpret_cast<int *>(k->comm);
+  A.scal = reinterpret_cast<const double *>(k->comm + KNN_COMM_HDR);
+  A.ring = k->ring;
+  for (int r = 0; r < GL_MAX_PEERS; ++r) {
+    char *base = (r == k->rank || r >= k->world) ? k->comm : k->peer_comm[r];
+    A.hdr_peer[r] = reinterpret_cast<int *>(base);
+    A.scal_peer[r] = reinterpret_cast<double *>(base + KNN_COMM_HDR);
+    A.ab_out_peer[r] = reinterpret_cast<V *>(base + KNN_COMM_HDR + KNN_COMM_SCAL + (k->parity ? 0 : k->ab_bytes));
+  }
+  if (k->fused == 3)
+    knn_fused_kernel<F, true><<<grid, KNN_THREADS, 0, st>>>(A);
+  else
+    knn_fused_kernel<F, false><<<grid, KNN_THREADS, 0, st>>>(A);
   GL_LAUNCH_CHECK();
   k->parity ^= 1;
   return GL_OK;
@@ -264,7 +290,8 @@ template <typename F> static int knn_node_launch(gl_knn_solver *k, bool init, cu
   A.ab = s->ab;
   A.flags = s->flags;
   A.n = s->n; A.npad = s->npad; A.init = init ? 1 : 0; A.maxit = s->maxit;
-  A.row_begin = k->row_begin; A.row_end = k->row_end; A.fused = k->fused; A.scal = k->scal;
+  A.row_begin = k->row_begin; A.row_end = k->row_end; A.scal = k->scal;
+  A.fused = k->fused == 3 ? 0 : k->fused;   // peer mode: the init node step hands its partials to the exchange
   A.gamma = s->gamma;
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
@@ -330,8 +357,14 @@ extern "C" int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei, con
   k->ab_len = std::max<int64_t>(ab_len, k->s->npad);
   const size_t esz = dtype == GL_F32 ? 4 : 8;
   cudaStream_t st = as_stream(stream);
-  cudaError_t e = cudaMalloc(&k->s->ab, 2 * esz * (size_t)k->ab_len);
-  if (e == cudaSuccess) e = cudaMemsetAsync(k->s->ab, 0, 2 * esz * (size_t)k->ab_len, st);
+  k->ab_bytes = 2 * esz * (size_t)k->ab_len;
+  const size_t comm_bytes = KNN_COMM_HDR + KNN_COMM_SCAL + 2 * k->ab_bytes;
+  cudaError_t e = cudaMalloc((void **)&k->comm, comm_bytes);
+  if (e == cudaSuccess) e = cudaMemsetAsync(k->comm, 0, comm_bytes, st);
+  if (e == cudaSuccess) {
+    k->s->ab = k->comm + KNN_COMM_HDR + KNN_COMM_SCAL;
+    k->ab2 = k->comm + KNN_COMM_HDR + KNN_COMM_SCAL + k->ab_bytes;
+  }
   if (e == cudaSuccess) e = cudaMalloc((void **)&k->scal, 4 * sizeof(double));
   if (e == cudaSuccess) e = cudaMemsetAsync(k->scal, 0, 4 * sizeof(double), st);
   if (e != cudaSuccess) {
@@ -350,10 +383,15 @@ extern "C" int gl_knn_create_ordered(gl_knn_solver **out, const int32_t *ei, con
 
 extern "C" int gl_knn_destroy(gl_knn_solver *k) {
   if (!k) return GL_OK;
-  for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal, k->ab2,
-                  (void *)k->part})
+  for (void *q : k->ipc_opened)
+    if (q) cudaIpcCloseMemHandle(q);
+  for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal,
+                  (void *)k->part, (void *)k->ring, (void *)k->comm})
     if (q) cudaFree(q);
-  if (k->s) gl_solver_destroy(k->s);
+  if (k->s) {
+    k->s->ab = nullptr;   // lives inside the comm block freed above
+    gl_solver_destroy(k->s);
+  }
   delete k;
   return GL_OK;
 }
@@ -385,7 +423,7 @@ extern "C" int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double 
 
 extern "C" int gl_knn_edge_step(gl_knn_solver *k, void *stream) {
   if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
-  if (k->fused == 2)
+  if (k->fused >= 2)
     return k->dtype == GL_F32 ? knn_fused_launch<float>(k, as_stream(stream))
                               : knn_fused_launch<double>(k, as_stream(stream));
   return k->dtype == GL_F32 ? knn_slot_launch<float>(k, false, as_stream(stream))
@@ -394,7 +432,7 @@ extern "C" int gl_knn_edge_step(gl_knn_solver *k, void *stream) {
 
 extern "C" int gl_knn_node_step(gl_knn_solver *k, void *stream) {
   if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
-  if (k->fused == 2) return GL_OK;   // the node update ran inside the edge step
+  if (k->fused >= 2) return GL_OK;   // the node update ran inside the edge step
   return k->dtype == GL_F32 ? knn_node_launch<float>(k, false, as_stream(stream))
                             : knn_node_launch<double>(k, false, as_stream(stream));
 }
@@ -402,9 +440,12 @@ extern "C" int gl_knn_node_step(gl_knn_solver *k, void *stream) {
 extern "C" int gl_knn_decide(gl_knn_solver *k, int init, void *stream) {
   if (!k || !k->s->begun) return fail(GL_E_STATE, "gl_knn_begin first");
   gl_solver *s = k->s;
-  if (k->fused) return GL_OK;   // single shard: the node kernel has applied the stop rule
+  if (k->fused == 1 || k->fused == 2) return GL_OK;   // single shard: the node kernel has applied the stop rule
+  if (k->fused == 3 && !init) return GL_OK;           // peer mode: every launch decides for the previous iteration
   knn_decide_kernel<<<1, 1, 0, as_stream(stream)>>>(k->scal, s->gprev, s->resid, s->flags, init, s->maxit, s->tol);
   GL_LAUNCH_CHECK();
+  if (k->fused == 3)   // denominators of the first check: ring slot of "iteration -1"
+    GL_CUDA(cudaMemcpyAsync(k->ring + 2, s->gprev, 2 * sizeof(double), cudaMemcpyDeviceToDevice, as_stream(stream)));
   return GL_OK;
 }
 
@@ -415,6 +456,8 @@ extern "C" void *gl_knn_ab_ptr(gl_knn_solver *k, int64_t *n_entries) {
 }
 
 extern "C" void *gl_knn_scalars_ptr(gl_knn_solver *k) { return k ? k->scal : nullptr; }
+// device flag words of the shard (library-internal: the one-shot driver in knn.cu polls them)
+extern "C" const int *gl_knn_flags_ptr(gl_knn_solver *k) { return k ? k->s->flags : nullptr; }
 
 extern "C" int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, double *rel_dual, int *converged,
                              void *stream) {
@@ -441,17 +484,51 @@ extern "C" int gl_knn_store(gl_knn_solver *k, void *w_out, double edge_tol, void
 extern "C" int gl_knn_set_fused(gl_knn_solver *k, int fused) {
   if (!k) return fail(GL_E_ARG, "null solver");
   if (fused < 0 || fused > 2) return fail(GL_E_ARG, "fused must be 0, 1 or 2");
+  if (k->world > 1) return fail(GL_E_STATE, "a peer-connected shard runs only the one-launch peer iteration");
   if (fused == 2) {
     if (k->row_begin != 0 || k->row_end != k->s->npad)
       return fail(GL_E_STATE, "the one-launch iteration needs a single shard owning all rows");
     if (k->s->begun) return fail(GL_E_STATE, "choose the mode before gl_knn_begin");
-    const size_t esz = k->dtype == GL_F32 ? 4 : 8;
-    if (!k->ab2) {
-      GL_CUDA(cudaMalloc(&k->ab2, 2 * esz * (size_t)k->ab_len));
-      GL_CUDA(cudaMemset(k->ab2, 0, 2 * esz * (size_t)k->ab_len));
-    }
     if (!k->part) GL_CUDA(cudaMalloc((void **)&k->part, sizeof(double) * 4 * KNN_FUSED_MAX_GRID));
   }
   k->fused = fused;
+  return GL_OK;
+}
+
+// ---- peer (NVLink) exchange of the row-sharded solve ----------------------------------------------------
+extern "C" int gl_knn_comm_handle(gl_knn_solver *k, void *handle64) {
+  if (!k || !handle64) return fail(GL_E_ARG, "null argument");
+  cudaIpcMemHandle_t h;
+  GL_CUDA(cudaIpcGetMemHandle(&h, k->comm));
+  std::memcpy(handle64, &h, sizeof(h));
+  return GL_OK;
+}
+
+extern "C" int gl_knn_comm_connect(gl_knn_solver *k, int rank, int world, const void *handles) {
+  if (!k || !handles) return fail(GL_E_ARG, "null argument");
+  if (world < 1 || world > GL_MAX_PEERS || rank < 0 || rank >= world)
+    return fail(GL_E_ARG, "peer exchange supports 1..%d ranks (got rank %d of %d)", GL_MAX_PEERS, rank, world);
+  if (k->s->begun) return fail(GL_E_STATE, "connect before gl_knn_begin");
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) continue;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, static_cast<const char *>(handles) + 64 * r, sizeof(h));
+    if (k->ipc_opened[r]) {
+      cudaIpcCloseMemHandle(k->ipc_opened[r]);
+      k->ipc_opened[r] = nullptr;
+    }
+    void *p = nullptr;
+    GL_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    k->ipc_opened[r] = p;
+    k->peer_comm[r] = static_cast<char *>(p);
+  }
+  k->world = world;
+  k->rank = rank;
+  if (!k->part) GL_CUDA(cudaMalloc((void **)&k->part, sizeof(double) * 4 * KNN_FUSED_MAX_GRID));
+  if (!k->ring) {
+    GL_CUDA(cudaMalloc((void **)&k->ring, sizeof(double) * 4));
+    GL_CUDA(cudaMemset(k->ring, 0, sizeof(double) * 4));
+  }
+  k->fused = 3;
   return GL_OK;
 }

@@ -335,7 +335,7 @@ def knn_sharded_schedule(backend: KnnShardBackend, maxit: int, rank: int, world:
             break
 
 
-KNN_EXCHANGES = ("nccl",)
+KNN_EXCHANGES = ("peer", "nccl")
 
 
 class ShardedKNNSolver:
@@ -344,22 +344,49 @@ class ShardedKNNSolver:
     (slot sweep, node step, NCCL all-gather + all-reduce, decision) are captured in a CUDA graph."""
 
     def __init__(self, ei, ej, z, n_nodes: int, dtype=torch.float32, edge_init=None, group=None, rank=None,
-                 world=None, exchange: str = "nccl"):
+                 world=None, exchange: str = "auto", order_key=None):
         """``rank`` / ``world`` override the process group's (single-process emulation of several
-        shards in the tests; the caller then performs the exchange itself)."""
+        shards in the tests; the caller then performs the exchange itself).
+
+        ``exchange``: "peer" = the whole iteration is ONE launch per rank and the (gamma d, gamma pb)
+        slices, the residual partials and the sequence flags travel by stores into peer-mapped memory
+        over NVLink (``gl_knn_comm_*``; NCCL only carries the one initial all-gather of a solve);
+        "nccl" = slot sweep, node step, in-place ``ncclAllGather`` + ``ncclAllReduce`` and a decision
+        launch per iteration, all inside a captured graph; "auto" = peer for 2..8 ranks.
+
+        ``order_key`` (per-node non-negative integers, e.g. :func:`~graph_learning_b200.knn.locality_keys`):
+        the nodes are renumbered by ascending key before the rows are cut into contiguous shards, so that
+        a rank's far ends are mostly its own rows (setup-time torch glue; results stay per edge of the
+        caller's list)."""
         from .smooth_learning import _device, _gl_dtype, _to_device
         self.lib = nat.lib()
         self.group = group
-        if exchange not in KNN_EXCHANGES:
-            raise ValueError(f"exchange must be one of {KNN_EXCHANGES}")
-        self.exchange = exchange
+        if exchange not in KNN_EXCHANGES + ("auto",):
+            raise ValueError(f"exchange must be one of {KNN_EXCHANGES + ('auto',)}")
         self.emulated = world is not None
         self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.rank = rank if rank is not None else (dist.get_rank(group) if dist.is_initialized() else 0)
         self.n, self.dtype = int(n_nodes), dtype
+        if exchange == "auto":
+            exchange = "peer" if (not self.emulated and 2 <= self.world <= 8) else "nccl"
+        if exchange == "peer" and (self.emulated or self.world > 8):
+            raise ValueError("the peer exchange needs one process per GPU and at most 8 ranks")
+        self.exchange = exchange if self.world > 1 else ("nccl" if self.emulated else "single")
         dev = _device()
         ei = torch.as_tensor(ei, device=dev).to(torch.int32).contiguous()
         ej = torch.as_tensor(ej, device=dev).to(torch.int32).contiguous()
+        key32 = None
+        if order_key is not None and self.exchange == "single":
+            # one GPU: the library arranges its rows itself (Morton key, stable global degree sort)
+            key32 = torch.as_tensor(order_key, device=dev).to(torch.int32).contiguous()
+        elif order_key is not None:
+            key = torch.as_tensor(order_key, device=dev).to(torch.int64)
+            if key.numel() != self.n:
+                raise ValueError("order_key must hold one key per node")
+            lab = torch.empty(self.n, dtype=torch.int32, device=dev)
+            lab[torch.argsort(key, stable=True)] = torch.arange(self.n, dtype=torch.int32, device=dev)
+            a, b = lab[ei.long()], lab[ej.long()]
+            ei, ej = torch.minimum(a, b).contiguous(), torch.maximum(a, b).contiguous()
         z = _to_device(z, dtype)
         self.nnz_global = int(z.numel())
         dm = ctypes.c_int()
@@ -373,10 +400,13 @@ class ShardedKNNSolver:
         self._z = z[touch].contiguous()
         self._w0 = None if edge_init is None else _to_device(edge_init, dtype)[touch].contiguous()
         h = ctypes.c_void_p()
-        nat.check(self.lib.gl_knn_create(ctypes.byref(h), self._ei.data_ptr(), self._ej.data_ptr(), self._z.data_ptr(),
-                                         None if self._w0 is None else self._w0.data_ptr(), int(self._z.numel()), self.n,
-                                         _gl_dtype(dtype), self.row_begin, self.row_end, self.per * self.world, None))
+        nat.check(self.lib.gl_knn_create_ordered(
+            ctypes.byref(h), self._ei.data_ptr(), self._ej.data_ptr(), self._z.data_ptr(),
+            None if self._w0 is None else self._w0.data_ptr(), int(self._z.numel()), self.n, _gl_dtype(dtype),
+            self.row_begin, self.row_end, self.per * self.world, None if key32 is None else key32.data_ptr(), 0, 0, None))
         self._h = h
+        if self.exchange == "single":
+            nat.check(self.lib.gl_knn_set_fused(self._h, 2))   # whole iteration in one launch (knn_fused_kernel)
         from .smooth_learning import _wrap_device_memory
         cnt = ctypes.c_int64()
         ab_ptr = self.lib.gl_knn_ab_ptr(self._h, ctypes.byref(cnt))
@@ -384,13 +414,23 @@ class ShardedKNNSolver:
         self._scal = _wrap_device_memory(self.lib.gl_knn_scalars_ptr(self._h), 4, torch.float64, dev, owner=self)
         self._graph = None
         self.launches = 0
+        if self.exchange == "peer":
+            buf = ctypes.create_string_buffer(64)
+            nat.check(self.lib.gl_knn_comm_handle(self._h, buf))
+            handles = [None] * self.world
+            dist.all_gather_object(handles, buf.raw, group=group)
+            nat.check(self.lib.gl_knn_comm_connect(self._h, self.rank, self.world, b"".join(handles)))
+            dist.barrier(group=group)
 
     # -- backend protocol ---------------------------------------------------------------------------------
     def begin(self, alpha=1.0, beta=1.0, step_size=0.5, maxit=1000, tol=1e-5):
         self.maxit = int(maxit)
         nat.check(self.lib.gl_knn_begin(self._h, float(alpha), float(beta), float(step_size), int(maxit), float(tol),
                                         self.dmax, _cur_stream()))
-        self._graph = None
+        params = (float(alpha), float(beta), float(step_size), int(maxit), float(tol))
+        if getattr(self, "_graph_params", None) != params:
+            self._graph = None            # the parameters are baked into the captured launches
+            self._graph_params = params
         if self.emulated:
             return   # the caller exchanges and calls decide(True)
         knn_exchange(self, self.rank, self.world, self.group)
@@ -430,6 +470,8 @@ class ShardedKNNSolver:
         with torch.cuda.graph(g):
             for _ in range(iters):
                 self.edge_step()
+                if self.exchange in ("peer", "single"):
+                    continue          # the launch above was the whole iteration (exchange included)
                 self.node_step()
                 knn_exchange(self, self.rank, self.world, self.group)
                 self.decide(False)
@@ -438,15 +480,22 @@ class ShardedKNNSolver:
     def run(self, poll_every: int = 20) -> None:
         if self.maxit <= 0:
             return
+        peer = self.exchange == "peer"
+        one_launch = self.exchange in ("peer", "single")
         poll_every = max(1, min(poll_every, self.maxit))
+        if one_launch:
+            poll_every += poll_every & 1      # the two (a, b) buffers swap roles every launch: even count per graph
         if self._graph is None or self._graph_iters != poll_every:
             self._capture(poll_every)
         it = 0
-        while it < self.maxit:
+        # peer mode: a launch applies the stop rule to the iteration before it, so one more launch than
+        # iterations is enqueued (it only decides; launches after the stop are no-ops on the device)
+        total = self.maxit + 1 if peer else self.maxit
+        while it < total:
             self._graph.replay()
             it += poll_every
-            self.launches += 3 * poll_every
-            if self.done():
+            self.launches += (1 if one_launch else 3) * poll_every
+            if it >= total or self.status().converged:
                 break
 
     def gather(self, edge_tol: float = 1e-3) -> torch.Tensor:
@@ -464,6 +513,8 @@ class ShardedKNNSolver:
         self._graph = None
         if getattr(self, "_h", None):
             torch.cuda.synchronize()
+            if self.exchange == "peer":
+                dist.barrier(group=self.group)   # nobody unmaps memory a peer may still write
             self.lib.gl_knn_destroy(self._h)
             self._h = None
 

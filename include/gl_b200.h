@@ -290,6 +290,17 @@ int64_t gl_knn_padded_slots(gl_knn_solver *k);
  * 2: the whole iteration -- slot sweep, node update, stop rule -- runs inside gl_knn_edge_step as ONE
  * launch (gl_knn_node_step and gl_knn_decide become no-ops); choose before gl_knn_begin. */
 int gl_knn_set_fused(gl_knn_solver *k, int fused);
+/* Peer (NVLink) exchange for the row-sharded solve: each rank exports the 64-byte CUDA IPC handle of its
+ * comm block (header, scalar block, both (a, b) buffers), the caller all-gathers the handles and
+ * connects.  From then on gl_knn_edge_step is the WHOLE iteration in one launch: slot sweep, node update
+ * of the own rows with the new (a, b) pairs stored into every rank's buffer, residual partials and a
+ * sequence flag pushed to every rank; the next launch waits for all flags and applies the stop rule to
+ * the iteration just completed (identical on every rank; a launch that decides "stop" leaves w
+ * untouched, so iteration count and weights are those of the reference rule).  gl_knn_node_step and
+ * gl_knn_decide(k, 0) become no-ops; gl_knn_begin + the caller's one initial all-gather / all-reduce +
+ * gl_knn_decide(k, 1) stay as above.  Enqueue maxit + 1 launches (the last one only decides). */
+int gl_knn_comm_handle(gl_knn_solver *k, void *handle64_out);
+int gl_knn_comm_connect(gl_knn_solver *k, int rank, int world, const void *handles /* world x 64 B */);
 int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
                  int dmax, void *stream);
 int gl_knn_edge_step(gl_knn_solver *k, void *stream);
