@@ -95,6 +95,7 @@ SIGNATURES = {
     "gl_knn_ab_ptr": (c_void_p, [c_void_p, POINTER(c_int64)]),
     "gl_knn_scalars_ptr": (c_void_p, [c_void_p]),
     "gl_knn_status": (c_int, [c_void_p, _pi, _pd, _pd, _pi, c_void_p]),
+    "gl_knn_flags_ptr": (c_void_p, [c_void_p]),
     "gl_knn_store": (c_int, [c_void_p, c_void_p, c_double, c_void_p]),
     "gl_knn_build": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "gl_quadform_create": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_double, c_void_p]),

@@ -105,6 +105,14 @@ def _estimate_gauss_laplacian_parameters(
     return weights, means, lapl_host
 
 
+def _random_laplacians(n_nodes: int, n_components: int, random_state):
+    """Laplacians with uniform weights in [0, 1], one ``default_rng(random_state)`` per component as the
+    reference does (glmm.py:202-207 -> sampling/graphs.py:10-14)."""
+    e = n_nodes * (n_nodes - 1) // 2
+    return laplacian_squareform_vec(np.stack(
+        [np.random.default_rng(random_state).uniform(size=e) for _ in range(n_components)]))
+
+
 class GLMM(BaseMixture):
     """Graph Laplacian Mixture Model (Maretic & Frossard 2020); same constructor, attributes
     (``weights_``, ``means_``, ``laplacians_``, ``n_nodes_``) and ``fit`` / ``fit_predict`` /
@@ -174,9 +182,10 @@ class GLMM(BaseMixture):
             n = self.n_nodes_
             self.laplacians_ = np.tile(init * np.eye(n) - init / n * np.ones((n, n)), (self.n_components, 1, 1))
         elif init == "random":
-            rng = np.random.default_rng(self.random_state if isinstance(self.random_state, (int, np.integer)) else None)
-            e = self.n_nodes_ * (self.n_nodes_ - 1) // 2
-            self.laplacians_ = laplacian_squareform_vec(rng.uniform(size=(self.n_components, e)))
+            # the reference's sampler semantics (glmm.py:202-207 -> sampling/graphs.py:10-14): one
+            # default_rng(random_state) PER component -- an integer seed therefore gives every component the
+            # same Laplacian, a Generator is advanced from one component to the next
+            self.laplacians_ = _random_laplacians(self.n_nodes_, self.n_components, self.random_state)
         else:
             raise ValueError("Invalid Laplacian init")
         self.weights_, self.means_, self.laplacians_ = self._mstep(x, resp)

@@ -246,10 +246,17 @@ int gl_shard_rows(int n, int tile_begin, int tile_end, int *row_begin, int *row_
 int gl_solver_load_rows(gl_solver *s, const void *z_rows, const double *z_scale_host, const void *w_rows,
                         void *stream) {
   if (!s) return fail(GL_E_ARG, "null solver");
-  if (!z_rows) return fail(GL_E_ARG, "null distances");
   if (s->K != 1) return fail(GL_E_ARG, "gl_solver_load_rows serves a single graph");
-  int64_t e0 = 0;
-  GL_TRY(gl_shard_rows(s->n, s->tile_begin, s->tile_end, nullptr, nullptr, &e0, nullptr));
+  int64_t e0 = 0, e1 = 0;
+  GL_TRY(gl_shard_rows(s->n, s->tile_begin, s->tile_end, nullptr, nullptr, &e0, &e1));
+  if (e1 == e0) {   // a shard whose tiles hold no edge (e.g. the last node alone in its diagonal tile)
+    const size_t bytes = (size_t)s->gstride * s->esz;
+    GL_CUDA(cudaMemsetAsync(s->z, 0, bytes, as_stream(stream)));
+    GL_CUDA(cudaMemsetAsync(s->w, 0, bytes, as_stream(stream)));
+    s->begun = false;
+    return GL_OK;
+  }
+  if (!z_rows) return fail(GL_E_ARG, "null distances");
   // the kernels index the packed vector from its start; only elements of the shard's rows are touched
   const char *zb = static_cast<const char *>(z_rows) - (size_t)e0 * s->esz;
   const char *wb = w_rows ? static_cast<const char *>(w_rows) - (size_t)e0 * s->esz : nullptr;

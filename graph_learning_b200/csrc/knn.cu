@@ -18,8 +18,6 @@
 // This file holds the one-shot entry point; the stepwise / sharded solver is knn_sharded.cu.
 #include "knn_kernels.cuh"
 
-extern "C" const int *gl_knn_flags_ptr(gl_knn_solver *k);   // knn_sharded.cu (library-internal)
-
 namespace gl {
 
 // One-shot solve = the stepwise solver on a single shard [0, npad) in its one-launch form (slot sweep,

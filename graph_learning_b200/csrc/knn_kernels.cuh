@@ -270,8 +270,11 @@ template <typename F> struct KnnFusedArgs {
 //     returns before touching w, so the weights and the iteration count are exactly the reference's.
 // Buffer reuse is safe without further flags: a rank writes into a peer's out buffer only after that peer
 // has published the end of the previous iteration, which was the last reader of that buffer.
-template <typename F, bool PEER = false>
-__global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused_kernel(const KnnFusedArgs<F> A) {
+// U = columns of a slice in flight per batch (two batches are in flight), MINB = resident CTAs per SM the
+// register budget is sized for: (4, 4) = 64 registers, the default; the others are measurement variants
+// (GL_KNN_VARIANT).
+template <typename F, bool PEER = false, int U = KNN_UNROLL, int MINB = (sizeof(F) == 4 ? 4 : 2)>
+__global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnFusedArgs<F> A) {
   if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][4];
   __shared__ int s_last;
@@ -343,11 +346,11 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
     // per-row partial sums in the edge dtype (a row holds a few dozen slots), folded into float64 when
     // the row ends -- the dense tile routine does the same over 64 edges (edge_tile.cuh)
     F acc_p = F(0), acc_w = F(0), row_r = F(0), row_w = F(0);
-    int j[KNN_UNROLL], jn[KNN_UNROLL];
-    F wo[KNN_UNROLL], zz[KNN_UNROLL], won[KNN_UNROLL], zzn[KNN_UNROLL];
+    int j[U], jn[U];
+    F wo[U], zz[U], won[U], zzn[U];
     auto fetch = [&](long long p0, int *jj, F *ww, F *zv) {
 #pragma unroll
-      for (int u = 0; u < KNN_UNROLL; ++u) {
+      for (int u = 0; u < U; ++u) {
         const long long p = p0 + 32LL * u;
         const bool in = p < end;
         jj[u] = in ? dst[p] : -1;
@@ -356,13 +359,13 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
       }
     };
     fetch(base, j, wo, zz);
-    for (long long p0 = base; p0 < end; p0 += 32LL * KNN_UNROLL) {
-      typename Vec2<F>::type abj[KNN_UNROLL];
+    for (long long p0 = base; p0 < end; p0 += 32LL * U) {
+      typename Vec2<F>::type abj[U];
 #pragma unroll
-      for (int u = 0; u < KNN_UNROLL; ++u) abj[u] = ab[j[u] < 0 ? me : j[u]];   // far end: one gather
-      fetch(p0 + 32LL * KNN_UNROLL, jn, won, zzn);
+      for (int u = 0; u < U; ++u) abj[u] = ab[j[u] < 0 ? me : j[u]];   // far end: one gather
+      fetch(p0 + 32LL * U, jn, won, zzn);
 #pragma unroll
-      for (int u = 0; u < KNN_UNROLL; ++u)
+      for (int u = 0; u < U; ++u)
         if (j[u] >= 0) {
           const F y = c * wo[u] - (abi.x + abj[u].x);
           F pv = y - tgz * zz[u];
@@ -377,7 +380,7 @@ __global__ void __launch_bounds__(KNN_THREADS, sizeof(F) == 4 ? 4 : 2) knn_fused
           row_w += wn * wn;
         }
 #pragma unroll
-      for (int u = 0; u < KNN_UNROLL; ++u) {
+      for (int u = 0; u < U; ++u) {
         j[u] = jn[u];
         wo[u] = won[u];
         zz[u] = zzn[u];

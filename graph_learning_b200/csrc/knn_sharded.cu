@@ -273,6 +273,8 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
     A.scal_peer[r] = reinterpret_cast<double *>(base + KNN_COMM_HDR);
     A.ab_out_peer[r] = reinterpret_cast<V *>(base + KNN_COMM_HDR + KNN_COMM_SCAL + (k->parity ? 0 : k->ab_bytes));
   }
+  // (U, MINB) = (4, 4) is the measured best at n = 1e6, k = 20 on B200 (ms per iteration, tools/knn_probe.py,
+  // profiles/r2_knn_probe.jsonl): (4, 4) 0.085 | (6, 3) 0.087 | (8, 2) 0.095 | (8, 3, spills) 0.097 | (2, 6) 0.107
   if (k->fused == 3)
     knn_fused_kernel<F, true><<<grid, KNN_THREADS, 0, st>>>(A);
   else
@@ -456,7 +458,6 @@ extern "C" void *gl_knn_ab_ptr(gl_knn_solver *k, int64_t *n_entries) {
 }
 
 extern "C" void *gl_knn_scalars_ptr(gl_knn_solver *k) { return k ? k->scal : nullptr; }
-// device flag words of the shard (library-internal: the one-shot driver in knn.cu polls them)
 extern "C" const int *gl_knn_flags_ptr(gl_knn_solver *k) { return k ? k->s->flags : nullptr; }
 
 extern "C" int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, double *rel_dual, int *converged,

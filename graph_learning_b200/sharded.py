@@ -487,16 +487,34 @@ class ShardedKNNSolver:
             poll_every += poll_every & 1      # the two (a, b) buffers swap roles every launch: even count per graph
         if self._graph is None or self._graph_iters != poll_every:
             self._capture(poll_every)
-        it = 0
         # peer mode: a launch applies the stop rule to the iteration before it, so one more launch than
         # iterations is enqueued (it only decides; launches after the stop are no-ops on the device)
         total = self.maxit + 1 if peer else self.maxit
-        while it < total:
-            self._graph.replay()
-            it += poll_every
-            self.launches += (1 if one_launch else 3) * poll_every
-            if it >= total or self.status().converged:
+        n_graphs = -(-total // poll_every)
+        # pipelined polling: replay g + 1 is enqueued before the status words of replay g are looked at
+        # (asynchronous copy into pinned memory + an event), so the device never waits for the host
+        if getattr(self, "_flags_host", None) is None:
+            from .smooth_learning import _wrap_device_memory
+            self._flags_host = torch.zeros((2, 8), dtype=torch.int32).pin_memory()
+            self._flags_dev = _wrap_device_memory(self.lib.gl_knn_flags_ptr(self._h), 8, torch.int32, self._z.device,
+                                                  owner=self)
+            self._poll_ev = [torch.cuda.Event(), torch.cuda.Event()]
+        launched = checked = 0
+        while True:
+            while launched < n_graphs and launched - checked < 2:
+                self._graph.replay()
+                self._flags_host[launched & 1].copy_(self._flags_dev, non_blocking=True)
+                self._poll_ev[launched & 1].record()
+                launched += 1
+                self.launches += (1 if one_launch else 3) * poll_every
+            if checked >= launched:
                 break
+            self._poll_ev[checked & 1].synchronize()
+            done = bool(self._flags_host[checked & 1, 0].item())
+            checked += 1
+            if done:
+                break
+        torch.cuda.current_stream().synchronize()
 
     def gather(self, edge_tol: float = 1e-3) -> torch.Tensor:
         """Weights over the GLOBAL edge list on every rank (each edge is written by the owner of its

@@ -310,6 +310,10 @@ void *gl_knn_ab_ptr(gl_knn_solver *k, int64_t *n_entries);
 void *gl_knn_scalars_ptr(gl_knn_solver *k);
 int gl_knn_status(gl_knn_solver *k, int *n_iter, double *rel_primal, double *rel_dual, int *converged,
                   void *stream);
+/* Device pointer of the shard's 8 status words (int): [0] = solve finished (stop rule or maxit),
+ * [1] = iterations completed, [2] = stop rule fired, [5] = peer exchange timed out.  For drivers that
+ * poll without blocking the stream (asynchronous copy into pinned memory between graph replays). */
+const int *gl_knn_flags_ptr(gl_knn_solver *k);
 int gl_knn_store(gl_knn_solver *k, void *w_out_dev, double edge_tol, void *stream);
 
 /* k nearest neighbours between the COLUMNS of X (m, n) float32 (no reference code):

@@ -252,6 +252,18 @@ def assignment():
          log_prob=log_prob, dense=dense, smoothness_dense=smooth_dense)
 
 
+def glmm_random_init():
+    """GLMM(laplacian_init="random"): the reference draws every component with
+    sample_uniform_laplacian(n, self.random_state) (glmm.py:202-207, sampling/graphs.py:10-14)."""
+    from graph_learn.sampling.graphs import sample_uniform_laplacian
+    n, k = 7, 3
+    same = np.stack([sample_uniform_laplacian(n, 3) for _ in range(k)])          # integer seed: identical draws
+    gen = np.random.default_rng(11)
+    advancing = np.stack([sample_uniform_laplacian(n, gen) for _ in range(k)])   # a Generator advances
+    save("glmm_random_init_n7", n=np.int64(n), k=np.int64(k), int_seed=np.int64(3), laplacians_int_seed=same,
+         generator_seed=np.int64(11), laplacians_generator=advancing)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1:          # regenerate only the named sets
         for name in sys.argv[1:]:
@@ -265,3 +277,4 @@ if __name__ == "__main__":
     window_model()
     clustering()
     assignment()
+    glmm_random_init()

@@ -91,3 +91,14 @@ def test_window_logmodel_golden(golden, ws, k):
     assert rel(np.asarray(mdl.theta_), g[f"theta_ws{ws}_k{k}"]) < 1e-12
     assert mdl.weights_.shape == g[f"weights_ws{ws}_k{k}"].shape
     assert rel(mdl.weights_, g[f"weights_ws{ws}_k{k}"]) < 1e-9
+
+
+def test_glmm_random_laplacian_init_follows_the_reference_sampler(golden):
+    """laplacian_init="random": one default_rng(random_state) per component (glmm.py:202-207,
+    sampling/graphs.py:10-14) -- an integer seed repeats the draw, a Generator advances."""
+    from graph_learning_b200.clustering.glmm import _random_laplacians
+    g = golden("glmm_random_init_n7")
+    n, k = int(g["n"]), int(g["k"])
+    assert np.allclose(_random_laplacians(n, k, int(g["int_seed"])), g["laplacians_int_seed"], rtol=1e-13, atol=0)
+    gen = np.random.default_rng(int(g["generator_seed"]))
+    assert np.allclose(_random_laplacians(n, k, gen), g["laplacians_generator"], rtol=1e-13, atol=0)
