@@ -260,7 +260,13 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
   A.gamma = s->gamma;
   A.four_ag = 4.0 * s->alpha * s->gamma;
   A.tol = s->tol;
-  const int grid = std::max(1, std::min((k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32), KNN_FUSED_MAX_GRID));
+  static const int per_sm = [] {
+    const char *e = getenv("GL_KNN_CTAS_PER_SM");   // measurement aid; default = the resident count (one wave)
+    return e ? atoi(e) : 0;
+  }();
+  const int resident = 148 * (per_sm > 0 ? per_sm : (sizeof(F) == 4 ? 4 : 2));
+  const int want = (k->nslices + KNN_THREADS / 32 - 1) / (KNN_THREADS / 32);
+  const int grid = std::max(1, std::min(want, std::min(KNN_FUSED_MAX_GRID, resident)));
   A.world = k->world;
   A.rank = k->rank;
   A.row_begin = k->row_begin;

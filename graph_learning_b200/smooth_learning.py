@@ -548,12 +548,16 @@ def gsp_learn_graph_log_degrees(
                              f"{(n_edges,) if n_dim == 1 else (n_edges, n_graphs)}")
 
     solver = Solver(n, n_graphs, dt)
+    nvtx = torch.cuda.nvtx.range
     try:
-        solver.load(zk.contiguous(), z_scale, w0)
-        solver.begin(alpha, beta, step_size, maxit, tol)
-        solver.run()
-        info = solver.status()
-        result = solver.square(edge_tol) if n_dim == 1 else solver.store(edge_tol)
+        with nvtx("gl.load"):
+            solver.load(zk.contiguous(), z_scale, w0)
+        with nvtx("gl.solve"):
+            solver.begin(alpha, beta, step_size, maxit, tol)
+            solver.run()
+            info = solver.status()
+        with nvtx("gl.store"):
+            result = solver.square(edge_tol) if n_dim == 1 else solver.store(edge_tol)
     finally:
         solver.close()
     res = result
@@ -658,15 +662,18 @@ class LogModel(BaseEstimator):
             sharded = sharded_workspace(n, dt, group)
             solver = sharded.solver
             tile_range = sharded.tile_range if sharded.world > 1 else None
+        nvtx = torch.cuda.nvtx.range      # phase ranges for nsys / ncu --nvtx
         try:
             method = _resolve_method("auto", dt, m)
-            _pdist_into(xd, None, None, solver.z_view(0), nat.LAYOUT_TILED, solver.tile_begin, solver.tile_end, method)
+            with nvtx("gl.pdist_sq_tiles"):
+                _pdist_into(xd, None, None, solver.z_view(0), nat.LAYOUT_TILED, solver.tile_begin, solver.tile_end, method)
             if self.avg_degree is None:
                 self.theta_ = 1
             else:
-                self.theta_ = _theta_tiles(solver.z_view(0), n, self.avg_degree, tile_range,
-                                           None if group is False else group)
-                solver.scale_z(self.theta_)
+                with nvtx("gl.theta"):
+                    self.theta_ = _theta_tiles(solver.z_view(0), n, self.avg_degree, tile_range,
+                                               None if group is False else group)
+                    solver.scale_z(self.theta_)
             w0 = None
             if self.edge_init is not None:
                 w0 = _to_device(self.edge_init, dt).reshape(1, -1).contiguous()
@@ -674,15 +681,19 @@ class LogModel(BaseEstimator):
                     raise ValueError(f"edge_init has shape {tuple(np.shape(self.edge_init))}, expected {(n * (n - 1) // 2,)}")
             solver.load_w_packed(w0)
             if sharded is None:
-                solver.begin(1, 1, self.step_size, self.maxit, self.tol)
-                solver.run()
-                info = solver.status()
-                result = solver.square(self.edge_tol)
+                with nvtx("gl.solve"):
+                    solver.begin(1, 1, self.step_size, self.maxit, self.tol)
+                    solver.run()
+                    info = solver.status()
+                with nvtx("gl.tiles_to_square"):
+                    result = solver.square(self.edge_tol)
             else:
-                sharded.begin(1, 1, self.step_size, self.maxit, self.tol)
-                sharded.run()
-                info = sharded.status()
-                result = sharded.gather_square(self.edge_tol, self.weights_on)
+                with nvtx("gl.solve_sharded"):
+                    sharded.begin(1, 1, self.step_size, self.maxit, self.tol)
+                    sharded.run()
+                    info = sharded.status()
+                with nvtx("gl.gather_square"):
+                    result = sharded.gather_square(self.edge_tol, self.weights_on)
         finally:
             if sharded is None:
                 solver.close()

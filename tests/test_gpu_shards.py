@@ -152,7 +152,7 @@ def test_logmodel_fit_resident_route(sl, dtype):
     # out= (extra): preallocated host result
     out = np.empty((150, 150), dtype=np.float64 if dtype == "float64" else np.float32)
     mdl3 = sl.LogModel(avg_degree=5, maxit=300, dtype=dtype).fit(x, out=out)
-    assert mdl3.weights_ is out and np.array_equal(out, mdl.weights_)
+    assert mdl3.weights_ is out and rel(out, mdl.weights_) < 1e-6   # two runs: atomic summation order differs
     with pytest.raises(ValueError, match="edge_init"):
         sl.LogModel(avg_degree=5, edge_init=np.zeros(7)).fit(x)
 
