@@ -96,8 +96,14 @@ def _estimate_gauss_laplacian_parameters(
     else:
         theta_inv = _to_device(np.asarray(1.0 / np.asarray(theta, dtype=np.float64)), sq_dist.dtype)
 
-    edge_weights = gsp_learn_graph_log_degrees(sq_dist * theta_inv, alpha=1, beta=1, edge_init=edge_init,
-                                               dtype=dtype)                          # :79
+    if theta_inv.numel() in (1, n_components):
+        # scalar / per-component theta rides along as z_scale (multiplied into Z while it is tiled)
+        sc = theta_inv.double().reshape(-1).cpu().numpy()
+        edge_weights = gsp_learn_graph_log_degrees(sq_dist, alpha=1, beta=1, edge_init=edge_init, dtype=dtype,
+                                                   z_scale=np.broadcast_to(sc, (n_components,)))      # :79
+    else:   # per-edge thetas of the block form (smooth_learning.py:220-235): an elementwise product
+        edge_weights = gsp_learn_graph_log_degrees(sq_dist * theta_inv, alpha=1, beta=1, edge_init=edge_init,
+                                                   dtype=dtype)                      # :79
     lapl = laplacian_squareform_vec(delta * edge_weights)                           # :83
     lapl_host = lapl.cpu().numpy().astype(np.float64)
     if return_device:

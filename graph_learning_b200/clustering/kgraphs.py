@@ -67,10 +67,10 @@ class KGraphs(BaseEstimator, ClusterMixin):
         """Laplacians (K, n, n) of all clusters from the current labels, on the device (:96-108)."""
         n_nodes = x_dev.shape[1]
         sq_dist = torch.stack([pdist_sq(x_dev[labels == k], dtype=x_dev.dtype) for k in range(self.n_clusters)])
-        theta = torch.tensor([[_theta_packed(sq_dist[k], n_nodes, self.avg_degree)] for k in range(self.n_clusters)],
-                             dtype=sq_dist.dtype, device=sq_dist.device)
-        edge_weights = self.delta * gsp_learn_graph_log_degrees(sq_dist * theta, alpha=1, beta=1, dtype=self.dtype)
-        return laplacian_squareform_vec(edge_weights)
+        # theta per cluster (:98-101) rides along as z_scale: multiplied into Z while it is tiled, no extra pass
+        theta = [_theta_packed(sq_dist[k], n_nodes, self.avg_degree) for k in range(self.n_clusters)]
+        edge_weights = gsp_learn_graph_log_degrees(sq_dist, alpha=1, beta=1, dtype=self.dtype, z_scale=theta)
+        return laplacian_squareform_vec(self.delta * edge_weights)
 
     def _graph_step(self, x_dev: torch.Tensor) -> np.ndarray:
         labels = torch.as_tensor(self.labels_, device=x_dev.device)
