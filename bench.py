@@ -690,6 +690,8 @@ def parity_leg(a, env, lib, nat, solver, sharded, solve, gathered_packed, z_full
         rel = None
         if env.rank == 0:
             from oracle import c_oracle
+            if env.world > 1:   # torchrun pins OMP_NUM_THREADS=1; the other ranks only wait here
+                out["oracle_threads"] = c_oracle.set_threads(max(1, (os.cpu_count() or 2) - 2 * env.world))
             t0 = time.perf_counter()
             wo, it_o, _, _ = c_oracle.solve(z64, maxit=its, tol=0.0, threshold=False)
             out["oracle_s"] += time.perf_counter() - t0

@@ -383,8 +383,17 @@ class ShardedKNNSolver:
             key = torch.as_tensor(order_key, device=dev).to(torch.int64)
             if key.numel() != self.n:
                 raise ValueError("order_key must hold one key per node")
+            # arrangement: ascending key (spatially compact shards), then inside every rank's row range a stable
+            # sort by decreasing degree (rows of one slice get similar lengths: no padding; rows of equal degree
+            # keep the key order) -- what the library does itself for a single full-range shard
+            arrangement = torch.argsort(key, stable=True)
+            deg = torch.bincount(ei.long(), minlength=self.n) + torch.bincount(ej.long(), minlength=self.n)
+            per = shard_rows(self.n, 0, self.world)[2]
+            pos = torch.arange(self.n, device=dev, dtype=torch.int64)
+            composite = (pos // per) * (int(deg.max()) + 1) + (int(deg.max()) - deg[arrangement])
+            arrangement = arrangement[torch.argsort(composite, stable=True)]
             lab = torch.empty(self.n, dtype=torch.int32, device=dev)
-            lab[torch.argsort(key, stable=True)] = torch.arange(self.n, dtype=torch.int32, device=dev)
+            lab[arrangement] = torch.arange(self.n, dtype=torch.int32, device=dev)
             a, b = lab[ei.long()], lab[ej.long()]
             ei, ej = torch.minimum(a, b).contiguous(), torch.maximum(a, b).contiguous()
         z = _to_device(z, dtype)

@@ -41,6 +41,17 @@ def threads():
     return lib().orc_threads()
 
 
+def set_threads(n: int) -> int:
+    """Override the OpenMP thread count (torchrun exports OMP_NUM_THREADS=1 to every rank; the parity leg
+    of bench.py runs the oracle on rank 0 only and may use the idle host cores).  Returns the new count."""
+    lib()
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(max(1, n)))
+    except OSError:
+        pass
+    return threads()
+
+
 def pdist_sq(x):
     x = np.ascontiguousarray(x, dtype=np.float64)
     m, n = x.shape
