@@ -238,6 +238,7 @@ def run_config5(a):
     launches = sv.launches
     value = nnz * iters * a.steps / (ms_sum * 1e-3)
     local_slots = int(sv.lib.gl_knn_local_slots(sv._h))
+    pushed = env.max_over_ranks(float(getattr(sv, "pushed_fraction", 0.0)))
     w = sv.gather()
     kept = int((w > 0).sum())
     sv.close()
@@ -254,7 +255,8 @@ def run_config5(a):
                    "l2": f"slot arrays {32 * nnz / 1e6:.0f} MB in total ({32 * nnz / env.world / 1e6:.0f} MB per rank) against a 126 MB L2: "
                          + ("larger than L2 on one GPU, streamed from HBM" if 32 * nnz / env.world > 126e6 else
                             "L2-RESIDENT per rank: the 'hbm' figure is an L2 rate (labelled)"),
-                   "parallelism": f"row-shard x{env.world}, exchange={exchange}, Morton row order"},
+                   "parallelism": f"row-shard x{env.world}, exchange={exchange}, Morton row order",
+                   "rows_pushed_to_a_peer_max_over_ranks": pushed},
         "gpu_launches": int(launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "gl::knn_fused_kernel (whole iteration in one launch)", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,

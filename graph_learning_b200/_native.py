@@ -88,6 +88,8 @@ SIGNATURES = {
     "gl_knn_set_fused": (c_int, [c_void_p, c_int]),
     "gl_knn_comm_handle": (c_int, [c_void_p, c_void_p]),
     "gl_knn_comm_connect": (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    "gl_knn_mark_far_ends": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "gl_knn_comm_need": (c_int, [c_void_p, c_void_p, c_void_p]),
     "gl_knn_begin": (c_int, [c_void_p, c_double, c_double, c_double, c_int, c_double, c_int, c_void_p]),
     "gl_knn_edge_step": (c_int, [c_void_p, c_void_p]),
     "gl_knn_node_step": (c_int, [c_void_p, c_void_p]),

@@ -38,6 +38,7 @@ struct gl_knn_solver {
   char *peer_comm[GL_MAX_PEERS] = {};
   void *ipc_opened[GL_MAX_PEERS] = {};
   double *ring = nullptr;           // fused == 3: [2][2] denominators of the previous two iterates
+  int32_t *need = nullptr;          // fused == 3, optional: per node, bit r = rank r references it (gl_knn_comm_need)
   void *ab2 = nullptr;              // second (a, b) buffer, roles swap every iteration (fused >= 2)
   double *part = nullptr;           // fused == 2: [CTAs][4] residual partials
   int parity = 0;                   // fused == 2: which buffer the next iteration READS
@@ -273,6 +274,7 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
   A.hdr = reinterpret_cast<int *>(k->comm);
   A.scal = reinterpret_cast<const double *>(k->comm + KNN_COMM_HDR);
   A.ring = k->ring;
+  A.need = k->need;
   for (int r = 0; r < GL_MAX_PEERS; ++r) {
     char *base = (r == k->rank || r >= k->world) ? k->comm : k->peer_comm[r];
     A.hdr_peer[r] = reinterpret_cast<int *>(base);
@@ -394,7 +396,7 @@ extern "C" int gl_knn_destroy(gl_knn_solver *k) {
   for (void *q : k->ipc_opened)
     if (q) cudaIpcCloseMemHandle(q);
   for (void *q : {(void *)k->dst, (void *)k->eid_canon, k->zs, k->ws, (void *)k->slice_off, (void *)k->scal,
-                  (void *)k->part, (void *)k->ring, (void *)k->comm})
+                  (void *)k->part, (void *)k->ring, (void *)k->need, (void *)k->comm})
     if (q) cudaFree(q);
   if (k->s) {
     k->s->ab = nullptr;   // lives inside the comm block freed above
@@ -537,5 +539,39 @@ extern "C" int gl_knn_comm_connect(gl_knn_solver *k, int rank, int world, const 
     GL_CUDA(cudaMemset(k->ring, 0, sizeof(double) * 4));
   }
   k->fused = 3;
+  return GL_OK;
+}
+
+// Far ends of this shard's slots as a 0/1 mark per node (the caller sums rank r's marks shifted to bit r
+// over the ranks -- any all-reduce -- and hands the result back with gl_knn_comm_need).
+static __global__ void knn_mark_far_ends_kernel(const int32_t *dst, long long total, int32_t *mark) {
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long long)gridDim.x * blockDim.x) {
+    const int32_t j = dst[p];
+    if (j >= 0) mark[j] = 1;
+  }
+}
+
+extern "C" int gl_knn_mark_far_ends(gl_knn_solver *k, int32_t *mark_dev, void *stream) {
+  if (!k || !mark_dev) return fail(GL_E_ARG, "null argument");
+  cudaStream_t st = as_stream(stream);
+  GL_CUDA(cudaMemsetAsync(mark_dev, 0, sizeof(int32_t) * (size_t)k->s->n, st));
+  if (k->total > 0) {
+    const int grid = (int)std::min<long long>((k->total + KNN_THREADS - 1) / KNN_THREADS, 148 * 8);
+    knn_mark_far_ends_kernel<<<grid, KNN_THREADS, 0, st>>>(k->dst, k->total, mark_dev);
+    GL_LAUNCH_CHECK();
+  }
+  return GL_OK;
+}
+
+extern "C" int gl_knn_comm_need(gl_knn_solver *k, const int32_t *need_dev, void *stream) {
+  if (!k) return fail(GL_E_ARG, "null solver");
+  if (k->fused != 3) return fail(GL_E_STATE, "gl_knn_comm_connect first");
+  if (!need_dev) {   // back to pushing every pair to every rank
+    if (k->need) cudaFree(k->need);
+    k->need = nullptr;
+    return GL_OK;
+  }
+  if (!k->need) GL_CUDA(cudaMalloc((void **)&k->need, sizeof(int32_t) * (size_t)k->s->n));
+  GL_CUDA(cudaMemcpyAsync(k->need, need_dev, sizeof(int32_t) * (size_t)k->s->n, cudaMemcpyDeviceToDevice, as_stream(stream)));
   return GL_OK;
 }

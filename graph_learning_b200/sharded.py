@@ -429,6 +429,15 @@ class ShardedKNNSolver:
             handles = [None] * self.world
             dist.all_gather_object(handles, buf.raw, group=group)
             nat.check(self.lib.gl_knn_comm_connect(self._h, self.rank, self.world, b"".join(handles)))
+            # who reads which node: a pair is pushed only to the ranks whose slots reference it
+            need = torch.empty(self.n, dtype=torch.int32, device=dev)
+            nat.check(self.lib.gl_knn_mark_far_ends(self._h, need.data_ptr(), None))
+            need <<= self.rank
+            dist.all_reduce(need, group=group)
+            nat.check(self.lib.gl_knn_comm_need(self._h, need.data_ptr(), None))
+            torch.cuda.synchronize()
+            self.pushed_fraction = float(((need & ~(1 << self.rank))[self.row_begin:min(self.row_end, self.n)] != 0)
+                                         .double().mean()) if self.row_begin < self.n else 0.0
             dist.barrier(group=group)
 
     # -- backend protocol ---------------------------------------------------------------------------------

@@ -301,6 +301,13 @@ int gl_knn_set_fused(gl_knn_solver *k, int fused);
  * gl_knn_decide(k, 1) stay as above.  Enqueue maxit + 1 launches (the last one only decides). */
 int gl_knn_comm_handle(gl_knn_solver *k, void *handle64_out);
 int gl_knn_comm_connect(gl_knn_solver *k, int rank, int world, const void *handles /* world x 64 B */);
+/* Optional traffic cut for the peer exchange: gl_knn_mark_far_ends writes 1 at every node this shard's
+ * slots reference (mark_dev: n int32); the caller combines the ranks' marks into a bit set per node
+ * (bit r = rank r references it; e.g. an all-reduce SUM of mark << rank) and passes it to
+ * gl_knn_comm_need on every rank.  A node's new pair is then stored only into the ranks that read it --
+ * with spatially compact shards a thin boundary layer instead of every row.  NULL restores the full push. */
+int gl_knn_mark_far_ends(gl_knn_solver *k, int32_t *mark_dev, void *stream);
+int gl_knn_comm_need(gl_knn_solver *k, const int32_t *need_dev, void *stream);
 int gl_knn_begin(gl_knn_solver *k, double alpha, double beta, double step_size, int maxit, double tol,
                  int dmax, void *stream);
 int gl_knn_edge_step(gl_knn_solver *k, void *stream);
