@@ -57,7 +57,8 @@ void free_all(gl_solver *s) {
   for (void *p : s->ipc_opened)
     if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
-                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace, s->ab, s->gram_part};
+                  s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace, s->ab, s->gram_part,
+                  s->small_state};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -152,7 +153,9 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
   if (rc == GL_OK) rc = alloc_zero(&s->a, s->esz * nk);
   if (rc == GL_OK) rc = alloc_zero(&s->b, s->esz * nk);
   s->xch_stride = (s->xch_len + 31) / 32 * 32;
-  if (rc == GL_OK) rc = alloc_zero((void **)&s->comm, 8 * (size_t)(COMM_HDR + 2 * s->xch_stride));
+  if (rc == GL_OK) rc = alloc_zero((void **)&s->comm, 8 * (size_t)(COMM_HDR + 3 * s->xch_stride));   // 3rd buffer: small kernel
+  if (rc == GL_OK && K == 1 && tile_begin == 0 && tile_end == num_tiles(n) && s->ntl <= 1024)
+    rc = alloc_zero((void **)&s->small_state, 8 * 3 * (size_t)s->npad);
   if (rc == GL_OK) s->xch = s->comm + COMM_HDR;
   if (rc == GL_OK) rc = alloc_zero((void **)&s->cta_partial, 16 * (size_t)((s->ntl > 1024 ? s->ntl : 1024) + s->npad / 256 + 8));
   if (rc == GL_OK) rc = alloc_zero((void **)&s->node_partial, 16 * (nk / 256 + 2));
@@ -293,7 +296,7 @@ int gl_solver_begin(gl_solver *s, double alpha, double beta, double step_size, i
   }
   // peer mode: the buffer of the coming exchange was cleared by the previous node tail and the
   // other one may still be read by a peer -- never touch them from the host side
-  if (s->world <= 1) GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)s->xch_len, st));
+  if (s->world <= 1) GL_CUDA(cudaMemsetAsync(s->xch, 0, sizeof(double) * (size_t)(3 * s->xch_stride), st));
   GL_CUDA(cudaMemsetAsync(s->flags, 0, sizeof(int) * FLAG_COUNT, st));
   GL_TRY(launch_edge_init(s, st));   // local partial of S w0 and the squared norm of every graph's w0
   return GL_OK;
@@ -391,6 +394,8 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   cudaStream_t user = as_stream(stream);
   const char *env = std::getenv("GL_B200_PERSISTENT");
   const bool persistent = s->K == 1 && s->ntl > 0 && !(env && env[0] == '0');
+  const char *env_small = std::getenv("GL_B200_SMALL");
+  const bool small = persistent && !(env_small && env_small[0] == '0') && small_applicable(s);
   if (poll_every <= 0) poll_every = persistent ? 50 : (((int64_t)s->ntl * s->K >= 4096) ? 8 : 32);
   if (poll_every > s->maxit) poll_every = s->maxit > 0 ? s->maxit : 1;
 
@@ -460,7 +465,8 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   while (!done) {
     while (launched < max_graphs && launched - checked < 2) {
       if (persistent) {
-        rc = launch_persistent(s, poll_every, st);  // one resident kernel runs the whole chunk
+        // one resident kernel runs the whole chunk (small problems: the one-barrier redundant-node form)
+        rc = small ? launch_persistent_small(s, poll_every, st) : launch_persistent(s, poll_every, st);
         if (rc != GL_OK) {
           cleanup();
           return rc;

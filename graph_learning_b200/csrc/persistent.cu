@@ -260,6 +260,229 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
   }
 }
 
+// ---- small problems: every CTA owns at most ONE tile (n <= ~2,900) ---------------------------------------
+// The whole problem is L2-resident there (config 2: 16 MB) and an iteration is latency: two grid barriers,
+// the fold, the node chunk and the decision cost ~10 us against ~2 us of sweep.  With one tile per CTA the
+// node phase is cheap enough to be done REDUNDANTLY by every CTA: after the single grid barrier (all degree
+// partials complete) each CTA runs the node update of smooth_learning.py:148-164 over all n nodes itself,
+// in the same fixed order, so every CTA holds bit-identical residual sums and takes the same stop decision
+// -- no second barrier, no decision stage, no broadcast.  Only the owner of a 256-node chunk writes the
+// node state; every CTA writes the (gamma d, gamma pb) values of its own tile's row and column block
+// (identical values from every writer) and reads them back for the next sweep.
+// Hazards are removed by buffering instead of barriers: the exchange buffer is TRIPLE buffered by
+// iteration (sweep t + 1 adds into buffer (t + 1) % 3 while slower CTAs still read buffer t % 3, owners
+// clear buffer (t + 2) % 3), the node state and the per-CTA residual partials are double buffered.
+template <typename F> struct SmallArgs {
+  EdgeArgs<F> E;                 // E.xch = exchange buffer 0, stride E.xch_stride, THREE buffers
+  double *st[2][3];              // [parity][d, yb, pb]
+  F *a, *b;
+  double *cta_partial;           // [2][grid][2]
+  double *gprev, *resid;
+  unsigned int *bar;
+  double gamma, four_ag, tol;
+  int maxit, iters;
+};
+
+template <typename F>
+__global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persistent_small_kernel(const SmallArgs<F> P) {
+  __shared__ EdgeSmem<F> sm;
+  EdgeArgs<F> A = P.E;
+  const int tid = threadIdx.x;
+  int *flags = A.flags;
+  if (ld_volatile_int(flags + FLAG_DONE)) return;
+  int it = ld_volatile_int(flags + FLAG_IT);
+  double gw_prev = __ldcg(P.gprev), gd_prev = __ldcg(P.gprev + 1);
+  unsigned gen = 0;
+  const int total = A.npad, grid = gridDim.x;
+  const bool has_tile = (int)blockIdx.x < A.ntl;
+  const int2 ij = has_tile ? A.tile_ij[blockIdx.x] : make_int2(-1, -1);
+  A.a = P.a;
+  A.b = P.b;
+  if (it > 0) {   // continuing launch: the sweep's (a, b) follow from the node state of the last iteration
+    const double *d = P.st[it & 1][0], *pb = P.st[it & 1][2];
+    for (int j = tid; j < total; j += EDGE_THREADS)
+      if (j / T == ij.x || j / T == ij.y) {
+        P.a[j] = (F)(P.gamma * __ldcg(d + j));
+        P.b[j] = (F)(P.gamma * __ldcg(pb + j));
+      }
+    __syncthreads();
+  }
+  for (int step = 0; step < P.iters; ++step) {
+    const int par = it & 1;
+    double *const xb = A.xch + (int64_t)(it % 3) * A.xch_stride;
+    double *const xclr = A.xch + (int64_t)((it + 2) % 3) * A.xch_stride;
+    double *const part = P.cta_partial + (int64_t)par * 2 * grid;
+    // ---------------- E phase: this CTA's tile ------------------------------------------------------
+    double r2 = 0.0, w2 = 0.0;
+    if (has_tile) edge_cta_tile<F, false, true>(A, sm, blockIdx.x, 0, xb, xb + total, r2, w2);
+    if (tid == 0) {
+      part[2 * blockIdx.x] = r2;
+      part[2 * blockIdx.x + 1] = w2;
+    }
+    grid_barrier(P.bar, gen);
+    // ---------------- N phase, redundantly on every CTA ----------------------------------------------
+    const double *d0 = P.st[par][0], *yb0 = P.st[par][1], *pb0 = P.st[par][2];
+    double *d1 = P.st[par ^ 1][0], *yb1 = P.st[par ^ 1][1], *pb1 = P.st[par ^ 1][2];
+    double my_rb2 = 0.0, my_d2 = 0.0;
+    constexpr int NB = 8;   // nodes per thread in flight: all loads of a batch are issued before any store
+    for (int j0 = tid; j0 < total; j0 += EDGE_THREADS * NB) {
+      double sp[NB], sw[NB], dv[NB], ybv[NB], pbv[NB];
+#pragma unroll
+      for (int u = 0; u < NB; ++u) {
+        const int j = j0 + u * EDGE_THREADS;
+        const bool in = j < A.n;
+        sp[u] = in ? __ldcg(xb + j) : 0.0;
+        sw[u] = in ? __ldcg(xb + total + j) : 0.0;
+        dv[u] = in ? __ldcg(d0 + j) : 0.0;
+        ybv[u] = in ? __ldcg(yb0 + j) : 0.0;
+        pbv[u] = in ? __ldcg(pb0 + j) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < NB; ++u) {
+        const int j = j0 + u * EDGE_THREADS;
+        if (j >= total) break;
+        double dn = 0.0, rbv = 0.0, ybn = 0.0, pbn = 0.0;
+        if (j < A.n) {
+          const double qb = pbv[u] + P.gamma * sp[u];            // :154
+          rbv = qb - ybv[u];
+          dn = (dv[u] - ybv[u]) + qb;                            // :164
+          ybn = dn + P.gamma * sw[u];                            // :148
+          pbn = (ybn - sqrt(ybn * ybn + P.four_ag)) / 2.0;       // :151
+        }
+        my_rb2 += rbv * rbv;
+        my_d2 += dn * dn;
+        if (j / T == ij.x || j / T == ij.y) {   // what this CTA's next sweep reads
+          P.a[j] = (F)(P.gamma * dn);
+          P.b[j] = (F)(P.gamma * pbn);
+        }
+        if (j / EDGE_THREADS == (int)blockIdx.x) {   // owner of the chunk: state of the next iteration, clear ahead
+          d1[j] = dn;
+          yb1[j] = ybn;
+          pb1[j] = pbn;
+          xclr[j] = 0.0;
+          xclr[total + j] = 0.0;
+        }
+      }
+    }
+    block_sum2(my_rb2, my_d2, sm.red);
+    double g_r = 0.0, g_w = 0.0;
+    for (int i = tid; i < grid; i += EDGE_THREADS) {
+      g_r += __ldcg(part + 2 * i);
+      g_w += __ldcg(part + 2 * i + 1);
+    }
+    block_sum2(g_r, g_w, sm.red);
+    bool conv = false;
+    double rp = CUDART_INF, rdl = CUDART_INF;
+    if (it >= 1) {  // the first iteration never stops: smooth_learning.py:156-161
+      rp = sqrt(g_r) / sqrt(gw_prev);
+      rdl = sqrt(my_rb2) / sqrt(gd_prev);
+      conv = (rp < P.tol) && (rdl < P.tol);
+    }
+    gw_prev = g_w;
+    gd_prev = my_d2;
+    const bool had_check = it >= 1;
+    ++it;
+    const bool done = conv || it >= P.maxit;
+    if (blockIdx.x == 0 && tid == 0) {
+      flags[FLAG_IT] = it;
+      if (had_check) {
+        P.resid[0] = rp;
+        P.resid[1] = rdl;
+      }
+      P.gprev[0] = gw_prev;
+      P.gprev[1] = gd_prev;
+      if (conv) flags[FLAG_CONVERGED] = 1;
+      if (done) {
+        __threadfence();
+        flags[FLAG_DONE] = 1;
+      }
+    }
+    if (done) break;
+  }
+}
+
+// canonical node state <- the parity buffer the small kernel ended on (so that stepwise calls,
+// gl_solver_node_state and a later gl_solver_run see one consistent state)
+__global__ void small_finalize_kernel(const int *flags, double *d, double *yb, double *pb, const double *d1,
+                                      const double *yb1, const double *pb1, int total) {
+  if ((flags[FLAG_IT] & 1) == 0) return;
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < total; j += gridDim.x * blockDim.x) {
+    d[j] = d1[j];
+    yb[j] = yb1[j];
+    pb[j] = pb1[j];
+  }
+}
+
+template <typename F> static int small_launch_t(gl_solver *s, int iters, cudaStream_t st) {
+  SmallArgs<F> P;
+  EdgeArgs<F> &A = P.E;
+  A.w = static_cast<F *>(s->w);
+  A.z = static_cast<const F *>(s->z);
+  A.r = nullptr;
+  A.gstride = s->gstride;
+  A.a = static_cast<const F *>(s->a);
+  A.b = static_cast<const F *>(s->b);
+  A.xch = s->xch;
+  A.xch_stride = s->xch_stride;
+  A.cta_partial = s->cta_partial;
+  A.hdr = reinterpret_cast<int *>(s->comm);
+  A.world = 1;
+  A.rank = 0;
+  A.peers = s->peers;
+  A.tile_ij = s->tile_ij;
+  A.flags = s->flags;
+  A.n = s->n;
+  A.npad = s->npad;
+  A.ntl = s->ntl;
+  A.c = (F)s->c;
+  A.tgz = (F)(2.0 * s->gamma);
+  P.st[0][0] = s->d; P.st[0][1] = s->yb; P.st[0][2] = s->pb;
+  P.st[1][0] = s->small_state; P.st[1][1] = s->small_state + s->npad; P.st[1][2] = s->small_state + 2 * (int64_t)s->npad;
+  P.a = static_cast<F *>(s->a);
+  P.b = static_cast<F *>(s->b);
+  P.cta_partial = s->cta_partial;
+  P.gprev = s->gprev;
+  P.resid = s->resid;
+  P.bar = s->grid_bar;
+  P.gamma = s->gamma;
+  P.four_ag = 4.0 * s->alpha * s->gamma;
+  P.tol = s->tol;
+  P.maxit = s->maxit;
+  P.iters = iters;
+  const int nchunks = (s->npad + EDGE_THREADS - 1) / EDGE_THREADS;
+  const int grid = s->ntl > nchunks ? s->ntl : nchunks;
+  GL_CUDA(cudaMemsetAsync(s->grid_bar, 0, sizeof(unsigned int), st));
+  void *args[] = {&P};
+  GL_CUDA(cudaLaunchCooperativeKernel((void *)persistent_small_kernel<F>, dim3(grid), dim3(EDGE_THREADS), args, 0, st));
+  small_finalize_kernel<<<8, 256, 0, st>>>(s->flags, s->d, s->yb, s->pb, P.st[1][0], P.st[1][1], P.st[1][2], s->npad);
+  g_launches.fetch_add(2, std::memory_order_relaxed);
+  GL_LAUNCH_CHECK();
+  return GL_OK;
+}
+
+// One tile per CTA and everything resident at once: is the redundant-node form applicable?
+bool small_applicable(gl_solver *s) {
+  if (s->K != 1 || s->world > 1 || s->ntl == 0 || s->trace) return false;
+  if (s->tile_begin != 0 || s->tile_end != num_tiles(s->n)) return false;
+  if (s->small_grid_max == 0) {
+    int per_sm = 0, sms = 0;
+    cudaError_t e = s->dtype == GL_F32
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, persistent_small_kernel<float>, EDGE_THREADS, 0)
+        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, persistent_small_kernel<double>, EDGE_THREADS, 0);
+    if (e != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device) != cudaSuccess) {
+      cudaGetLastError();
+      s->small_grid_max = -1;
+    } else {
+      s->small_grid_max = per_sm * sms > 0 ? per_sm * sms : -1;
+    }
+  }
+  return s->small_grid_max > 0 && s->ntl <= s->small_grid_max && s->small_state != nullptr;
+}
+
+int launch_persistent_small(gl_solver *s, int iters, cudaStream_t st) {
+  return s->dtype == GL_F32 ? small_launch_t<float>(s, iters, st) : small_launch_t<double>(s, iters, st);
+}
+
 template <typename F> static int persistent_launch_t(gl_solver *s, int iters, cudaStream_t st) {
   PersistArgs<F> P;
   EdgeArgs<F> &A = P.E;

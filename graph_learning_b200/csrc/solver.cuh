@@ -58,6 +58,8 @@ struct gl_solver {
   int *flags = nullptr;           // [FLAG_COUNT]
   unsigned int *grid_bar = nullptr;  // grid barrier counter of the persistent kernel
   int persist_grid = 0;           // resident CTAs of the persistent kernel (0 = not sized yet)
+  double *small_state = nullptr;  // K == 1, full range, small n: second parity of [d | yb | pb] (persistent_small_kernel)
+  int small_grid_max = 0;         // resident CTAs of persistent_small_kernel (0 = not sized yet, -1 = unusable)
   long long *trace = nullptr;     // optional phase timestamps of the persistent kernel: [TRACE_CAP][TRACE_STAMPS] ns
 
   // parameters of the current solve
@@ -78,5 +80,7 @@ int launch_signal(gl_solver *s, cudaStream_t st);
 int launch_gram_edges(gl_solver *s, cudaStream_t st);
 int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
 int launch_persistent(gl_solver *s, int iters, cudaStream_t st);
+int launch_persistent_small(gl_solver *s, int iters, cudaStream_t st);
+bool small_applicable(gl_solver *s);
 int fill_tile_table(gl_solver *s);
 }  // namespace gl

@@ -24,8 +24,17 @@ def sl():
     return m
 
 
+@pytest.fixture(params=["small", "large"])
+def driver(request, monkeypatch):
+    """K = 1 solves run inside one resident kernel; below ~2,900 nodes (one tile per CTA) that is the
+    one-barrier form with the node phase done redundantly by every CTA (persistent_small_kernel), above it
+    the two-barrier persistent_kernel.  GL_B200_SMALL=0 forces the latter so that both see every case."""
+    monkeypatch.setenv("GL_B200_SMALL", "1" if request.param == "small" else "0")
+    return request.param
+
+
 @pytest.mark.parametrize("its", [1, 2, 3, 5, 50])
-def test_iterates_fp64(golden, sl, its):
+def test_iterates_fp64(golden, sl, its, driver):
     g = golden("solver_n100")
     w, info = sl.gsp_learn_graph_log_degrees(g["z"] * g["theta"], 1, 1, maxit=its, edge_tol=-np.inf,
                                              return_info=True)
@@ -34,7 +43,7 @@ def test_iterates_fp64(golden, sl, its):
     assert rel(w, g[f"w_raw_it{its}"]) < 1e-12
 
 
-def test_converged_fp64(golden, sl):
+def test_converged_fp64(golden, sl, driver):
     g = golden("solver_n100")
     z = g["z"] * g["theta"]
     w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, return_info=True)
@@ -47,7 +56,7 @@ def test_converged_fp64(golden, sl):
     assert abs(info.rel_dual - oinfo.rel_dual) < 1e-6 * oinfo.rel_dual
 
 
-def test_converged_fp32(golden, sl):
+def test_converged_fp32(golden, sl, driver):
     g = golden("solver_n100")
     z = g["z"] * g["theta"]
     w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, dtype="float32", return_info=True)
@@ -61,7 +70,7 @@ def test_converged_fp32(golden, sl):
     assert np.array_equal((w > 0)[~band], (ref > 0)[~band])
 
 
-def test_alt_parameters_and_warm_start(golden, sl):
+def test_alt_parameters_and_warm_start(golden, sl, driver):
     g = golden("solver_n100")
     z = g["z"] * g["theta"]
     w = sl.gsp_learn_graph_log_degrees(z, 0.7, 1.9, maxit=400, tol=1e-6, step_size=0.8, edge_tol=1e-4)
@@ -91,7 +100,7 @@ def test_ndim_error(sl):
 
 
 @pytest.mark.parametrize("n", [2, 3, 127, 128, 129, 257, 300])
-def test_ragged_sizes_vs_oracle(sl, n):
+def test_ragged_sizes_vs_oracle(sl, n, driver):
     """Tile-boundary cases: n below / at / above multiples of the 128-node tile."""
     rng = np.random.default_rng(n)
     pts = rng.uniform(size=(n, 3))
@@ -102,7 +111,7 @@ def test_ragged_sizes_vs_oracle(sl, n):
     assert rel(w, orc.to_square(wo)) < 1e-11
 
 
-def test_n2000_fp64_vs_c_oracle(sl):
+def test_n2000_fp64_vs_c_oracle(sl, driver):
     """Config 2 size (n=2,000, E=1,999,000), maxit-limited, against the C one-sweep oracle."""
     from oracle import c_oracle
     rng = np.random.default_rng(7)
@@ -233,3 +242,32 @@ def test_peer_exchange_two_shards_one_gpu(sl):
         assert torch.equal(shards[0].node_state(), shards[1].node_state())
     for s in shards:
         s.close()
+
+
+@pytest.mark.parametrize("n", [700, 1500, 2900])
+def test_small_and_large_drivers_agree_and_continue_across_launches(sl, n, monkeypatch):
+    """More iterations than one launch holds (50 per launch): the small kernel's parity / triple-buffer
+    indices must carry over from launch to launch; converged run against the oracle; node state readable
+    afterwards (canonical buffers)."""
+    from oracle import c_oracle
+    rng = np.random.default_rng(n)
+    pts = rng.uniform(size=(n, 2))
+    z = orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1)) * (0.15 * n)
+    for maxit in (137, 1000):
+        wo, it_o, rp_o, _ = c_oracle.solve(z, maxit=maxit, threshold=False)
+        res = {}
+        for mode in ("1", "0"):
+            monkeypatch.setenv("GL_B200_SMALL", mode)
+            zt = torch.as_tensor(z, device="cuda")
+            s = sl.Solver(n, 1, torch.float64)
+            s.load(zt[None, :].contiguous())
+            s.begin(maxit=maxit)
+            s.run()
+            st = s.status()
+            res[mode] = (s.store(-np.inf)[0].cpu().numpy(), s.node_state().cpu().numpy(), st)
+            s.close()
+            assert st.n_iter == it_o
+            assert rel(res[mode][0], wo) < 1e-10
+            assert abs(st.rel_primal - rp_o) < 1e-7 * rp_o
+        assert rel(res["1"][0], res["0"][0]) < 1e-12
+        assert rel(res["1"][1], res["0"][1]) < 1e-12
