@@ -227,8 +227,10 @@ int gl_logmodel_solve(const void *z_packed_dev, const double *z_scale_host, int 
                       double alpha, double beta, const void *edge_init_packed_dev, int maxit,
                       double tol, double step_size, double edge_tol, void *w_packed_dev,
                       int *n_iter, double *rel_primal, double *rel_dual, void *stream);
-/* Same with HOST buffers (pageable or pinned): H2D of Z (and edge_init), solve, D2H of W.
- * This is the end-to-end path bench.py times as "e2e". */
+/* Same with HOST buffers (pageable or pinned): H2D of Z (and edge_init), solve, D2H of W.  This is
+ * the entry point the reference-side binding of INTEGRATION.md calls (integration/_gl_b200.py, driven by
+ * tests/test_gpu_boundary.py against the reference's goldens).  bench.py's "e2e" times the Python
+ * drop-in function instead, which returns the reference's dense (n, n) shape for a 1-D call. */
 int gl_logmodel_solve_host(const void *z_packed_host, const double *z_scale_host, int n, int K,
                            int dtype, double alpha, double beta,
                            const void *edge_init_packed_host, int maxit, double tol,
