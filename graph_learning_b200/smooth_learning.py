@@ -35,6 +35,7 @@ __all__ = [
     "pdist_sq",
     "pdist_sq_tiles",
     "SolveInfo",
+    "release_solver_cache",
 ]
 
 
@@ -479,6 +480,29 @@ def get_theta(sq_pdists, avg_degree, blocks=None):
 # --------------------------------------------------------------------------------------------
 # the solver (reference :47-174)
 # --------------------------------------------------------------------------------------------
+_solver_cache: dict = {}
+
+
+def _cached_solver(n: int, n_graphs: int, dt: torch.dtype) -> "Solver":
+    """The workspace of the last (n, K, dtype, device) solve is kept for the next call: the reference
+    rebuilds its operator on every call (:133), callers in a loop (GLMM / k-Graphs outer iterations, a
+    benchmark) should not pay two n^2-sized device allocations and frees per solve.  One workspace at a
+    time; :func:`release_solver_cache` frees it."""
+    key = (int(n), int(n_graphs), dt, torch.cuda.current_device())
+    ws = _solver_cache.get(key)
+    if ws is None or getattr(ws, "_h", None) is None:
+        release_solver_cache()
+        ws = Solver(n, n_graphs, dt)
+        _solver_cache[key] = ws
+    return ws
+
+
+def release_solver_cache() -> None:
+    """Free the cached single-GPU solver workspace (w, z and the node vectors of the last problem size)."""
+    for key in list(_solver_cache):
+        _solver_cache.pop(key).close()
+
+
 def gsp_learn_graph_log_degrees(
     distances,
     alpha: float,
@@ -547,7 +571,7 @@ def gsp_learn_graph_log_degrees(
             raise ValueError(f"edge_init has shape {tuple(edge_init.shape)}, expected "
                              f"{(n_edges,) if n_dim == 1 else (n_edges, n_graphs)}")
 
-    solver = Solver(n, n_graphs, dt)
+    solver = _cached_solver(n, n_graphs, dt)
     nvtx = torch.cuda.nvtx.range
     try:
         with nvtx("gl.load"):
@@ -558,8 +582,9 @@ def gsp_learn_graph_log_degrees(
             info = solver.status()
         with nvtx("gl.store"):
             result = solver.square(edge_tol) if n_dim == 1 else solver.store(edge_tol)
-    finally:
-        solver.close()
+    except BaseException:
+        release_solver_cache()
+        raise
     res = result
     if out is not None:
         out_t = torch.from_numpy(out) if isinstance(out, np.ndarray) else out
@@ -655,7 +680,7 @@ class LogModel(BaseEstimator):
         group = self._group()
         sharded = None
         if group is False:
-            solver = Solver(n, 1, dt)
+            solver = _cached_solver(n, 1, dt)
             tile_range = None
         else:
             from .sharded import sharded_workspace
@@ -694,9 +719,10 @@ class LogModel(BaseEstimator):
                     info = sharded.status()
                 with nvtx("gl.gather_square"):
                     result = sharded.gather_square(self.edge_tol, self.weights_on)
-        finally:
+        except BaseException:
             if sharded is None:
-                solver.close()
+                release_solver_cache()
+            raise
         return result, info
 
     def fit(self, x, out=None):
