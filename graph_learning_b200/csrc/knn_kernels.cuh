@@ -343,7 +343,8 @@ __global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnF
     const typename Vec2<F>::type abi = ab[me];
     const bool live = me < A.n;
     // node state of this row: issued now, consumed after the slice
-    const double dv = live ? A.d[me] : 0.0, ybv = live ? A.yb[me] : 0.0, pbv = live ? A.pb[me] : 0.0;
+    // (pb is not stored: it is a function of yb, recomputed below -- 16 MB less traffic per iteration at n = 1e6)
+    const double dv = live ? A.d[me] : 0.0, ybv = live ? A.yb[me] : 0.0;
     // per-row partial sums in the edge dtype (a row holds a few dozen slots), folded into float64 when
     // the row ends -- the dense tile routine does the same over 64 edges (edge_tile.cuh)
     F acc_p = F(0), acc_w = F(0), row_r = F(0), row_w = F(0);
@@ -393,6 +394,7 @@ __global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnF
     typename Vec2<F>::type pr;
     pr.x = pr.y = F(0);
     if (live) {
+      const double pbv = (ybv - sqrt(ybv * ybv + A.four_ag)) / 2.0;   // :151 of the previous iteration, bit-identical
       const double qb = pbv + A.gamma * (double)acc_p;            //                      :154
       const double rbv = qb - ybv;
       const double dn = (dv - ybv) + qb;                          //                      :164
@@ -402,7 +404,6 @@ __global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnF
       d2 += dn * dn;
       A.d[me] = dn;
       A.yb[me] = ybn;
-      A.pb[me] = pbn;
       pr.x = (F)(A.gamma * dn);
       pr.y = (F)(A.gamma * pbn);
     }
