@@ -50,8 +50,8 @@ def parse():
     p.add_argument("--iters", type=int, default=1000, help="solver iterations per step (maxit)")
     p.add_argument("--avg-degree", type=int, default=8)
     p.add_argument("--dtype", default="float32", choices=["float32", "float64"])
-    p.add_argument("--z-method", default="gram", choices=["gram", "gram2", "direct"],
-                   help="Z build (setup): tcgen05 Gram GEMM on 3-/2-term bf16 splits, or exact differences")
+    p.add_argument("--z-method", default="gram", choices=["gram", "gram16", "gram2", "direct"],
+                   help="Z build (setup): tcgen05 Gram GEMM on 3-slice bf16 / 2-slice fp16 / 2-slice bf16 splits, or exact differences")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-parity", action="store_true")
@@ -415,13 +415,14 @@ def run_dense(a):
     z_full = torch.empty(ntiles * tt, dtype=tdt, device=dev)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     use_gram = a.dtype == "float32" and a.z_method != "direct"
-    terms = 2 if a.z_method == "gram2" else 3
+    terms = 2 if a.z_method in ("gram2", "gram16") else 3
+    z_variant = 7 if a.z_method == "gram16" else 0
 
     def build_z():
         if use_gram:
             ws = _gram_workspace(m, n, terms, dev)
             nat.check(lib.gl_pdist_sq_gram(x.data_ptr(), m, n, x.stride(0), None, None, z_full.data_ptr(),
-                                           nat.LAYOUT_TILED, 0, ntiles, terms, 0, 0, ws.data_ptr(), ws.numel(), None))
+                                           nat.LAYOUT_TILED, 0, ntiles, terms, 0, z_variant, ws.data_ptr(), ws.numel(), None))
         else:
             nat.check(lib.gl_pdist_sq(x.data_ptr(), m, n, x.stride(0), None, None, z_full.data_ptr(),
                                       nat.LAYOUT_TILED, 0, ntiles, gdt, None))
@@ -749,7 +750,8 @@ def z_setup(a, z_ms, use_gram, terms, E, m, n, theta_ms, theta):
     nt = -(-n // 128)
     units = nt * (nt + 1) // 2                                       # default variant: 128 x 128 units
     m_pad = -(-m // 64) * 64
-    mma_flops = units * 2.0 * 128 * 128 * m_pad * (3 if terms == 2 else 6)
+    pairs = 4 if a.z_method == "gram16" else (3 if terms == 2 else 6)
+    mma_flops = units * 2.0 * 128 * 128 * m_pad * pairs
     achieved = mma_flops / (z_ms * 1e-3) / 1e12
     burst = sustained = None
     try:
@@ -759,7 +761,8 @@ def z_setup(a, z_ms, use_gram, terms, E, m, n, theta_ms, theta):
     except OSError:
         burst, sustained = 1590.0, 1400.0
     out.update({
-        "z_kernel": f"gl::gram_kernel<{terms},128,32,split> (tcgen05.mma kind::f16 on {terms}-slice bf16 operands with "
+        "z_method": a.z_method, "mma_products_per_k_step": pairs,
+        "z_kernel": f"gl::gram_kernel<{terms},128,32,split> (tcgen05.mma kind::f16 on {terms}-slice {'fp16' if a.z_method == 'gram16' else 'bf16'} operands with "
                     "an exact leading slice, TMA SWIZZLE_64B, leading/small TMEM accumulators folded into float64 "
                     "registers every 256 samples) + gl::gram_colmax_kernel + gl::gram_split_kernel",
         "z_roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s (bf16 MMA flops executed, "

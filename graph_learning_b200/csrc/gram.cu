@@ -36,6 +36,7 @@
 //          through the 126 MB L2).
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <type_traits>
 #include <vector>
@@ -166,6 +167,23 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int n_dim) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_dim >> 3) << 17) | ((uint32_t)(GR_BM >> 4) << 24);
 }
 
+// Same with A = B = F16 (format code 0): the two-slice normalised form (gram_split16_kernel).
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int n_dim) {
+  return (1u << 4) | ((uint32_t)(n_dim >> 3) << 17) | ((uint32_t)(GR_BM >> 4) << 24);
+}
+// Power-of-two scale exponent of a node from its column maximum (float bits): 2^e > max_t |y_ti|.
+__host__ __device__ inline int gram_node_exponent(int colmax_bits) {
+  float mx;
+#ifdef __CUDA_ARCH__
+  mx = __int_as_float(colmax_bits);
+#else
+  memcpy(&mx, &colmax_bits, sizeof(mx));
+#endif
+  int e = 0;
+  if (mx > 0.f) frexpf(mx, &e);   // mx = f * 2^e, f in [0.5, 1)
+  return e < -100 ? -100 : (e > 127 ? 127 : e);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Stage 1: split + transpose + norms
 // ------------------------------------------------------------------------------------------------
@@ -272,6 +290,76 @@ gram_split_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, co
         ((s_norm[0][tid] + s_norm[1][tid]) + s_norm[2][tid]) + s_norm[3][tid];
 }
 
+// Two-slice fp16 form (variant 7).  Every node is normalised by its own power of two, yh = y * 2^-e_i with
+// |yh| < 1, and cut into  yh0 = k / 256 (|k| <= 256: exact in fp16; products of leading slices are integers
+// <= 2^16 in units of 2^-16, so 256 of them sum EXACTLY in the fp32 TMEM accumulator, as in the bf16 form)
+// and yh1 = fp16(yh - yh0), |yh1| <= 2^-9, whose 11 significant bits leave an absolute error <= 2^-21 --
+// fp16 carries 3 more bits per slice than bf16, which is what lets two slices replace three.  The GEMM then
+// needs the four products (0,0) | (0,1) (1,0) (1,1) instead of six, and the epilogue scales the normalised
+// Gram entry back by 2^(e_i + e_j) (exact).  fp16's narrow exponent range is why the planes are
+// normalised; the residual plane may use fp16 subnormals (spacing 2^-24: finer than needed).
+__global__ void __launch_bounds__(256)
+gram_split16_kernel(const float *__restrict__ X, int64_t m, int n, int64_t ldx, const float *__restrict__ row_scale,
+                    const float *__restrict__ col_shift, __half *__restrict__ planes, int64_t m_pad, int n_pad,
+                    double *__restrict__ norm_part, int64_t seg_len, const int *__restrict__ colmax) {
+  __shared__ float tile[GR_SPLIT_TILE][GR_SPLIT_TILE + 1];
+  __shared__ double s_norm[4][GR_SPLIT_TILE];
+  const int tid = threadIdx.x;
+  const int node0 = blockIdx.x * GR_SPLIT_TILE;
+  const int64_t t_begin = (int64_t)blockIdx.y * seg_len;
+  const int64_t t_end = min(t_begin + seg_len, m_pad);
+  const int lx = tid & 63, ly = tid >> 6;
+  const int gnode = node0 + lx;
+  const float sh = (col_shift && gnode < n) ? col_shift[gnode] : 0.f;
+  const int wx = tid >> 2, wy = tid & 3;
+  const int64_t plane_stride = (int64_t)n_pad * m_pad;
+  double nsum = 0.0;
+  const int e = gram_node_exponent(colmax[node0 + wx]);
+  const float q_up = ldexpf(1.f, 8 - e), q_down = ldexpf(1.f, e - 8), inv_scale = ldexpf(1.f, -e);
+
+  for (int64_t t0 = t_begin; t0 < t_end; t0 += GR_SPLIT_TILE) {
+#pragma unroll
+    for (int r = 0; r < GR_SPLIT_TILE / 4; ++r) {
+      const int row = ly + 4 * r;
+      const int64_t tt = t0 + row;
+      float y = 0.f;
+      if (tt < m && gnode < n) {
+        const float sc = row_scale ? row_scale[tt] : 1.f;
+        y = sc * (X[tt * ldx + gnode] - sh);
+      }
+      tile[row][lx] = y;
+      nsum += (double)y * (double)y;
+    }
+    __syncthreads();
+    uint32_t p0[8], p1[8];
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+      __half h0[2], h1[2];
+#pragma unroll
+      for (int x = 0; x < 2; ++x) {
+        const float v = tile[wy * 16 + i + x][wx];
+        const float k = rintf(v * q_up);                    // |k| <= 256
+        h0[x] = __float2half_rn(k * (1.f / 256.f));         // exact
+        h1[x] = __float2half_rn((v - k * q_down) * inv_scale);   // residual (exact in fp32) in normalised units
+      }
+      p0[i >> 1] = (uint32_t)__half_as_ushort(h0[0]) | ((uint32_t)__half_as_ushort(h0[1]) << 16);
+      p1[i >> 1] = (uint32_t)__half_as_ushort(h1[0]) | ((uint32_t)__half_as_ushort(h1[1]) << 16);
+    }
+    uint4 *d0 = reinterpret_cast<uint4 *>(planes + (int64_t)(node0 + wx) * m_pad + t0 + wy * 16);
+    uint4 *d1 = reinterpret_cast<uint4 *>(planes + plane_stride + (int64_t)(node0 + wx) * m_pad + t0 + wy * 16);
+    d0[0] = make_uint4(p0[0], p0[1], p0[2], p0[3]);
+    d0[1] = make_uint4(p0[4], p0[5], p0[6], p0[7]);
+    d1[0] = make_uint4(p1[0], p1[1], p1[2], p1[3]);
+    d1[1] = make_uint4(p1[4], p1[5], p1[6], p1[7]);
+    __syncthreads();
+  }
+  s_norm[ly][lx] = nsum;
+  __syncthreads();
+  if (tid < GR_SPLIT_TILE)
+    norm_part[(int64_t)blockIdx.y * n_pad + node0 + tid] =
+        ((s_norm[0][tid] + s_norm[1][tid]) + s_norm[2][tid]) + s_norm[3][tid];
+}
+
 // norms[i] = sum over segments, fixed order (deterministic)
 __global__ void gram_norm_reduce_kernel(const double *__restrict__ norm_part, int n_pad, int segs,
                                         double *__restrict__ norms) {
@@ -285,7 +373,8 @@ __global__ void gram_norm_reduce_kernel(const double *__restrict__ norm_part, in
 // ------------------------------------------------------------------------------------------------
 // Stage 2: the GEMM
 // ------------------------------------------------------------------------------------------------
-template <int TERMS, int BN, int BK, bool SPLIT>
+// FMT 0: bf16 slices in true units (3 or 6 products); FMT 1: fp16 normalised slices, TERMS = 2, 4 products
+template <int TERMS, int BN, int BK, bool SPLIT, int FMT = 0>
 struct GramCfg {
   static constexpr int ROW_BYTES = BK * 2;                             // bf16
   static constexpr int A_PLANE = GR_BM * ROW_BYTES;                    // bytes
@@ -302,7 +391,8 @@ struct GramCfg {
   static constexpr int THREADS = 32 * (GR_CTRL_WARPS + EPI_WARPS);
   static constexpr int TMEM_COLS = (SPLIT ? 4 : 2) * BN;               // double-buffered accumulator(s)
   static constexpr int SMALL_OFF = 2 * BN;                             // first column of the small-term tiles
-  static constexpr int PAIRS = TERMS == 2 ? 3 : 6;
+  static constexpr int PAIRS = TERMS == 2 ? (FMT == 1 ? 4 : 3) : 6;
+  static_assert(FMT == 0 || (TERMS == 2 && SPLIT), "the fp16 form is the 2-slice split-accumulator scheme");
   static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
   static_assert(STAGES >= 2, "need at least a double-buffered operand pipeline");
   static_assert(TMEM_COLS <= 512, "TMEM has 512 columns");
@@ -318,13 +408,14 @@ struct GramArgs {
   float *Z;
   int layout, n, nt, tile_begin, tile_end;
   int debug;              // diagnostics only (GL_GRAM_DEBUG): 1 = skip the TMEM folds, 2 = skip the MMAs, 4 = 1 pair
+  const int *colmax;      // FMT 1: column maxima (float bits) -> per-node scale exponents for the epilogue
 };
 
-template <int TERMS, int BN, int BK, bool SPLIT>
-__global__ void __launch_bounds__(GramCfg<TERMS, BN, BK, SPLIT>::THREADS, 1)
+template <int TERMS, int BN, int BK, bool SPLIT, int FMT = 0>
+__global__ void __launch_bounds__(GramCfg<TERMS, BN, BK, SPLIT, FMT>::THREADS, 1)
 gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
             const GramArgs args) {
-  using C = GramCfg<TERMS, BN, BK, SPLIT>;
+  using C = GramCfg<TERMS, BN, BK, SPLIT, FMT>;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)C::STAGES * C::STAGE_BYTES);
@@ -383,7 +474,7 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) ==================================================================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BN);
+      constexpr uint32_t idesc = FMT == 1 ? umma_idesc_f16(BN) : umma_idesc_bf16(BN);
       // cross terms in decreasing weight: (a-plane, b-plane)
       constexpr int pa[6] = {0, 0, 1, 1, 0, 2};
       constexpr int pb[6] = {0, 1, 0, 1, 2, 0};
@@ -489,6 +580,14 @@ gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       const int gi = I * GR_BM + r;
       const int c0 = col0 - J * GR_BM;
       const double ni = args.norms[gi];
+      if (FMT == 1) {   // normalised Gram entries back to true units: x 2^(e_i + e_j), exact
+        const int ei = gram_node_exponent(args.colmax[gi]);
+#pragma unroll
+        for (int x = 0; x < CPW; ++x) {
+          const int ex = ei + gram_node_exponent(args.colmax[col0 + x]);    // in [-200, 254]: a normal double
+          acc[x] = (AccT)((double)acc[x] * __longlong_as_double((long long)(ex + 1023) << 52));
+        }
+      }
       if (args.layout == GL_LAYOUT_TILED) {
         float *dst = args.Z + (int64_t)(tile - args.tile_begin) * TT + r * T + c0;
 #pragma unroll
@@ -606,9 +705,9 @@ static void build_units(int nt, int nb /*tiles per unit*/, int tile_begin, int t
   }
 }
 
-template <int TERMS, int BN, int BK, bool SPLIT>
+template <int TERMS, int BN, int BK, bool SPLIT, int FMT = 0>
 static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &base, int n_sms, cudaStream_t st) {
-  using C = GramCfg<TERMS, BN, BK, SPLIT>;
+  using C = GramCfg<TERMS, BN, BK, SPLIT, FMT>;
   EncodeTiledFn encode;
   GL_TRY(get_encode_fn(&encode));
   CUtensorMap map_a, map_b;
@@ -618,10 +717,11 @@ static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &b
   const CUtensorMapSwizzle sw = BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   const cuuint32_t box_a[3] = {BK, GR_BM, TERMS};
   const cuuint32_t box_b[3] = {BK, BN, TERMS};
-  CUresult r1 = encode(&map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_a, estride,
+  const CUtensorMapDataType dtp = FMT == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUresult r1 = encode(&map_a, dtp, 3, ws + L.off_planes, gdim, gstride, box_a, estride,
                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  CUresult r2 = encode(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_b, estride,
+  CUresult r2 = encode(&map_b, dtp, 3, ws + L.off_planes, gdim, gstride, box_b, estride,
                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS)
@@ -629,7 +729,7 @@ static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &b
   GramArgs a = base;
   a.num_kb = (int)(L.m_pad / BK);
   a.kb_per_chunk = std::max(1, a.kb_per_chunk / BK);   // caller passed samples per chunk
-  auto kern = gram_kernel<TERMS, BN, BK, SPLIT>;
+  auto kern = gram_kernel<TERMS, BN, BK, SPLIT, FMT>;
   GL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
   const int grid = std::min(n_sms, a.n_units);
   kern<<<grid, C::THREADS, C::SMEM_BYTES, st>>>(map_a, map_b, a);
@@ -682,8 +782,9 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
                                     (long long)m, (long long)ldx, n);
   if (layout != GL_LAYOUT_PACKED && layout != GL_LAYOUT_TILED) return fail(GL_E_ARG, "bad layout");
   if (terms != 2 && terms != 3) return fail(GL_E_ARG, "terms must be 2 or 3");
-  if (variant < 0 || variant > 6) return fail(GL_E_ARG, "variant must be 0..6");
+  if (variant < 0 || variant > 7) return fail(GL_E_ARG, "variant must be 0..7");
   if (variant == 6 && terms != 3) return fail(GL_E_ARG, "the CTA-pair variant needs terms = 3");
+  if (variant == 7 && terms != 2) return fail(GL_E_ARG, "the fp16 two-slice variant needs terms = 2");
   if (layout == GL_LAYOUT_PACKED) {
     tile_begin = 0;
     tile_end = num_tiles(n);
@@ -716,7 +817,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   // The split-accumulator variants of the 3-term form carry the exact leading slice.  With 2 terms
   // the residual slice alone cannot hold the bits the quantisation pushes into it, so the 2-term
   // form keeps plain round-to-nearest bf16 slices (still with separate accumulators).
-  const bool exact0 = (variant <= 1 || variant == 6) && terms == 3;
+  const bool exact0 = ((variant <= 1 || variant == 6) && terms == 3) || variant == 7;
   int *colmax = reinterpret_cast<int *>(ws + L.off_colmax);
   const float *Xf = (const float *)X, *rsf = (const float *)row_scale, *csf = (const float *)col_shift;
   if (exact0) {
@@ -727,7 +828,10 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
 #define GL_SPLIT(TERMS_, EX_)                                                                                \
   gram_split_kernel<TERMS_, EX_><<<sgrid, 256, 0, st>>>(Xf, m, n, ldx, rsf, csf, planes, L.m_pad, L.n_pad, \
                                                         norm_part, L.seg_len, colmax)
-  if (terms == 2) {
+  if (variant == 7) {
+    gram_split16_kernel<<<sgrid, 256, 0, st>>>(Xf, m, n, ldx, rsf, csf, reinterpret_cast<__half *>(planes), L.m_pad, L.n_pad,
+                                               norm_part, L.seg_len, colmax);
+  } else if (terms == 2) {
     GL_SPLIT(2, false);
   } else {
     if (exact0) GL_SPLIT(3, true); else GL_SPLIT(3, false);
@@ -761,6 +865,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   a.nt = nt;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
+  a.colmax = colmax;
   {
     const char *dbg = getenv("GL_GRAM_DEBUG");   // timing diagnostics of the pipeline stages; results are wrong
     a.debug = dbg ? atoi(dbg) : 0;
@@ -771,6 +876,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   //          2 / 3 = single accumulator, 256- / 128-wide units, 32-sample k-blocks
   //          4 / 5 = single accumulator, 256- / 128-wide units, 64-sample k-blocks
   if (variant == 6) return launch_gram_2cta(L, ws, a, n_sms, st);
+  if (variant == 7) return launch_gram<2, 128, 32, true, 1>(L, ws, a, n_sms, st);
   if (terms == 3) {
     switch (variant) {
       case 0: return launch_gram<3, 128, 32, true>(L, ws, a, n_sms, st);

@@ -352,8 +352,8 @@ def release_gram_workspace() -> None:
 
 
 def _resolve_method(method: str, dt: torch.dtype, m: int) -> str:
-    if method not in ("auto", "direct", "gram", "gram2"):
-        raise ValueError(f"method must be auto, direct, gram or gram2, got {method!r}")
+    if method not in ("auto", "direct", "gram", "gram2", "gram16"):
+        raise ValueError(f"method must be auto, direct, gram, gram16 or gram2, got {method!r}")
     if method == "auto":
         return "gram" if (dt == torch.float32 and m >= GRAM_MIN_SAMPLES) else "direct"
     if method != "direct" and dt != torch.float32:
@@ -368,7 +368,9 @@ def _pdist_into(xd, rs, cs, out, layout, tile_begin, tile_end, method, chunk=0, 
         nat.check(nat.lib().gl_pdist_sq(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
                                         layout, tile_begin, tile_end, _gl_dtype(xd.dtype), _stream()))
         return
-    terms = 2 if method == "gram2" else 3
+    terms = 2 if method in ("gram2", "gram16") else 3
+    if method == "gram16":
+        variant = 7      # fp16 two-slice form (normalised planes, four products)
     ws = _gram_workspace(m, n, terms, xd.device)
     nat.check(nat.lib().gl_pdist_sq_gram(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
                                          layout, tile_begin, tile_end, terms, int(chunk), int(variant),

@@ -42,7 +42,7 @@ def smooth300():
 
 
 @pytest.mark.parametrize("m,n", [(1, 2), (5, 3), (64, 130), (257, 129), (300, 515), (1000, 100)])
-@pytest.mark.parametrize("method,tol", [("gram", TOL3), ("gram2", TOL2)])
+@pytest.mark.parametrize("method,tol", [("gram", TOL3), ("gram2", TOL2), ("gram16", TOL3)])
 def test_gram_shapes_vs_oracle(sl, m, n, method, tol):
     """Ragged sizes: n and m off the 128 / 64 grid, a single sample, the smallest graph."""
     rng = np.random.default_rng(m * 1000 + n)
@@ -215,3 +215,62 @@ def test_logmodel_fit_float32_through_the_tensor_core_path(sl, smooth300):
     raw, _ = orc.solve_two_pass(z * theta, maxit=400, edge_tol=-np.inf)
     away = np.abs(orc.to_square(raw) - 1e-3) > 1e-5
     assert ((mdl.weights_ > 0) == (w_ref_sq > 0))[away].all()
+
+
+# ---- fp16 two-slice form (variant 7, method "gram16"): normalised planes, four products ------------------
+def test_gram16_precision_on_smooth_signals(sl, smooth300):
+    """Two fp16 slices (8-bit exact leading slice + 11-bit remainder, per-node power-of-two normalisation)
+    against float64 on signals where the Gram form cancels: same error budget as the 3-slice bf16 form."""
+    x = smooth300.astype(np.float32)
+    ref = orc.pdist_sq(x.astype(np.float64))
+    scale = (x.astype(np.float64) ** 2).sum(0).mean()
+    err = lambda z: np.abs(z.cpu().numpy().astype(np.float64) - ref).max() / scale  # noqa: E731
+    z16 = sl.pdist_sq(x, method="gram16")
+    assert rel(z16.cpu().numpy(), ref) < TOL3
+    assert err(z16) < 1e-6
+    assert err(z16) <= 4 * err(sl.pdist_sq(x, method="gram")) + 1e-7
+    assert rel(sl.pdist_sq(x, method="gram16", chunk=64).cpu().numpy(), ref) < TOL3
+
+
+def test_gram16_scales_offsets_and_weighted_form(sl):
+    """Nodes of very different magnitude (the normalisation is per node), a node of zeros, a huge and a tiny
+    overall scale (outside fp16's range in true units), and the GLMM weighted / centred form."""
+    rng = np.random.default_rng(8)
+    x = rng.standard_normal((400, 160)).astype(np.float32)
+    x *= np.exp(rng.uniform(-6, 6, size=160)).astype(np.float32)[None, :]
+    x[:, 5] = 0.0
+    for factor in (1.0, 3.0e4, 1.0e-6):
+        xs = (x * np.float32(factor)).astype(np.float32)
+        ref = orc.pdist_sq(xs.astype(np.float64))
+        z = sl.pdist_sq(xs, method="gram16").cpu().numpy()
+        assert np.isfinite(z).all() and (z >= 0).all()
+        assert rel(z, ref) < TOL3
+    resp = rng.uniform(0.1, 1.0, size=400).astype(np.float32)
+    mean = x.mean(0).astype(np.float32)
+    y = resp.astype(np.float64)[:, None] * (x.astype(np.float64) - mean.astype(np.float64))
+    z = sl.pdist_sq(x, row_scale=resp, col_shift=mean, method="gram16").cpu().numpy()
+    assert rel(z, orc.pdist_sq(y)) < TOL3
+
+
+def test_gram16_tiled_range_and_weights(sl, smooth300):
+    rng = np.random.default_rng(12)
+    n, m = 700, 320
+    x = torch.from_numpy(rng.standard_normal((m, n)).astype(np.float32)).cuda()
+    nt = -(-n // 128)
+    total = nt * (nt + 1) // 2
+    full = sl.pdist_sq_tiles(x, 0, total, method="direct")
+    out = sl.pdist_sq_tiles(x, 3, 11, method="gram16")
+    ref = full[3 * 128 * 128:11 * 128 * 128]
+    assert rel(out.cpu().numpy(), ref.cpu().numpy()) < TOL3
+    assert (out[ref == 0] == 0).all()
+    # learned weights from gram16 distances within the float32 tolerance of the float64 solve
+    xs = smooth300
+    z64 = orc.pdist_sq(xs)
+    theta = orc.theta_for_degree(orc.to_square(z64), 6)
+    w_ref, info_ref = orc.solve_two_pass(z64 * theta, maxit=400)
+    z16 = sl.pdist_sq(xs.astype(np.float32), method="gram16")
+    th16 = sl._theta_packed(z16, 300, 6)
+    assert abs(th16 - theta) < 1e-5 * theta
+    w16, info = sl.gsp_learn_graph_log_degrees(z16, 1, 1, maxit=400, z_scale=th16, return_info=True)
+    assert info.n_iter == info_ref.n_iter
+    assert rel(w16.cpu().numpy(), orc.to_square(w_ref)) < 1e-4
