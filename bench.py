@@ -50,7 +50,7 @@ def parse():
     p.add_argument("--iters", type=int, default=1000, help="solver iterations per step (maxit)")
     p.add_argument("--avg-degree", type=int, default=8)
     p.add_argument("--dtype", default="float32", choices=["float32", "float64"])
-    p.add_argument("--z-method", default="gram", choices=["gram", "gram16", "gram2", "direct"],
+    p.add_argument("--z-method", default="gram16", choices=["gram", "gram16", "gram2", "direct"],
                    help="Z build (setup): tcgen05 Gram GEMM on 3-slice bf16 / 2-slice fp16 / 2-slice bf16 splits, or exact differences")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")

@@ -47,7 +47,7 @@ def run_config4(a):
     rd = resp.t().contiguous()
 
     def distances():
-        return torch.stack([sl.pdist_sq(x, row_scale=rd[k], col_shift=means[k], method="gram") for k in range(K)])
+        return torch.stack([sl.pdist_sq(x, row_scale=rd[k], col_shift=means[k], method="gram16") for k in range(K)])
 
     z = distances()
     torch.cuda.synchronize()

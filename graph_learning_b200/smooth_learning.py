@@ -326,8 +326,9 @@ def sum_squareform(n: int):
 # --------------------------------------------------------------------------------------------
 # pairwise squared distances (reference :278) and theta (reference :177-235)
 # --------------------------------------------------------------------------------------------
-# tensor-core Gram form: used by "auto" for float32 when there are enough samples to pay for the
-# split pre-pass; the exact direct-difference kernel stays the float64 path and the parity anchor.
+# tensor-core Gram form (two-slice fp16 since round 2): used by "auto" for float32 when there are enough
+# samples to pay for the split pre-pass; the exact direct-difference kernel stays the float64 path and
+# the parity anchor.
 GRAM_MIN_SAMPLES = 256
 _gram_ws = {}
 
@@ -355,7 +356,7 @@ def _resolve_method(method: str, dt: torch.dtype, m: int) -> str:
     if method not in ("auto", "direct", "gram", "gram2", "gram16"):
         raise ValueError(f"method must be auto, direct, gram, gram16 or gram2, got {method!r}")
     if method == "auto":
-        return "gram" if (dt == torch.float32 and m >= GRAM_MIN_SAMPLES) else "direct"
+        return "gram16" if (dt == torch.float32 and m >= GRAM_MIN_SAMPLES) else "direct"
     if method != "direct" and dt != torch.float32:
         raise ValueError("the tensor-core Gram form is float32 only; use method='direct' for float64")
     return method
@@ -382,8 +383,10 @@ def pdist_sq(x, row_scale=None, col_shift=None, dtype=None, method="auto", chunk
 
     With ``row_scale`` (m,) / ``col_shift`` (n,) the signals are first mapped to
     ``row_scale[:, None] * (x - col_shift)`` -- the GLMM M-step form (glmm.py:61-68).
-    ``method``: "direct" = exact differences on the FMA pipe (float32/float64); "gram" = tcgen05
-    Gram GEMM on 3-term bf16 splits (float32, ~fp32 accuracy); "gram2" = 2-term splits (faster,
+    ``method``: "direct" = exact differences on the FMA pipe (float32/float64); "gram16" = tcgen05
+    Gram GEMM on two fp16 slices of per-node normalised signals (float32 accuracy: weights within
+    3e-6 of the float64 solve; four products per k-step; the float32 default); "gram" = the same on
+    three bf16 slices (six products, 1.35x slower, same accuracy); "gram2" = 2-term bf16 splits (faster,
     ~16 bits); "auto" = gram for float32 with >= 256 samples, direct otherwise.
     Returns a CUDA tensor of shape (E,).
     """

@@ -173,7 +173,7 @@ def test_gram_config2_size_against_direct(sl):
 
 
 def test_auto_picks_gram_for_float32(sl, smooth300):
-    assert sl._resolve_method("auto", torch.float32, 1000) == "gram"
+    assert sl._resolve_method("auto", torch.float32, 1000) == "gram16"
     assert sl._resolve_method("auto", torch.float32, 10) == "direct"
     assert sl._resolve_method("auto", torch.float64, 1000) == "direct"
     with pytest.raises(ValueError):
@@ -207,7 +207,7 @@ def test_logmodel_fit_float32_through_the_tensor_core_path(sl, smooth300):
     theta = orc.theta_for_degree(orc.to_square(z), 6)
     w_ref, info_ref = orc.solve_two_pass(z * theta, maxit=400)
     w_ref_sq = orc.to_square(w_ref)
-    assert sl._resolve_method("auto", torch.float32, x.shape[0]) == "gram"
+    assert sl._resolve_method("auto", torch.float32, x.shape[0]) == "gram16"
     mdl = sl.LogModel(avg_degree=6, maxit=400, dtype="float32").fit(x)
     assert abs(mdl.theta_ - theta) < 1e-5 * theta
     assert mdl.n_iter_ == info_ref.n_iter

@@ -35,7 +35,7 @@ def test_edge_count_must_be_triangular(sl):
 
 
 def test_method_resolution(sl):
-    assert sl._resolve_method("auto", torch.float32, sl.GRAM_MIN_SAMPLES) == "gram"
+    assert sl._resolve_method("auto", torch.float32, sl.GRAM_MIN_SAMPLES) == "gram16"
     assert sl._resolve_method("auto", torch.float32, sl.GRAM_MIN_SAMPLES - 1) == "direct"
     assert sl._resolve_method("auto", torch.float64, 10 ** 6) == "direct"
     with pytest.raises(ValueError, match="method must be"):

@@ -25,8 +25,8 @@ def main():
     print(json.dumps({"n": n, "m": m, "theta64": th64, "iters64": info64.n_iter, "mean_norm2": scale,
                       "z_median_over_norm2": float(z64.median()) / scale, "z_min_over_norm2": float(z64.min()) / scale,
                       "edges_kept": int((w64t > 0).sum().item() // 2)}), flush=True)
-    for method, chunk, variant in (("direct", 0, 0), ("gram", 256, 0), ("gram", 128, 0), ("gram", 64, 0), ("gram", 512, 0),
-                                   ("gram2", 256, 0), ("gram", 256, 2), ("gram", 1 << 20, 0)):
+    for method, chunk, variant in (("direct", 0, 0), ("gram", 256, 0), ("gram16", 256, 0), ("gram16", 128, 0), ("gram", 64, 0),
+                                   ("gram2", 256, 0), ("gram", 256, 2)):
         z = sl.pdist_sq(x, method=method, chunk=chunk, variant=variant)
         th = sl._theta_packed(z, n, k)
         w, info = sl.gsp_learn_graph_log_degrees(z * th, 1, 1, maxit=maxit, return_info=True, dtype="float32")
