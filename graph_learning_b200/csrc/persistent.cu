@@ -118,6 +118,13 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
     GL_STAMP(2);
     // ---------------- N phase --------------------------------------------------------------------
     if (blockIdx.x == 0) {
+      // The degree partials are complete (barrier above): publish them at once.  The two residual
+      // scalars are folded afterwards and published through a SECOND flag (HDR_SIG2), which a peer only
+      // needs at the very end of its node phase -- the fold is off every rank's critical path.
+      if (A.world > 1 && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
+        __threadfence_system();
+        st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
+      }
       double r2 = 0.0, w2 = 0.0;
       for (int i = tid; i < (int)gridDim.x; i += EDGE_THREADS) {
         r2 += __ldcg(A.cta_partial + 2 * i);
@@ -129,9 +136,9 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
         xb[2 * total + 1] += w2;
       }
       __syncthreads();
-      if (A.world > 1 && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
+      if (A.world > 1 && tid < A.world) {
         __threadfence_system();
-        st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
+        st_relaxed_sys(A.peers.hdr[tid] + HDR_SIG2 + A.rank, seq + 1);
       }
     }
     GL_STAMP(3);
@@ -200,6 +207,15 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
         if (c == 0) {  // edge-side sums over the ranks, then clear the slots of the next exchange
           double r2 = 0.0, w2 = 0.0;
           if (A.world > 1) {
+            for (int r = 0; r < A.world; ++r) {   // the scalars travel behind their own flag (published after the fold)
+              const long long t0 = clock64();
+              while (ld_acquire_sys(A.hdr + HDR_SIG2 + r) < seq + 1) {
+                if (clock64() - t0 > 6000000000LL) {
+                  flags[FLAG_ERROR] = 1;
+                  break;
+                }
+              }
+            }
             for (int r = 0; r < A.world; ++r) {
               r2 += ld_relaxed_sys(A.peers.xch[r] + rd_off + 2 * total);
               w2 += ld_relaxed_sys(A.peers.xch[r] + rd_off + 2 * total + 1);

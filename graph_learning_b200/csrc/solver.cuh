@@ -22,6 +22,7 @@ constexpr int GL_MAX_PEERS = 8;
 constexpr int TRACE_CAP = 4096, TRACE_STAMPS = 8;
 constexpr int COMM_HDR = 64;  // doubles (512 B)
 constexpr int HDR_SEQ = 16;
+constexpr int HDR_SIG2 = 8;   // sig2[r] (r < 8): last sequence number whose residual scalars rank r has published
 struct PeerView {
   double *xch[GL_MAX_PEERS];  // base of every rank's xch buffer 0 (peer-mapped)
   int *hdr[GL_MAX_PEERS];     // base of every rank's header
