@@ -14,6 +14,8 @@
 // bounds the sharded case: at 8 GPUs the per-rank edge sweep is ~50 us.
 #include <math_constants.h>
 
+#include <cstdlib>
+
 #include "edge_tile.cuh"
 
 namespace gl {
@@ -28,6 +30,7 @@ template <typename F> struct PersistArgs {
   long long *trace;   // nullable: [TRACE_CAP][TRACE_STAMPS] globaltimer stamps of CTA 0
   double gamma, four_ag, tol;
   int maxit, iters, nchunks;
+  int early_publish;   // peer mode: publish the degree partials before the fold (scalars behind HDR_SIG2)
 };
 
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
@@ -121,7 +124,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
       // The degree partials are complete (barrier above): publish them at once.  The two residual
       // scalars are folded afterwards and published through a SECOND flag (HDR_SIG2), which a peer only
       // needs at the very end of its node phase -- the fold is off every rank's critical path.
-      if (A.world > 1 && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
+      if (A.world > 1 && P.early_publish && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
         __threadfence_system();
         st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
       }
@@ -139,6 +142,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
       if (A.world > 1 && tid < A.world) {
         __threadfence_system();
         st_relaxed_sys(A.peers.hdr[tid] + HDR_SIG2 + A.rank, seq + 1);
+        if (!P.early_publish) st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
       }
     }
     GL_STAMP(3);
@@ -536,6 +540,10 @@ template <typename F> static int persistent_launch_t(gl_solver *s, int iters, cu
   P.maxit = s->maxit;
   P.iters = iters;
   P.nchunks = (s->npad + EDGE_THREADS - 1) / EDGE_THREADS;
+  {
+    const char *e = std::getenv("GL_B200_EARLY_PUBLISH");   // measurement / bisecting aid; default on
+    P.early_publish = !(e && e[0] == '0');
+  }
   if (s->persist_grid == 0) {
     int per_sm = 0, sms = 0;
     GL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, persistent_kernel<F>, EDGE_THREADS, 0));
