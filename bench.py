@@ -412,6 +412,10 @@ def run_dense(a):
 
     # ---- synthetic inputs (setup, untimed except for the reported Z build) ----------------------
     x = rgg_signals_filtered(n, m, seed=0, device=dev, dtype=tdt)
+    if world > 1:
+        # one realisation for all ranks: the generator's sparse products (cuSPARSE) are not bit-reproducible
+        # from device to device, and the parity leg compares the shards with rank 0's copy of Z
+        dist.broadcast(x, 0)
     z_full = torch.empty(ntiles * tt, dtype=tdt, device=dev)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     use_gram = a.dtype == "float32" and a.z_method != "direct"
@@ -457,7 +461,9 @@ def run_dense(a):
         sharded.load_tiles(z_full)
         solver = sharded.solver
     solver.scale_z(theta)          # theta multiplied into the resident tiles in place (smooth_learning.py:289)
-    z_full.mul_(theta)             # the same scaling on the setup copy (used by the parity / e2e legs below)
+    # the same scaling on the setup copy used by the parity / e2e legs: product in float64, rounded once,
+    # exactly what gl_solver_scale_z does
+    z_full.copy_((z_full.double() * theta).to(tdt))
 
     def solve(iters, tol=0.0):
         solver.w_view(0).zero_()

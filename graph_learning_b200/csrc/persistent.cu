@@ -120,14 +120,18 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
     grid_barrier(P.bar, gen);
     GL_STAMP(2);
     // ---------------- N phase --------------------------------------------------------------------
-    if (blockIdx.x == 0) {
-      // The degree partials are complete (barrier above): publish them at once.  The two residual
-      // scalars are folded afterwards and published through a SECOND flag (HDR_SIG2), which a peer only
-      // needs at the very end of its node phase -- the fold is off every rank's critical path.
-      if (A.world > 1 && P.early_publish && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
-        __threadfence_system();
-        st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
-      }
+    // The degree partials are complete (barrier above): CTA 0 publishes them at once and goes straight to
+    // its node chunk.  The two residual scalars are folded by a CTA that owns NO node chunk and travel
+    // behind a SECOND flag (HDR_SIG2), which a peer only needs at the very end of its node phase -- the
+    // fold is off every rank's critical path (measured on 2 GPUs: folding in CTA 0 after the publish was
+    // slower than the old order, because CTA 0's own chunk then started a fence later).
+    const bool early = A.world > 1 && P.early_publish && (int)gridDim.x > P.nchunks;
+    const int fold_cta = early ? (int)gridDim.x - 1 : 0;
+    if (blockIdx.x == 0 && early && tid < A.world) {  // one publishing thread per peer: fences and stores overlap
+      __threadfence_system();
+      st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
+    }
+    if ((int)blockIdx.x == fold_cta) {
       double r2 = 0.0, w2 = 0.0;
       for (int i = tid; i < (int)gridDim.x; i += EDGE_THREADS) {
         r2 += __ldcg(A.cta_partial + 2 * i);
@@ -142,7 +146,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
       if (A.world > 1 && tid < A.world) {
         __threadfence_system();
         st_relaxed_sys(A.peers.hdr[tid] + HDR_SIG2 + A.rank, seq + 1);
-        if (!P.early_publish) st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
+        if (!early) st_relaxed_sys(A.peers.hdr[tid] + A.rank, seq + 1);
       }
     }
     GL_STAMP(3);
