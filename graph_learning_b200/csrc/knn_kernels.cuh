@@ -225,45 +225,6 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_sell_kernel(const int32_t *__
   }
 }
 
-// ---- bulk-async (TMA 1-D) staging of the slot arrays ---------------------------------------------------
-static __device__ __forceinline__ uint32_t knn_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-static __device__ __forceinline__ void knn_mbar_init(uint64_t *bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(knn_smem_u32(bar)), "r"(count));
-}
-static __device__ __forceinline__ void knn_mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(knn_smem_u32(bar)), "r"(bytes) : "memory");
-}
-static __device__ __forceinline__ void knn_mbar_wait(uint64_t *bar, uint32_t parity) {
-  const uint32_t addr = knn_smem_u32(bar);
-  uint32_t ok = 0;
-  while (!ok) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(addr), "r"(parity)
-        : "memory");
-  }
-}
-// global -> shared bulk copy (bytes a multiple of 16, both addresses 16-byte aligned), completion on `bar`
-static __device__ __forceinline__ void knn_bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(knn_smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(knn_smem_u32(bar))
-               : "memory");
-}
-// Ring geometry of the staged sweep: COLS columns of a slice per chunk (32 slots each), DEPTH chunks in
-// flight per warp.  One stage = [dst COLS x 128 B | w COLS x 32 F | z COLS x 32 F].
-template <typename F> struct KnnStage {
-  static constexpr int COLS = sizeof(F) == 4 ? 8 : 4;
-  static constexpr int DEPTH = 3;
-  static constexpr int DST_BYTES = COLS * 128;
-  static constexpr int WZ_BYTES = COLS * 32 * (int)sizeof(F);
-  static constexpr int STAGE_BYTES = DST_BYTES + 2 * WZ_BYTES;
-  static constexpr int RING_BYTES = DEPTH * STAGE_BYTES;                       // per warp
-  static constexpr int SMEM_BYTES = (KNN_THREADS / 32) * (RING_BYTES + DEPTH * 8);   // rings + mbarriers
-};
-
 // Whole iteration in ONE launch (single shard).  Because a lane owns ALL slots of its row, the row's
 // degree sums S p and S w' are complete inside that lane when its slice ends, so the node update of
 // smooth_learning.py:148-164 for that node follows at once: no (S p, S w') round trip through memory, no
@@ -313,13 +274,7 @@ template <typename F> struct KnnFusedArgs {
 // U = columns of a slice in flight per batch (two batches are in flight), MINB = resident CTAs per SM the
 // register budget is sized for: (4, 4) = 64 registers, the default; the others are measurement variants
 // (GL_KNN_VARIANT).
-//
-// STAGED = true (round 2): the slot arrays of a warp's slices are not loaded into registers by the lanes
-// but streamed into a per-warp shared-memory ring by 1-D bulk-async copies (cp.async.bulk, mbarrier
-// completion): lane 0 keeps DEPTH chunks of COLS columns in flight -- three contiguous copies per chunk,
-// running ahead ACROSS slice boundaries -- so the bytes in flight no longer cost registers or occupancy,
-// and the lanes' only exposed latency is the far-end gather.
-template <typename F, bool PEER = false, int U = KNN_UNROLL, int MINB = (sizeof(F) == 4 ? 4 : 2), bool STAGED = false>
+template <typename F, bool PEER = false, int U = KNN_UNROLL, int MINB = (sizeof(F) == 4 ? 4 : 2)>
 __global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnFusedArgs<F> A) {
   if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;
   __shared__ double s_red[KNN_THREADS / 32][4];
@@ -382,122 +337,6 @@ __global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnF
   const F c = A.c, tgz = A.tgz;
   double res = 0.0, wsq = 0.0, rb2 = 0.0, d2 = 0.0;
   const int warps = gridDim.x * (KNN_THREADS / 32);
-  if constexpr (STAGED) {
-    using S = KnnStage<F>;
-    constexpr int C = S::COLS, D = S::DEPTH;
-    extern __shared__ __align__(128) unsigned char knn_dyn_smem[];
-    unsigned char *ring = knn_dyn_smem + (size_t)wp * S::RING_BYTES;
-    uint64_t *full = reinterpret_cast<uint64_t *>(knn_dyn_smem + (size_t)(KNN_THREADS / 32) * S::RING_BYTES) + wp * D;
-    if (lane == 0) {
-      for (int q = 0; q < D; ++q) knn_mbar_init(&full[q], 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncwarp();
-    // ---- fetch cursor (lane 0): next chunk to request, running ahead of the consumer across slices ----
-    int fs = blockIdx.x * (KNN_THREADS / 32) + wp;
-    long long f_off = 0, f_end = 0;
-    auto seek = [&]() {   // position on the next non-empty slice of this warp
-      while (fs < A.nslices) {
-        f_off = A.slice_off[fs];
-        f_end = A.slice_off[fs + 1];
-        if (f_end > f_off) return;
-        fs += warps;
-      }
-    };
-    auto issue = [&](int stage) {
-      if (fs >= A.nslices) return;
-      const long long cols_left = (f_end - f_off) >> 5;
-      const int ncol = cols_left < C ? (int)cols_left : C;
-      unsigned char *st = ring + (size_t)stage * S::STAGE_BYTES;
-      knn_mbar_expect_tx(&full[stage], (uint32_t)ncol * (128u + 64u * (uint32_t)sizeof(F)));
-      knn_bulk_g2s(st, dst + f_off, (uint32_t)ncol * 128u, &full[stage]);
-      knn_bulk_g2s(st + S::DST_BYTES, w + f_off, (uint32_t)ncol * 32u * (uint32_t)sizeof(F), &full[stage]);
-      knn_bulk_g2s(st + S::DST_BYTES + S::WZ_BYTES, z + f_off, (uint32_t)ncol * 32u * (uint32_t)sizeof(F), &full[stage]);
-      f_off += (long long)ncol * 32;
-      if (f_off >= f_end) {
-        fs += warps;
-        seek();
-      }
-    };
-    if (lane == 0) {
-      seek();
-      for (int q = 0; q < D; ++q) issue(q);
-    }
-    __syncwarp();
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int s = blockIdx.x * (KNN_THREADS / 32) + wp; s < A.nslices; s += warps) {
-      const long long off = A.slice_off[s];
-      const int width = (int)((A.slice_off[s + 1] - off) >> 5);
-      const int me = (PEER ? A.row_begin : 0) + s * 32 + lane;
-      const typename Vec2<F>::type abi = ab[me];
-      const bool live = me < A.n;
-      const double dv = live ? A.d[me] : 0.0, ybv = live ? A.yb[me] : 0.0;
-      F acc_p = F(0), acc_w = F(0), row_r = F(0), row_w = F(0);
-      for (int c0 = 0; c0 < width; c0 += C) {
-        const int ncol = width - c0 < C ? width - c0 : C;
-        knn_mbar_wait(&full[stage], phase);
-        const unsigned char *st = ring + (size_t)stage * S::STAGE_BYTES;
-        const int32_t *sd = reinterpret_cast<const int32_t *>(st);
-        const F *sw = reinterpret_cast<const F *>(st + S::DST_BYTES);
-        const F *sz = reinterpret_cast<const F *>(st + S::DST_BYTES + S::WZ_BYTES);
-        int j[C];
-        typename Vec2<F>::type abj[C];
-#pragma unroll
-        for (int u = 0; u < C; ++u) j[u] = u < ncol ? sd[u * 32 + lane] : -1;
-#pragma unroll
-        for (int u = 0; u < C; ++u) abj[u] = ab[j[u] < 0 ? me : j[u]];   // far end: one gather
-#pragma unroll
-        for (int u = 0; u < C; ++u)
-          if (j[u] >= 0) {
-            const F wo = sw[u * 32 + lane], zz = sz[u * 32 + lane];
-            const F y = c * wo - (abi.x + abj[u].x);
-            F pv = y - tgz * zz;
-            pv = pv > F(0) ? pv : F(0);
-            const F q = c * pv - (abi.y + abj[u].y);
-            const F r = q - y;
-            const F wn = (wo - y) + q;
-            w[off + (long long)(c0 + u) * 32 + lane] = wn;
-            acc_p += pv;
-            acc_w += wn;
-            row_r += r * r;
-            row_w += wn * wn;
-          }
-        __syncwarp();                         // every lane is done with this stage ...
-        if (lane == 0) issue(stage);          // ... before the next chunk is copied over it
-        if (++stage == D) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-      res += (double)row_r;
-      wsq += (double)row_w;
-      typename Vec2<F>::type pr;
-      pr.x = pr.y = F(0);
-      if (live) {
-        const double pbv = (ybv - sqrt(ybv * ybv + A.four_ag)) / 2.0;
-        const double qb = pbv + A.gamma * (double)acc_p;
-        const double rbv = qb - ybv;
-        const double dn = (dv - ybv) + qb;
-        const double ybn = dn + A.gamma * (double)acc_w;
-        const double pbn = (ybn - sqrt(ybn * ybn + A.four_ag)) / 2.0;
-        rb2 += rbv * rbv;
-        d2 += dn * dn;
-        A.d[me] = dn;
-        A.yb[me] = ybn;
-        pr.x = (F)(A.gamma * dn);
-        pr.y = (F)(A.gamma * pbn);
-      }
-      A.ab_out[me] = pr;
-      if constexpr (PEER) {
-        const int nd = A.need ? (live ? A.need[me] : 0) : -1;
-#pragma unroll
-        for (int r = 0; r < GL_MAX_PEERS; ++r)
-          if (r < A.world && r != A.rank && ((nd >> r) & 1)) A.ab_out_peer[r][me] = pr;
-      }
-    }
-  } else
   for (int s = blockIdx.x * (KNN_THREADS / 32) + wp; s < A.nslices; s += warps) {
     const long long base = A.slice_off[s] + lane, end = A.slice_off[s + 1];
     const int me = (PEER ? A.row_begin : 0) + s * 32 + lane;

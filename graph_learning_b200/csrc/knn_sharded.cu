@@ -283,24 +283,7 @@ template <typename F> static int knn_fused_launch(gl_knn_solver *k, cudaStream_t
   }
   // (U, MINB) = (4, 4) is the measured best at n = 1e6, k = 20 on B200 (ms per iteration, tools/knn_probe.py,
   // profiles/r2_knn_probe.jsonl): (4, 4) 0.085 | (6, 3) 0.087 | (8, 2) 0.095 | (8, 3, spills) 0.097 | (2, 6) 0.107
-  static const bool staged = [] {
-    const char *e = getenv("GL_KNN_STAGED");   // bulk-async staged sweep (round 2); 0 = the register-prefetch form
-    return !(e && e[0] == '0');
-  }();
-  if (staged) {
-    using S = KnnStage<F>;
-    constexpr int MINB = 3;
-    const int sgrid = std::max(1, std::min(want, std::min(KNN_FUSED_MAX_GRID, 148 * (per_sm > 0 ? per_sm : MINB))));
-    if (k->fused == 3) {
-      auto kern = knn_fused_kernel<F, true, KNN_UNROLL, MINB, true>;
-      GL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::SMEM_BYTES));
-      kern<<<sgrid, KNN_THREADS, S::SMEM_BYTES, st>>>(A);
-    } else {
-      auto kern = knn_fused_kernel<F, false, KNN_UNROLL, MINB, true>;
-      GL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::SMEM_BYTES));
-      kern<<<sgrid, KNN_THREADS, S::SMEM_BYTES, st>>>(A);
-    }
-  } else if (k->fused == 3)
+  if (k->fused == 3)
     knn_fused_kernel<F, true><<<grid, KNN_THREADS, 0, st>>>(A);
   else
     knn_fused_kernel<F, false><<<grid, KNN_THREADS, 0, st>>>(A);
