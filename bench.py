@@ -52,6 +52,7 @@ def parse():
     p.add_argument("--dtype", default="float32", choices=["float32", "float64"])
     p.add_argument("--z-method", default="gram16", choices=["gram", "gram16", "gram2", "direct"],
                    help="Z build (setup): tcgen05 Gram GEMM on 3-slice bf16 / 2-slice fp16 / 2-slice bf16 splits, or exact differences")
+    p.add_argument("--z-variant", type=int, default=-1, help="kernel variant of the Gram GEMM (-1: the method's default)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-parity", action="store_true")
@@ -420,7 +421,7 @@ def run_dense(a):
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     use_gram = a.dtype == "float32" and a.z_method != "direct"
     terms = 2 if a.z_method in ("gram2", "gram16") else 3
-    z_variant = 7 if a.z_method == "gram16" else 0
+    z_variant = a.z_variant if a.z_variant >= 0 else (7 if a.z_method == "gram16" else 0)
 
     def build_z():
         if use_gram:

@@ -737,8 +737,9 @@ static int launch_gram(const GramLayout &L, unsigned char *ws, const GramArgs &b
   return GL_OK;
 }
 
+template <int TERMS_ = 3, int FMT_ = 0>
 static int launch_gram_2cta(const GramLayout &L, unsigned char *ws, const GramArgs &base, int n_sms, cudaStream_t st) {
-  using C = Gram2Cfg;
+  using C = Gram2CfgT<TERMS_, FMT_>;
   EncodeTiledFn encode;
   GL_TRY(get_encode_fn(&encode));
   CUtensorMap map_a, map_b;
@@ -747,10 +748,11 @@ static int launch_gram_2cta(const GramLayout &L, unsigned char *ws, const GramAr
   const cuuint32_t estride[3] = {1, 1, 1};
   const cuuint32_t box_a[3] = {C::BK, GR_BM, C::TERMS};
   const cuuint32_t box_b[3] = {C::BK, C::BN / 2, C::TERMS};
-  CUresult r1 = encode(&map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_a, estride,
+  const CUtensorMapDataType dtp = FMT_ == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUresult r1 = encode(&map_a, dtp, 3, ws + L.off_planes, gdim, gstride, box_a, estride,
                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  CUresult r2 = encode(&map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ws + L.off_planes, gdim, gstride, box_b, estride,
+  CUresult r2 = encode(&map_b, dtp, 3, ws + L.off_planes, gdim, gstride, box_b, estride,
                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS)
@@ -758,9 +760,10 @@ static int launch_gram_2cta(const GramLayout &L, unsigned char *ws, const GramAr
   GramArgs a = base;
   a.num_kb = (int)(L.m_pad / C::BK);
   a.kb_per_chunk = std::max(1, a.kb_per_chunk / C::BK);
-  GL_CUDA(cudaFuncSetAttribute(gram_kernel_2cta, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+  auto kern = gram_kernel_2cta<TERMS_, FMT_>;
+  GL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
   const int clusters = std::max(1, std::min(n_sms / 2, a.n_units));
-  gram_kernel_2cta<<<2 * clusters, C::THREADS, C::SMEM_BYTES, st>>>(map_a, map_b, a);
+  kern<<<2 * clusters, C::THREADS, C::SMEM_BYTES, st>>>(map_a, map_b, a);
   GL_LAUNCH_CHECK();
   return GL_OK;
 }
@@ -782,9 +785,9 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
                                     (long long)m, (long long)ldx, n);
   if (layout != GL_LAYOUT_PACKED && layout != GL_LAYOUT_TILED) return fail(GL_E_ARG, "bad layout");
   if (terms != 2 && terms != 3) return fail(GL_E_ARG, "terms must be 2 or 3");
-  if (variant < 0 || variant > 7) return fail(GL_E_ARG, "variant must be 0..7");
+  if (variant < 0 || variant > 8) return fail(GL_E_ARG, "variant must be 0..8");
   if (variant == 6 && terms != 3) return fail(GL_E_ARG, "the CTA-pair variant needs terms = 3");
-  if (variant == 7 && terms != 2) return fail(GL_E_ARG, "the fp16 two-slice variant needs terms = 2");
+  if ((variant == 7 || variant == 8) && terms != 2) return fail(GL_E_ARG, "the fp16 two-slice variants need terms = 2");
   if (layout == GL_LAYOUT_PACKED) {
     tile_begin = 0;
     tile_end = num_tiles(n);
@@ -817,7 +820,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   // The split-accumulator variants of the 3-term form carry the exact leading slice.  With 2 terms
   // the residual slice alone cannot hold the bits the quantisation pushes into it, so the 2-term
   // form keeps plain round-to-nearest bf16 slices (still with separate accumulators).
-  const bool exact0 = ((variant <= 1 || variant == 6) && terms == 3) || variant == 7;
+  const bool exact0 = ((variant <= 1 || variant == 6) && terms == 3) || variant == 7 || variant == 8;
   int *colmax = reinterpret_cast<int *>(ws + L.off_colmax);
   const float *Xf = (const float *)X, *rsf = (const float *)row_scale, *csf = (const float *)col_shift;
   if (exact0) {
@@ -828,7 +831,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
 #define GL_SPLIT(TERMS_, EX_)                                                                                \
   gram_split_kernel<TERMS_, EX_><<<sgrid, 256, 0, st>>>(Xf, m, n, ldx, rsf, csf, planes, L.m_pad, L.n_pad, \
                                                         norm_part, L.seg_len, colmax)
-  if (variant == 7) {
+  if (variant == 7 || variant == 8) {
     gram_split16_kernel<<<sgrid, 256, 0, st>>>(Xf, m, n, ldx, rsf, csf, reinterpret_cast<__half *>(planes), L.m_pad, L.n_pad,
                                                norm_part, L.seg_len, colmax);
   } else if (terms == 2) {
@@ -845,7 +848,7 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   const int bn = (variant == 2 || variant == 4) ? 256 : 128;
   const int nt = tiles_per_side(n);
   std::vector<int2> units;
-  if (variant == 6)
+  if (variant == 6 || variant == 8)
     build_units_2cta(nt, tile_begin, tile_end, units);
   else
     build_units(nt, bn / T, tile_begin, tile_end, units);
@@ -875,7 +878,8 @@ extern "C" int gl_pdist_sq_gram(const void *X, int64_t m, int n, int64_t ldx, co
   //          1 = same with 64-sample k-blocks (SWIZZLE_128B)
   //          2 / 3 = single accumulator, 256- / 128-wide units, 32-sample k-blocks
   //          4 / 5 = single accumulator, 256- / 128-wide units, 64-sample k-blocks
-  if (variant == 6) return launch_gram_2cta(L, ws, a, n_sms, st);
+  if (variant == 6) return launch_gram_2cta<3, 0>(L, ws, a, n_sms, st);
+  if (variant == 8) return launch_gram_2cta<2, 1>(L, ws, a, n_sms, st);
   if (variant == 7) return launch_gram<2, 128, 32, true, 1>(L, ws, a, n_sms, st);
   if (terms == 3) {
     switch (variant) {

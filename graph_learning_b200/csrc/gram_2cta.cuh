@@ -75,28 +75,37 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16_m256(int n_dim) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_dim >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 }
 
-struct Gram2Cfg {
-  static constexpr int TERMS = 3, BN = 128, BK = 32;
+__host__ __device__ constexpr uint32_t umma_idesc_f16_m256(int n_dim) {
+  return (1u << 4) | ((uint32_t)(n_dim >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+}
+
+// TERMS_ / FMT_ as in GramCfg: (3, 0) = three bf16 slices, six products; (2, 1) = two normalised fp16 slices,
+// four products (gram_split16_kernel), scaled back by 2^(e_i + e_j) in the epilogue.
+template <int TERMS_ = 3, int FMT_ = 0>
+struct Gram2CfgT {
+  static constexpr int TERMS = TERMS_, FMT = FMT_, BN = 128, BK = 32;
   static constexpr int ROW_BYTES = BK * 2;
   static constexpr int A_PLANE = GR_BM * ROW_BYTES;            // 8 KB: this CTA's 128 rows
   static constexpr int B_PLANE = (BN / 2) * ROW_BYTES;         // 4 KB: this CTA's half of the columns' rows
-  static constexpr int STAGE_BYTES = TERMS * (A_PLANE + B_PLANE);   // 36 KB per CTA
-  static constexpr int STAGES = 6;
+  static constexpr int STAGE_BYTES = TERMS * (A_PLANE + B_PLANE);   // 36 KB (24 KB with two slices) per CTA
+  static constexpr int STAGES = TERMS == 3 ? 6 : 8;
   static constexpr int COLS_PER_WARP = 32;
   static constexpr int EPI_WARPS = 4 * (BN / COLS_PER_WARP);
   static constexpr int THREADS = 32 * (GR_CTRL_WARPS + EPI_WARPS);
   static constexpr int TMEM_COLS = 4 * BN;
   static constexpr int SMALL_OFF = 2 * BN;
-  static constexpr int PAIRS = 6;
+  static constexpr int PAIRS = TERMS == 3 ? 6 : (FMT == 1 ? 4 : 3);
   static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 + 256;
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory");
 };
+using Gram2Cfg = Gram2CfgT<3, 0>;
 
 // units: (Ip, J): tile rows 2*Ip and 2*Ip + 1, tile column J
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Gram2Cfg::THREADS, 1)
+template <int TERMS_ = 3, int FMT_ = 0>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((Gram2CfgT<TERMS_, FMT_>::THREADS), 1)
 gram_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const GramArgs args) {
-  using C = Gram2Cfg;
+  using C = Gram2CfgT<TERMS_, FMT_>;
   constexpr int BN = C::BN, BK = C::BK;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -162,7 +171,7 @@ gram_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else if (warp == 1) {
     // ===== MMA issuer: one thread of the LEADER CTA drives both tensor cores ==========================
     if (lane == 0 && leader) {
-      constexpr uint32_t idesc = umma_idesc_bf16_m256(BN);
+      constexpr uint32_t idesc = C::FMT == 1 ? umma_idesc_f16_m256(BN) : umma_idesc_bf16_m256(BN);
       constexpr int pa[6] = {0, 0, 1, 1, 0, 2};
       constexpr int pb[6] = {0, 1, 0, 1, 2, 0};
       int s = 0;
@@ -248,6 +257,14 @@ gram_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int gi = I * GR_BM + r;
       const int c0 = cb * CPW;
       const double ni = args.norms[gi];
+      if (C::FMT == 1) {   // normalised Gram entries back to true units: x 2^(e_i + e_j), exact
+        const int ei = gram_node_exponent(args.colmax[gi]);
+#pragma unroll
+        for (int x = 0; x < CPW; ++x) {
+          const int ex = ei + gram_node_exponent(args.colmax[col0 + x]);
+          acc[x] *= __longlong_as_double((long long)(ex + 1023) << 52);
+        }
+      }
       if (args.layout == GL_LAYOUT_TILED) {
         float *dst = args.Z + (int64_t)(tile - args.tile_begin) * TT + r * T + c0;
 #pragma unroll

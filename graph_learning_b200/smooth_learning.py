@@ -370,8 +370,8 @@ def _pdist_into(xd, rs, cs, out, layout, tile_begin, tile_end, method, chunk=0, 
                                         layout, tile_begin, tile_end, _gl_dtype(xd.dtype), _stream()))
         return
     terms = 2 if method in ("gram2", "gram16") else 3
-    if method == "gram16":
-        variant = 7      # fp16 two-slice form (normalised planes, four products)
+    if method == "gram16" and variant not in (7, 8):
+        variant = 7      # fp16 two-slice form (normalised planes, four products); 8 = the same on CTA pairs
     ws = _gram_workspace(m, n, terms, xd.device)
     nat.check(nat.lib().gl_pdist_sq_gram(_ptr(xd), m, n, xd.stride(0), _ptr(rs), _ptr(cs), _ptr(out),
                                          layout, tile_begin, tile_end, terms, int(chunk), int(variant),

@@ -230,6 +230,26 @@ def test_gram16_precision_on_smooth_signals(sl, smooth300):
     assert err(z16) < 1e-6
     assert err(z16) <= 4 * err(sl.pdist_sq(x, method="gram")) + 1e-7
     assert rel(sl.pdist_sq(x, method="gram16", chunk=64).cpu().numpy(), ref) < TOL3
+    # the same scheme on CTA pairs (cta_group::2, each CTA loading half of the shared operand): identical
+    # products in the same order, hence bit-identical distances
+    zp = sl.pdist_sq(x, method="gram16", variant=8)
+    assert torch.equal(zp, z16)
+
+
+@pytest.mark.parametrize("m,n", [(64, 130), (257, 129), (300, 515), (1000, 300)])
+def test_gram16_pair_variant_shapes_and_tiles(sl, m, n):
+    rng = np.random.default_rng(m + n)
+    x = rng.standard_normal((m, n)).astype(np.float32)
+    ref = orc.pdist_sq(x.astype(np.float64))
+    assert rel(sl.pdist_sq(x, method="gram16", variant=8).cpu().numpy(), ref) < TOL3
+    nt = -(-n // 128)
+    total = nt * (nt + 1) // 2
+    xt = torch.from_numpy(x).cuda()
+    full = sl.pdist_sq_tiles(xt, 0, total, method="gram16")
+    for b, e in [(0, total), (1, total), (total - 1, total)]:
+        if e > b:
+            part = sl.pdist_sq_tiles(xt, b, e, method="gram16", variant=8)
+            assert torch.equal(part, full[b * 128 * 128:e * 128 * 128])
 
 
 def test_gram16_scales_offsets_and_weighted_form(sl):
