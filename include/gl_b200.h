@@ -123,7 +123,11 @@ int gl_pdist_sq(const void *X_dev, int64_t m, int n, int64_t ldx, const void *ro
  *                tensor core's truncating accumulation leaves a bias of ~1e-5 |y|^2);
  *            4 / 5 = same with 64-sample k-blocks (4 needs terms = 2);
  *            6 = the precise scheme as a CTA pair: tcgen05.mma.cta_group::2 (M = 256) on 2-CTA clusters,
- *                each CTA loading its own rows and half of the shared operand (terms = 3).
+ *                each CTA loading its own rows and half of the shared operand (terms = 3);
+ *            7 = TWO fp16 slices (terms = 2) of per-node power-of-two normalised signals: exact 8-bit
+ *                leading slice + 11-bit remainder, four products per k-step, rescaled exactly in the
+ *                epilogue; float32-grade like variant 0 and 1.36x faster (what the Python front end uses);
+ *            8 = variant 7 on CTA pairs (terms = 2; bit-identical to 7, measured slightly slower).
  * `workspace_dev` (any alignment, gl_gram_workspace_bytes(m, n, terms) bytes) receives the split,
  * transposed operand planes.  Needs an sm_100 device. */
 int64_t gl_gram_workspace_bytes(int64_t m, int n, int terms);
