@@ -165,3 +165,25 @@ def test_solver_function_z_scale(golden, sl):
     g1 = golden("solver_n100")
     w1 = sl.gsp_learn_graph_log_degrees(g1["z"], 1, 1, z_scale=float(g1["theta"]))
     assert rel(w1, g1["w_final"]) < 1e-9
+
+
+def test_logmodel_without_avg_degree_and_workspace_cache(sl):
+    """avg_degree=None: theta_ = 1, distances unscaled (:279-280).  Alternating problem sizes replace the
+    cached single-GPU workspace; release_solver_cache frees it."""
+    from graph_learning_b200.synthetic import rgg_signals_exact
+    for n, m in ((60, 80), (140, 90), (60, 80)):
+        x = rgg_signals_exact(n, m, seed=n)
+        mdl = sl.LogModel(maxit=40).fit(x)
+        assert mdl.theta_ == 1
+        w_ref, info = orc.solve_two_pass(orc.pdist_sq(x), maxit=40)
+        assert mdl.n_iter_ == info.n_iter
+        assert rel(mdl.weights_, orc.to_square(w_ref)) < 1e-9
+        z = orc.pdist_sq(x)
+        w = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=40)          # the function form shares the cache
+        assert rel(w, orc.to_square(w_ref)) < 1e-9
+        assert len(sl._solver_cache) == 1
+    sl.release_solver_cache()
+    assert len(sl._solver_cache) == 0
+    # and the next call simply builds a new workspace
+    w = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=40)
+    assert rel(w, orc.to_square(w_ref)) < 1e-9
