@@ -75,8 +75,13 @@ class ShardedLogModelSolver:
         self.tile_range = shard_tiles(n, self.rank, self.world)
         self.solver = Solver(n, n_graphs, dtype, tile_range=self.tile_range)
         self._xch = self.solver.exchange()
+        # a rank without tiles (tiny n, many ranks) cannot run the persistent kernel the peer exchange lives
+        # in: such a split uses the collective form on every rank
+        every_rank_has_tiles = all(e > b for b, e in (shard_tiles(n, r, self.world) for r in range(self.world)))
         if exchange == "auto":
-            exchange = "peer" if (self.world > 1 and n_graphs == 1 and self.world <= 8) else "nccl"
+            exchange = "peer" if (self.world > 1 and n_graphs == 1 and self.world <= 8 and every_rank_has_tiles) else "nccl"
+        elif exchange == "peer" and not every_rank_has_tiles:
+            raise ValueError(f"n={n} leaves some of the {self.world} ranks without a tile: use exchange='nccl' (or fewer ranks)")
         self.exchange = exchange if self.world > 1 else "none"
         if self.exchange == "peer":
             handles = [None] * self.world

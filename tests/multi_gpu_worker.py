@@ -102,6 +102,11 @@ def main():
     wo, _ = orc.solve_one_pass(z_np / 3.0 * 3.0, maxit=25, edge_init=w0.copy())
     if rank == 0:
         assert res is out and rel(out.numpy(), orc.to_square(wo)) <= 1e-11
+    # tiny problem: one tile in all, the second rank owns none -> the collective form on every rank
+    zt_small = z_np[:100 * 99 // 2].copy()
+    w_s = sl.gsp_learn_graph_log_degrees(zt_small, 1, 1, maxit=40, distributed=True)
+    wo_s, _ = orc.solve_one_pass(zt_small, maxit=40)
+    assert rel(w_s, orc.to_square(wo_s)) <= 1e-11
     # a (K, E) batch is not sharded: every rank solves it (replicas), same answer as one GPU
     zb = np.stack([z_np, z_np * 1.3])
     wb = sl.gsp_learn_graph_log_degrees(zb, 1, 1, maxit=20, distributed=True)
