@@ -558,9 +558,25 @@ template <typename F> static int persistent_launch_t(gl_solver *s, int iters, cu
     if (grid > want) grid = want;
     s->persist_grid = grid;
   }
+  int grid = s->persist_grid;
+  // Static stride assignment gives CTA b the tiles b, b + grid, ...: with ntl = q * grid + r the first r
+  // CTAs sweep one tile more than the others, and that last partial wave runs with too few CTAs to
+  // saturate HBM while the rest wait at the grid barrier (8 GPUs at n = 20,000: 1,550 tiles on 296
+  // CTAs = 5.24 per CTA, 3-7 us of barrier wait per iteration in the phase trace).  Shrinking the grid
+  // to ceil(ntl / ceil(ntl / grid)) gives every CTA the same count (259 x 6 there).
+  {
+    const char *e = std::getenv("GL_B200_BALANCED_GRID");
+    const bool balanced = !(e && e[0] == '0');
+    if (balanced && s->ntl > grid) {
+      const int per = (s->ntl + grid - 1) / grid;
+      int g2 = (s->ntl + per - 1) / per;
+      if (g2 < P.nchunks + 1) g2 = P.nchunks + 1 < grid ? P.nchunks + 1 : grid;
+      if (g2 < grid) grid = g2;
+    }
+  }
   GL_CUDA(cudaMemsetAsync(s->grid_bar, 0, sizeof(unsigned int), st));
   void *args[] = {&P};
-  GL_CUDA(cudaLaunchCooperativeKernel((void *)persistent_kernel<F>, dim3(s->persist_grid), dim3(EDGE_THREADS), args, 0, st));
+  GL_CUDA(cudaLaunchCooperativeKernel((void *)persistent_kernel<F>, dim3(grid), dim3(EDGE_THREADS), args, 0, st));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return GL_OK;
 }

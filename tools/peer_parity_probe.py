@@ -40,11 +40,12 @@ def main():
     one.run()
     w1 = one.store(-np.inf)[0].double()
     one.close()
+    var = os.environ.get("PROBE_TOGGLE", "GL_B200_EARLY_PUBLISH")   # which switch the repeats alternate
     sv = ShardedLogModelSolver(n, torch.float32, exchange="peer")
     sv.load_packed(z32[None, :].contiguous())
     for rep in range(2 * reps):
         mode = "1" if rep % 2 == 0 else "0"
-        os.environ["GL_B200_EARLY_PUBLISH"] = mode
+        os.environ[var] = mode
         dist.barrier()
         sv.solver.w_view(0).zero_()
         sv.begin(1.0, 1.0, 0.5, 20, 0.0)
@@ -62,7 +63,7 @@ def main():
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        rec = {"early_publish": mode, "vs_1gpu": float((w - w1).norm() / w1.norm()), "us_per_iteration": float(t.item()) * 1e3 / 400}
+        rec = {var: mode, "vs_1gpu": float((w - w1).norm() / w1.norm()), "us_per_iteration": float(t.item()) * 1e3 / 400}
         if rank == 0:
             rec["vs_oracle"] = float(np.linalg.norm(w.cpu().numpy() - wo) / np.linalg.norm(wo))
         out["runs"].append(rec)
