@@ -558,22 +558,10 @@ template <typename F> static int persistent_launch_t(gl_solver *s, int iters, cu
     if (grid > want) grid = want;
     s->persist_grid = grid;
   }
-  int grid = s->persist_grid;
-  // Static stride assignment gives CTA b the tiles b, b + grid, ...: with ntl = q * grid + r the first r
-  // CTAs sweep one tile more than the others, and that last partial wave runs with too few CTAs to
-  // saturate HBM while the rest wait at the grid barrier (8 GPUs at n = 20,000: 1,550 tiles on 296
-  // CTAs = 5.24 per CTA, 3-7 us of barrier wait per iteration in the phase trace).  Shrinking the grid
-  // to ceil(ntl / ceil(ntl / grid)) gives every CTA the same count (259 x 6 there).
-  {
-    const char *e = std::getenv("GL_B200_BALANCED_GRID");
-    const bool balanced = !(e && e[0] == '0');
-    if (balanced && s->ntl > grid) {
-      const int per = (s->ntl + grid - 1) / grid;
-      int g2 = (s->ntl + per - 1) / per;
-      if (g2 < P.nchunks + 1) g2 = P.nchunks + 1 < grid ? P.nchunks + 1 : grid;
-      if (g2 < grid) grid = g2;
-    }
-  }
+  // (A grid shrunk to ceil(ntl / ceil(ntl / grid)) CTAs, so that every CTA sweeps the same number of tiles, was
+  // measured in round 2: 69.4 vs 69.9 us per iteration on 8 GPUs, 111.6 vs 111.2 on 4 -- the barrier wait in the
+  // phase trace comes from CTA-to-CTA variance, not from a partial last wave; not kept.)
+  const int grid = s->persist_grid;
   GL_CUDA(cudaMemsetAsync(s->grid_bar, 0, sizeof(unsigned int), st));
   void *args[] = {&P};
   GL_CUDA(cudaLaunchCooperativeKernel((void *)persistent_kernel<F>, dim3(grid), dim3(EDGE_THREADS), args, 0, st));
