@@ -63,6 +63,7 @@ SIGNATURES = {
     "gl_solver_node_tail": (c_int, [c_void_p, c_void_p]),
     "gl_solver_comm_handle": (c_int, [c_void_p, c_void_p]),
     "gl_solver_comm_connect": (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    "gl_solver_comm_first_nodes": (c_int, [c_void_p, _pi]),
     "gl_solver_comm_ptr": (c_void_p, [c_void_p, POINTER(c_int64)]),
     "gl_solver_comm_connect_ptrs": (c_int, [c_void_p, c_int, c_int, POINTER(c_void_p)]),
     "gl_solver_comm_publish": (c_int, [c_void_p, c_void_p]),

@@ -359,6 +359,20 @@ int gl_solver_comm_connect_ptrs(gl_solver *s, int rank, int world, void *const *
   return GL_OK;
 }
 
+int gl_solver_comm_first_nodes(gl_solver *s, const int *first_node) {
+  if (!s) return fail(GL_E_ARG, "null solver");
+  if (s->graph_exec) {   // the table is baked into captured launches
+    cudaGraphExecDestroy(s->graph_exec);
+    s->graph_exec = nullptr;
+  }
+  for (int r = 0; r < GL_MAX_PEERS; ++r) {
+    int v = (first_node && r < s->world) ? first_node[r] : 0;
+    if (v < 0 || v > s->npad) return fail(GL_E_ARG, "first_node[%d] = %d out of range", r, v);
+    s->peers.first_node[r] = v;
+  }
+  return GL_OK;
+}
+
 int gl_solver_comm_connect(gl_solver *s, int rank, int world, const void *handles) {
   if (!s || !handles) return fail(GL_E_ARG, "null argument");
   if (world < 1 || world > GL_MAX_PEERS || rank < 0 || rank >= world)

@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(EDGE_THREADS, sizeof(F) == 4 ? 2 : 1) persiste
 #pragma unroll
           for (int r = 0; r < GL_MAX_PEERS; ++r) {
             vp[r] = vw[r] = 0.0;
-            if (r < A.world) {
+            if (r < A.world && idx >= A.peers.first_node[r]) {   // below a rank's first row block its partials are zeros
               vp[r] = ld_relaxed_sys(A.peers.xch[r] + rd_off + idx);
               vw[r] = ld_relaxed_sys(A.peers.xch[r] + rd_off + total + idx);
             }

@@ -26,6 +26,8 @@ constexpr int HDR_SIG2 = 8;   // sig2[r] (r < 8): last sequence number whose res
 struct PeerView {
   double *xch[GL_MAX_PEERS];  // base of every rank's xch buffer 0 (peer-mapped)
   int *hdr[GL_MAX_PEERS];     // base of every rank's header
+  int first_node[GL_MAX_PEERS];  // rank r's tiles touch no node below this one: its partials there are exact zeros
+                                 // and need not be read (0 = read everything; gl_solver_comm_first_nodes)
 };
 
 struct gl_solver {

@@ -87,6 +87,14 @@ class ShardedLogModelSolver:
             handles = [None] * self.world
             dist.all_gather_object(handles, self.solver.comm_handle(), group=group)
             self.solver.comm_connect(self.rank, self.world, b"".join(handles))
+            # rank r's tiles start in tile row I0(r): its partials of the nodes above are zeros, peers skip them
+            firsts = (ctypes.c_int * self.world)()
+            for r in range(self.world):
+                rb, re = shard_tiles(n, r, self.world)
+                row0 = ctypes.c_int()
+                nat.check(nat.lib().gl_shard_rows(n, rb, re, ctypes.byref(row0), None, None, None))
+                firsts[r] = row0.value if re > rb else 0
+            nat.check(nat.lib().gl_solver_comm_first_nodes(self.solver._h, firsts))
             dist.barrier(group=group)
         self.launches = 0
         self._graph: Optional[torch.cuda.CUDAGraph] = None

@@ -200,6 +200,11 @@ void *gl_solver_exchange_ptr(gl_solver *s, int64_t *n_doubles);
  * and begin_finish directly follows begin.  world == 1 restores the plain mode. */
 int gl_solver_comm_handle(gl_solver *s, void *handle64_out);
 int gl_solver_comm_connect(gl_solver *s, int rank, int world, const void *handles /* world x 64 B */);
+/* Optional hint after connecting: first_node[r] (world ints) = the first node rank r's tiles touch (its
+ * first tile row x 128).  Rank r's degree partials below that node are exact zeros, so the persistent
+ * kernel's node phase skips those peer reads (about a quarter of the NVLink traffic of the exchange on
+ * 8 ranks; sums unchanged bit for bit).  NULL = read everything. */
+int gl_solver_comm_first_nodes(gl_solver *s, const int *first_node);
 void *gl_solver_comm_ptr(gl_solver *s, int64_t *n_bytes);
 int gl_solver_comm_connect_ptrs(gl_solver *s, int rank, int world, void *const *comm_ptrs);
 /* Publish this rank's flag as a stand-alone launch (the node tail also does it on entry).  Only
