@@ -19,7 +19,7 @@ import torch.distributed as dist
 from . import _native as nat
 
 __all__ = ["shard_tiles", "ShardBackend", "sharded_schedule", "ShardedLogModelSolver", "sharded_workspace",
-           "solve_distributed", "release_workspaces", "shard_rows", "KnnShardBackend",
+           "solve_distributed", "release_workspaces", "shard_rows", "knn_shard_labels", "KnnShardBackend",
            "knn_exchange", "knn_sharded_schedule", "ShardedKNNSolver"]
 
 
@@ -351,6 +351,25 @@ def knn_sharded_schedule(backend: KnnShardBackend, maxit: int, rank: int, world:
 KNN_EXCHANGES = ("peer", "nccl")
 
 
+def knn_shard_labels(key: torch.Tensor, ei: torch.Tensor, ej: torch.Tensor, n: int, world: int) -> torch.Tensor:
+    """New node numbers (int32, old -> new) for a row-sharded kNN solve: ascending ``key`` first (Morton
+    codes: spatially compact shards, so that most far ends of a rank's slots are its own rows), then inside
+    every rank's row range a stable sort by decreasing degree (rows of one 32-row slice get similar lengths:
+    no padding; rows of equal degree keep the key order) -- what the library does itself for a single
+    full-range shard.  Plain torch ops on the tensors' device (setup-time glue)."""
+    dev = key.device
+    arrangement = torch.argsort(key.to(torch.int64), stable=True)
+    deg = torch.bincount(ei.long(), minlength=n) + torch.bincount(ej.long(), minlength=n)
+    per = shard_rows(n, 0, world)[2]
+    pos = torch.arange(n, device=dev, dtype=torch.int64)
+    dmax = int(deg.max()) if n else 0
+    composite = (pos // per) * (dmax + 1) + (dmax - deg[arrangement])
+    arrangement = arrangement[torch.argsort(composite, stable=True)]
+    lab = torch.empty(n, dtype=torch.int32, device=dev)
+    lab[arrangement] = torch.arange(n, dtype=torch.int32, device=dev)
+    return lab
+
+
 class ShardedKNNSolver:
     """CUDA backend of the row-sharded kNN-support solve (``gl_knn_*``): one process per GPU, each
     rank builds the directed slots of its own rows from the edges touching them; iterations
@@ -396,17 +415,7 @@ class ShardedKNNSolver:
             key = torch.as_tensor(order_key, device=dev).to(torch.int64)
             if key.numel() != self.n:
                 raise ValueError("order_key must hold one key per node")
-            # arrangement: ascending key (spatially compact shards), then inside every rank's row range a stable
-            # sort by decreasing degree (rows of one slice get similar lengths: no padding; rows of equal degree
-            # keep the key order) -- what the library does itself for a single full-range shard
-            arrangement = torch.argsort(key, stable=True)
-            deg = torch.bincount(ei.long(), minlength=self.n) + torch.bincount(ej.long(), minlength=self.n)
-            per = shard_rows(self.n, 0, self.world)[2]
-            pos = torch.arange(self.n, device=dev, dtype=torch.int64)
-            composite = (pos // per) * (int(deg.max()) + 1) + (int(deg.max()) - deg[arrangement])
-            arrangement = arrangement[torch.argsort(composite, stable=True)]
-            lab = torch.empty(self.n, dtype=torch.int32, device=dev)
-            lab[arrangement] = torch.arange(self.n, dtype=torch.int32, device=dev)
+            lab = knn_shard_labels(key, ei, ej, self.n, self.world)
             a, b = lab[ei.long()], lab[ej.long()]
             ei, ej = torch.minimum(a, b).contiguous(), torch.maximum(a, b).contiguous()
         z = _to_device(z, dtype)
