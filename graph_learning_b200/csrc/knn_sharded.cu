@@ -8,6 +8,13 @@
 // (8 B x n in fp32; by the caller: NCCL in-place all-gather, graph_learning_b200/sharded.py).
 // Per iteration:  edge_step -> node_step -> [all-gather ab | all-reduce 4 scalars] -> decide.
 // The node state (d, yb, pb) of foreign rows is never touched.
+//
+// Peer mode (round 2, gl_knn_comm_connect): the exchange moves INTO the one-launch iteration kernel
+// (knn_fused_kernel<F, PEER = true>): a row's new pair is stored straight into the out buffer of every
+// rank that references that node (gl_knn_comm_need), the residual partials and a sequence flag follow
+// through peer-mapped memory, and the next launch evaluates the stop rule for the iteration before it.
+// One launch per iteration per rank, no collective; the ab buffers, the scalar block and the flags live
+// in one CUDA-IPC exported "comm block" per rank.
 #include <cstdlib>
 #include <cstring>
 

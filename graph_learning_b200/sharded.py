@@ -1,10 +1,16 @@
 """Multi-GPU LogModel solve: the triangle's 128x128 tiles are split into contiguous,
 work-balanced shards, one per rank (one process per GPU, ``torch.distributed``); every rank keeps
 its shard of w and z resident and the node vectors replicated.  Per iteration the only exchange is
-ONE all-reduce of the float64 exchange buffer [S p | S w' | residual Grams] (2nK + 2K^2 values,
-320 KB at n = 20,000) between the edge pass and the node tail.
+the sum of the float64 exchange buffer [S p | S w' | residual sums] (2n + 2 values, 320 KB at
+n = 20,000) between the edge pass and the node tail: either ONE NCCL all-reduce
+inside a captured graph (``exchange="nccl"``) or -- the default for 2..8 ranks -- reads of every rank's
+partials from peer-mapped memory inside the persistent iteration kernel (``exchange="peer"``).
 
-The schedule is written against a tiny backend protocol so that the same driver runs the CUDA
+:func:`solve_distributed` and :func:`sharded_workspace` put that path behind the reference-facing calls
+(``gsp_learn_graph_log_degrees(..., distributed=True)``, ``LogModel(..., distributed=True)``);
+:class:`ShardedKNNSolver` is the row-sharded kNN-support solve (config 5).
+
+The dense schedule is written against a tiny backend protocol so that the same driver runs the CUDA
 ``Solver`` over NCCL and, in the CPU test-suite, a host emulation over gloo.
 """
 from __future__ import annotations
