@@ -271,3 +271,23 @@ def test_small_and_large_drivers_agree_and_continue_across_launches(sl, n, monke
             assert abs(st.rel_primal - rp_o) < 1e-7 * rp_o
         assert rel(res["1"][0], res["0"][0]) < 1e-12
         assert rel(res["1"][1], res["0"][1]) < 1e-12
+
+
+@pytest.mark.parametrize("n", [2176, 2944])
+def test_small_driver_float32_at_its_size_limit(sl, n, monkeypatch):
+    """float32 near the largest problem the one-barrier kernel takes (one tile per resident CTA: 276 tiles
+    at n = 2,944), two resident CTAs per SM: against the C oracle and the two-barrier kernel."""
+    from oracle import c_oracle
+    rng = np.random.default_rng(n)
+    pts = rng.uniform(size=(n, 2))
+    z = (orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1)) * (0.15 * n)).astype(np.float32)
+    wo, it_o, _, _ = c_oracle.solve(z.astype(np.float64), maxit=120, threshold=False)
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("GL_B200_SMALL", mode)
+        w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=120, edge_tol=-np.inf, dtype="float32", return_info=True)
+        assert info.n_iter == it_o
+        assert rel(orc.to_packed(w), wo) < 1e-4
+        out[mode] = w
+        sl.release_solver_cache()
+    assert rel(out["1"], out["0"]) < 1e-5
