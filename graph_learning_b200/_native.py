@@ -48,6 +48,7 @@ SIGNATURES = {
     "gl_pdist_sq_gram": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                  c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "gl_theta": (c_int, [c_void_p, c_int, c_int, c_int, c_int, _pd, c_void_p]),
+    "gl_theta_noalloc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, _pd, c_void_p]),
     "gl_theta_partial": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "gl_theta_dense": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, _pd, c_void_p]),
     "gl_solver_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int]),

@@ -216,3 +216,67 @@ extern "C" int gl_theta_partial(const void *Z_tiles, int n, int tile_begin, int 
   return theta_launch(Z_tiles, GL_LAYOUT_TILED, n, n, 0, avg_degree, dtype, tile_begin, tile_end, nullptr, nullptr,
                       cand_out, as_stream(stream));
 }
+
+// ---- allocation-free variant ---------------------------------------------------------------------
+// gl_theta_noalloc: gl_theta for callers that may not call cudaMalloc (CUDA graph capture around the
+// call site, serving loops, harnesses that forbid allocation).  No counterpart in the reference.
+// The per-row statistics that gl_theta keeps in a cudaMalloc'd
+// buffer live in a file-scope device array instead: 2 * GL_THETA_NOALLOC_MAX_NODES + 2 doubles (1 MiB)
+// held by every device that loads the library until the process exits.
+//
+// * In host code `g_theta_scratch` is only a host-side stand-in for the symbol, not a device address:
+//   the address a kernel may use comes from cudaGetSymbolAddress, taken once per device with that device
+//   current (theta_scratch_ptr below) and passed to the kernels like any other pointer.
+// * Every word the call reads from the scratch is written earlier in the same call, on the same stream
+//   (row statistics by theta_rows_kernel for all n rows, the two means by theta_mean_kernel), and
+//   nothing is accumulated into it, so no part of it has to start at zero and nothing is cleared.  The
+//   array keeps the last call's values otherwise.
+// * All calls on a device share the one array: calls that overlap on the GPU (different streams, or
+//   different host threads) race.  Serialise them, or use gl_theta.
+constexpr int THETA_NOALLOC_MAX_NODES = GL_THETA_NOALLOC_MAX_NODES;  // include/gl_b200.h
+constexpr int THETA_NOALLOC_MAX_DEVICES = 64;
+static __device__ __align__(256) double g_theta_scratch[2 * (size_t)THETA_NOALLOC_MAX_NODES + 2];
+
+static int theta_scratch_ptr(double **out) {
+  static std::atomic<double *> cache[THETA_NOALLOC_MAX_DEVICES];  // zero-initialised
+  int dev = -1;
+  GL_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= THETA_NOALLOC_MAX_DEVICES) return fail(GL_E_ARG, "device ordinal %d out of range", dev);
+  double *p = cache[dev].load(std::memory_order_acquire);
+  if (!p) {  // once per device, with that device current; concurrent first calls get the same address
+    cudaError_t e = cudaGetSymbolAddress((void **)&p, g_theta_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(GL_E_CUDA, "cudaGetSymbolAddress(theta scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+    cache[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return GL_OK;
+}
+
+extern "C" int gl_theta_noalloc(const void *Z, int layout, int n, int avg_degree, int dtype, double *theta_host,
+                                void *stream) {
+  if (layout != GL_LAYOUT_PACKED && layout != GL_LAYOUT_TILED) return fail(GL_E_ARG, "bad layout");
+  if (n < 2) return fail(GL_E_SHAPE, "need at least 2 nodes, got n=%d", n);
+  if (n > THETA_NOALLOC_MAX_NODES)
+    return fail(GL_E_SHAPE, "gl_theta_noalloc handles at most %d nodes (static scratch), got n=%d; use gl_theta",
+                THETA_NOALLOC_MAX_NODES, n);
+  if (avg_degree < 1 || avg_degree >= n)
+    return fail(GL_E_ARG, "avg_degree must be in [1, n-1], got %d (n=%d)", avg_degree, n);
+  if (!Z || !theta_host) return fail(GL_E_ARG, "null argument");
+  if (dtype != GL_F32 && dtype != GL_F64) return fail(GL_E_ARG, "dtype must be GL_F32 or GL_F64");
+  double *buf = nullptr;
+  int rc = theta_scratch_ptr(&buf);
+  if (rc != GL_OK) return rc;
+  cudaStream_t st = as_stream(stream);
+  rc = theta_launch(Z, layout, n, n, 0, avg_degree, dtype, 0, num_tiles(n), buf, buf + n, nullptr, st);
+  if (rc != GL_OK) return rc;
+  theta_mean_kernel<<<1, 256, 0, st>>>(buf, buf + n, n, buf + 2 * (size_t)n);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  double h[2] = {0, 0};
+  if (e == cudaSuccess) e = cudaMemcpyAsync(h, buf + 2 * (size_t)n, sizeof(h), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return fail(GL_E_CUDA, "gl_theta_noalloc failed: %s", cudaGetErrorString(e));
+  *theta_host = sqrt(h[0] * h[1]);  // smooth_learning.py:219
+  return GL_OK;
+}

@@ -154,6 +154,18 @@ int gl_theta_partial(const void *Z_tiles_dev, int n, int tile_begin, int tile_en
  * (smooth_learning.py:220-235, get_theta(sq_pdists[slice1, slice2], ...)). */
 int gl_theta_dense(const void *M_dev, int rows, int cols, int64_t ld, int avg_degree, int dtype,
                    double *theta_host, void *stream);
+/* Allocation-free gl_theta.  No counterpart in the reference: added
+ * for callers that may not call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and result as gl_theta, but the per-row statistics
+ * live in a file-scope static device array of 2 * GL_THETA_NOALLOC_MAX_NODES + 2 doubles (1 MiB, held by
+ * every device that loads the library until exit) instead of a cudaMalloc'd buffer; the call makes no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  n > GL_THETA_NOALLOC_MAX_NODES is
+ * refused with GL_E_SHAPE.  All calls on a device share the one array (it keeps the last call's
+ * contents; every word a call reads it has written itself, so nothing needs clearing): calls that
+ * overlap on the GPU race -- serialise them or use gl_theta. */
+#define GL_THETA_NOALLOC_MAX_NODES 65536
+int gl_theta_noalloc(const void *Z_dev, int layout, int n, int avg_degree, int dtype, double *theta_host,
+                     void *stream);
 
 /* ---- the solver (smooth_learning.py:47-174, gsp_learn_graph_log_degrees) ----------------- */
 /* Workspace for K graphs on n nodes owning tiles [tile_begin, tile_end) of the triangle
