@@ -58,7 +58,7 @@ void free_all(gl_solver *s) {
     if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
                   s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace, s->ab, s->gram_part,
-                  s->small_state};
+                  s->small_state, s->batch_partial, s->egram_part};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -167,6 +167,16 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
     while (kp < K) kp <<= 1;
     const size_t ctas = (size_t)s->npad / (256 / kp);
     rc = alloc_zero((void **)&s->gram_part, sizeof(double) * ctas * 2 * KK);
+  }
+  if (rc == GL_OK && K > 1 && K <= 16 && s->gram_part) {  // resident batched kernel (persistent_batch.cu)
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device) == cudaSuccess && sms > 0) {
+      s->egram_ctas = 2 * sms;
+      rc = alloc_zero((void **)&s->batch_partial, sizeof(double) * 2 * 2 * (size_t)s->ntl * K);
+      if (rc == GL_OK) rc = alloc_zero((void **)&s->egram_part, sizeof(double) * (size_t)s->egram_ctas * 2 * KK);
+    } else {
+      cudaGetLastError();
+    }
   }
   if (rc == GL_OK) rc = alloc_zero((void **)&s->flags, sizeof(int) * FLAG_COUNT);
   if (rc == GL_OK) rc = alloc_zero((void **)&s->grid_bar, 64);
@@ -407,9 +417,12 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   if (!s || !s->begun) return fail(GL_E_STATE, "gl_solver_begin/begin_finish must be called first");
   cudaStream_t user = as_stream(stream);
   const char *env = std::getenv("GL_B200_PERSISTENT");
-  const bool persistent = s->K == 1 && s->ntl > 0 && !(env && env[0] == '0');
+  const char *env_batch = std::getenv("GL_B200_BATCH");
+  const bool batch = s->K > 1 && s->ntl > 0 && !(env && env[0] == '0') && !(env_batch && env_batch[0] == '0') &&
+                     batch_applicable(s);
+  const bool persistent = (s->K == 1 && s->ntl > 0 && !(env && env[0] == '0')) || batch;
   const char *env_small = std::getenv("GL_B200_SMALL");
-  const bool small = persistent && !(env_small && env_small[0] == '0') && small_applicable(s);
+  const bool small = persistent && !batch && !(env_small && env_small[0] == '0') && small_applicable(s);
   if (poll_every <= 0) poll_every = persistent ? 50 : (((int64_t)s->ntl * s->K >= 4096) ? 8 : 32);
   if (poll_every > s->maxit) poll_every = s->maxit > 0 ? s->maxit : 1;
 
@@ -479,8 +492,11 @@ int gl_solver_run(gl_solver *s, int poll_every, void *stream) {
   while (!done) {
     while (launched < max_graphs && launched - checked < 2) {
       if (persistent) {
-        // one resident kernel runs the whole chunk (small problems: the one-barrier redundant-node form)
-        rc = small ? launch_persistent_small(s, poll_every, st) : launch_persistent(s, poll_every, st);
+        // one resident kernel runs the whole chunk (small problems: the one-barrier redundant-node form;
+        // K > 1: the batched form with the shared spectral stop rule)
+        rc = batch   ? launch_persistent_batch(s, poll_every, st)
+             : small ? launch_persistent_small(s, poll_every, st)
+                     : launch_persistent(s, poll_every, st);
         if (rc != GL_OK) {
           cleanup();
           return rc;

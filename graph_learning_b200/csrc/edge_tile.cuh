@@ -9,6 +9,7 @@ template <typename F> struct EdgeArgs {
   F *w;
   const F *z;
   F *r;  // batch mode: q - y
+  F *w_out = nullptr;  // two-buffer mode (PP): w' goes here and A.w keeps the previous iterate; nullptr = in place
   int64_t gstride;
   const F *a, *b;          // gamma*d, gamma*pb   [K][npad]
   double *xch;             // exchange buffer 0: [S p | S w' | G_r | G_w]; buffer 1 at +xch_stride
@@ -34,7 +35,7 @@ template <typename F, int CNT> __device__ __forceinline__ void rs_stage(F *v, in
   }
 }
 
-template <typename F, bool BATCH, bool MASKED>
+template <typename F, bool BATCH, bool MASKED, bool PP = false>
 __device__ __forceinline__ void edge_tile(const EdgeArgs<F> &A, F *__restrict__ wt,
                                           const F *__restrict__ zt, F *__restrict__ rt, int I, int J,
                                           const F (*s_ab)[2], const F *aj, const F *bj, F *csp, F *csw,
@@ -122,7 +123,7 @@ __device__ __forceinline__ void edge_tile(const EdgeArgs<F> &A, F *__restrict__ 
         }
         if (active(ch, v)) {
           const int off = r * T + v * 32 * VEC + lane * VEC;
-          st_stream(reinterpret_cast<V *>(wt + off), vec_pack<F>(wn));
+          st_stream(reinterpret_cast<V *>((PP ? rt : wt) + off), vec_pack<F>(wn));   // PP: rt is the second w buffer
           if (BATCH) st_stream(reinterpret_cast<V *>(rt + off), vec_pack<F>(rq));
         }
       }
@@ -153,7 +154,7 @@ template <typename F> struct EdgeSmem {
 // into the degree accumulators g_sp / g_sw.  COHERENT_AB: read a/b through L2 (persistent kernel:
 // they were rewritten by other SMs during this launch).  On return thread 0 holds the tile's
 // residual sums in (r2, w2).  Ends with a __syncthreads-safe state for reuse.
-template <typename F, bool BATCH, bool COHERENT_AB>
+template <typename F, bool BATCH, bool COHERENT_AB, bool PP = false>
 __device__ __forceinline__ void edge_cta_tile(const EdgeArgs<F> &A, EdgeSmem<F> &sm, int t, int k,
                                               double *g_sp, double *g_sw, double &r2, double &w2) {
   using V = typename Vec<F>::type;
@@ -185,12 +186,13 @@ __device__ __forceinline__ void edge_cta_tile(const EdgeArgs<F> &A, EdgeSmem<F> 
   const int64_t base = (int64_t)k * A.gstride + (int64_t)t * TT;
   F *wt = A.w + base;
   const F *zt = A.z + base;
-  F *rt = BATCH ? A.r + base : nullptr;
+  static_assert(!(BATCH && PP), "the two-buffer mode keeps the previous iterate instead of q - y");
+  F *rt = BATCH ? A.r + base : (PP ? A.w_out + base : nullptr);
   F rowfinal, res = F(0), wsq = F(0);
   if (masked)
-    edge_tile<F, BATCH, true>(A, wt, zt, rt, I, J, sm.ab, aj, bj, csp, csw, &rowfinal, res, wsq);
+    edge_tile<F, BATCH, true, PP>(A, wt, zt, rt, I, J, sm.ab, aj, bj, csp, csw, &rowfinal, res, wsq);
   else
-    edge_tile<F, BATCH, false>(A, wt, zt, rt, I, J, sm.ab, aj, bj, csp, csw, &rowfinal, res, wsq);
+    edge_tile<F, BATCH, false, PP>(A, wt, zt, rt, I, J, sm.ab, aj, bj, csp, csw, &rowfinal, res, wsq);
 
   // ---- row totals: one float64 atomic per (row, quantity) -----------------------------------
   {

@@ -12,6 +12,7 @@ enum {
   FLAG_ERROR = 5,       // peer exchange timed out
   FLAG_NEED = 6,        // K > 1: the node tail could not rule the stop out from the cheap bound; the
                         // edge Gram + decide kernels evaluate the exact spectral norms this iteration
+  FLAG_WBUF = 7,        // K > 1, resident kernel: which buffer holds the current iterate (0 = w, 1 = r used as second w)
   FLAG_COUNT = 8
 };
 
@@ -63,6 +64,10 @@ struct gl_solver {
   int persist_grid = 0;           // resident CTAs of the persistent kernel (0 = not sized yet)
   double *small_state = nullptr;  // K == 1, full range, small n: second parity of [d | yb | pb] (persistent_small_kernel)
   int small_grid_max = 0;         // resident CTAs of persistent_small_kernel (0 = not sized yet, -1 = unusable)
+  double *batch_partial = nullptr; // K > 1: [2][ntl * K][2] per-item residual sums of persistent_batch_kernel
+  double *egram_part = nullptr;   // K > 1: [egram_ctas][2][K*K] per-CTA exact edge Grams (deciding iterations)
+  int egram_ctas = 0;             // CTAs egram_part was sized for (two per SM)
+  int batch_grid_max = 0;         // resident CTAs of persistent_batch_kernel (0 = not sized yet, -1 = unusable)
   long long *trace = nullptr;     // optional phase timestamps of the persistent kernel: [TRACE_CAP][TRACE_STAMPS] ns
 
   // parameters of the current solve
@@ -85,5 +90,7 @@ int launch_node_tail(gl_solver *s, bool init, cudaStream_t st);
 int launch_persistent(gl_solver *s, int iters, cudaStream_t st);
 int launch_persistent_small(gl_solver *s, int iters, cudaStream_t st);
 bool small_applicable(gl_solver *s);
+int launch_persistent_batch(gl_solver *s, int iters, cudaStream_t st);
+bool batch_applicable(gl_solver *s);
 int fill_tile_table(gl_solver *s);
 }  // namespace gl

@@ -79,7 +79,49 @@ def test_alt_parameters_and_warm_start(golden, sl, driver):
     assert rel(w, g["w_warm"]) < 1e-11
 
 
-def test_batched_shared_stop(golden, sl):
+@pytest.fixture(params=["resident", "classic"])
+def batch_driver(request, monkeypatch):
+    """K > 1 solves (2 <= K <= 16) run inside one resident kernel with the shared spectral stop rule
+    decided on the device by every CTA (persistent_batch_kernel); GL_B200_BATCH=0 restores the classic
+    per-iteration launches (edge pass + node tail + gated edge Grams) so that both see every case."""
+    monkeypatch.setenv("GL_B200_BATCH", "1" if request.param == "resident" else "0")
+    return request.param
+
+
+@pytest.mark.parametrize("K,n,tol", [(2, 40, 1e-5), (5, 300, 1e-4), (8, 260, 1e-4), (16, 130, 1e-4), (3, 513, 1e-3)])
+def test_batched_converged_vs_oracle(sl, batch_driver, K, n, tol):
+    """Batches that stop on the shared rule (smooth_learning.py:158-166) part-way: the dual ratio falls below
+    tol long before the primal one, so many iterations take the exact edge-Gram stage.  Same iteration count
+    as the oracle, fp64 weights to 1e-10, fp32 to 1e-4; K = 5 and 3 leave node-chunk lanes idle, n = 513 has a
+    one-node last tile row."""
+    rng = np.random.default_rng(K * 1000 + n)
+    zs = []
+    for k in range(K):
+        pts = rng.uniform(size=(n, 2 + k % 3))
+        z = orc.to_packed(((pts[:, None] - pts[None]) ** 2).sum(-1))
+        zs.append(z * orc.theta_for_degree(orc.to_square(z), 6))
+    z = np.stack(zs)
+    wo, oinfo = orc.solve_two_pass(z, maxit=600, tol=tol, threshold=False)
+    assert oinfo.n_iter < 600
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=600, tol=tol, edge_tol=-np.inf, return_info=True)
+    assert info.converged and info.n_iter == oinfo.n_iter
+    assert rel(w, wo) < 1e-10
+    assert abs(info.rel_primal - oinfo.rel_primal) < 1e-6 * oinfo.rel_primal
+    assert abs(info.rel_dual - oinfo.rel_dual) < 1e-6 * oinfo.rel_dual
+    w32, info32 = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=600, tol=tol, edge_tol=-np.inf, dtype="float32",
+                                                 return_info=True)
+    assert abs(info32.n_iter - oinfo.n_iter) <= 2
+    assert rel(w32, wo) < 1e-4
+    # maxit-limited: the last iteration reports exact residuals
+    wm, om = orc.solve_two_pass(z, maxit=7, tol=0.0, threshold=False)
+    w7, i7 = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=7, tol=0.0, edge_tol=-np.inf, return_info=True)
+    assert i7.n_iter == 7 and not i7.converged
+    assert rel(w7, wm) < 1e-12
+    assert abs(i7.rel_primal - om.rel_primal) < 1e-6 * om.rel_primal
+    assert abs(i7.rel_dual - om.rel_dual) < 1e-6 * om.rel_dual
+
+
+def test_batched_shared_stop(golden, sl, batch_driver):
     g = golden("batched_n30")
     z = g["z"] * g["theta"]
     for its in (1, 2, 7, 40):
