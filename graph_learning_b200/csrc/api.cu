@@ -58,7 +58,7 @@ void free_all(gl_solver *s) {
     if (p) cudaIpcCloseMemHandle(p);
   void *ptrs[] = {s->w, s->z, s->r, s->tile_ij, s->d, s->yb, s->pb, s->rb, s->a, s->b,
                   s->comm, s->cta_partial, s->node_partial, s->gprev, s->resid, s->eig_scratch, s->flags, s->grid_bar, s->trace, s->ab, s->gram_part,
-                  s->small_state, s->batch_partial, s->egram_part};
+                  s->small_state, s->batch_partial, s->batch_node, s->egram_part};
   for (void *p : ptrs)
     if (p) cudaFree(p);
 }
@@ -173,6 +173,10 @@ int gl_solver_create(gl_solver **out, int n, int K, int dtype, int tile_begin, i
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device) == cudaSuccess && sms > 0) {
       s->egram_ctas = 2 * sms;
       rc = alloc_zero((void **)&s->batch_partial, sizeof(double) * 2 * 2 * (size_t)s->ntl * K);
+      int kp2 = 1;
+      while (kp2 < K) kp2 <<= 1;
+      const size_t chunks = (size_t)s->npad / (256 / kp2);
+      if (rc == GL_OK) rc = alloc_zero((void **)&s->batch_node, sizeof(double) * (nk + chunks * 2 * K));
       if (rc == GL_OK) rc = alloc_zero((void **)&s->egram_part, sizeof(double) * (size_t)s->egram_ctas * 2 * KK);
     } else {
       cudaGetLastError();

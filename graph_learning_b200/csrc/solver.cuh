@@ -65,6 +65,7 @@ struct gl_solver {
   double *small_state = nullptr;  // K == 1, full range, small n: second parity of [d | yb | pb] (persistent_small_kernel)
   int small_grid_max = 0;         // resident CTAs of persistent_small_kernel (0 = not sized yet, -1 = unusable)
   double *batch_partial = nullptr; // K > 1: [2][ntl * K][2] per-item residual sums of persistent_batch_kernel
+  double *batch_node = nullptr;   // K > 1: [K*npad] d of the previous iterate | [chunks][2][K] per-chunk squared norms
   double *egram_part = nullptr;   // K > 1: [egram_ctas][2][K*K] per-CTA exact edge Grams (deciding iterations)
   int egram_ctas = 0;             // CTAs egram_part was sized for (two per SM)
   int batch_grid_max = 0;         // resident CTAs of persistent_batch_kernel (0 = not sized yet, -1 = unusable)
