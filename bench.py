@@ -282,6 +282,14 @@ class ClockSampler:
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            # warm the two queries of the loop here: the first NVML clock / reasons query on a fresh process
+            # takes milliseconds and holds driver locks, which stalls kernel launches -- visible as a +30 %
+            # outlier when the whole timed region is 30 ms (config 2)
+            pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            try:
+                pynvml.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:  # noqa: BLE001
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
         except Exception:  # noqa: BLE001
             self.nv = None
 

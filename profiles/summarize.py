@@ -32,7 +32,7 @@ METRICS = [
     "lts__throughput.avg.pct_of_peak_sustained_elapsed", "launch__shared_mem_per_block_dynamic",
     "smsp__cycles_active.avg", "sm__cycles_active.avg",
 ]
-OURS = ("persistent_kernel", "gram_kernel", "gram_split_kernel", "gram_colmax_kernel", "gram_norm_reduce_kernel",
+OURS = ("persistent_kernel", "persistent_batch_kernel", "persistent_small_kernel", "gram_kernel", "gram_split_kernel", "gram_colmax_kernel", "gram_norm_reduce_kernel",
         "edge_pass_kernel", "node_tail_kernel", "edge_init_kernel", "theta_rows_kernel", "theta_mean_kernel",
         "pdist_kernel", "knn_", "pack_to_tiles", "tiles_to_", "store_packed", "gram_edges_kernel")
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}
