@@ -177,6 +177,21 @@ def batched():
     save("batched_n30", z=zs, theta=th, w=w, edge_init=init, w_warm=w_warm, w_single=w_single, **w_it)
 
 
+def batched_multitile():
+    """A batch that spans several 128-node tiles and stops on the shared rule part-way (default tol 1e-5):
+    K = 5 graphs (not a power of two), n = 140 nodes.  Inputs are stored as the point clouds the distances come
+    from (the tests rebuild z from them); outputs are the reference's thresholded weights, which pin the stop
+    iteration (one iteration more or less moves the weights by ~1e-5 relative)."""
+    rng = np.random.default_rng(140)
+    n, kk = 140, 5
+    pts = rng.uniform(size=(kk, n, 3))
+    zs = np.stack([pdist(p) ** 2 for p in pts])
+    th = np.array([[get_theta(squareform(z), 6)] for z in zs])
+    w = gsp_learn_graph_log_degrees(zs * th, 1, 1)
+    w_it = gsp_learn_graph_log_degrees(zs * th, 1, 1, maxit=12)      # maxit-limited, thresholded at 1e-5
+    save("batched_n140_k5", pts=pts, theta=th, w=w, w_it12=w_it)
+
+
 def window_model():
     """tests/test_models.py:26-28 data; outputs stored (the reference test asserts nothing)."""
     data = np.random.default_rng(240920).standard_normal((23, 7))
@@ -274,6 +289,7 @@ if __name__ == "__main__":
     theta_cases()
     operators()
     batched()
+    batched_multitile()
     window_model()
     clustering()
     assignment()

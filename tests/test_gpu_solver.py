@@ -121,6 +121,22 @@ def test_batched_converged_vs_oracle(sl, batch_driver, K, n, tol):
     assert abs(i7.rel_dual - om.rel_dual) < 1e-6 * om.rel_dual
 
 
+def test_batched_multitile_golden(golden, sl, batch_driver):
+    """The unmodified reference on a batch that spans several tiles (K = 5, n = 140, golden batched_n140_k5):
+    same stop iteration (240), weights to 1e-9, identical support; fp32 to 1e-4."""
+    g = golden("batched_n140_k5")
+    z = np.stack([orc.to_packed(((p[:, None] - p[None]) ** 2).sum(-1)) for p in g["pts"]]) * g["theta"]
+    w, info = sl.gsp_learn_graph_log_degrees(z, 1, 1, return_info=True)
+    assert info.converged and info.n_iter == 240
+    assert rel(w, g["w"]) < 1e-9
+    assert np.array_equal(w > 0, g["w"] > 0)
+    w12 = sl.gsp_learn_graph_log_degrees(z, 1, 1, maxit=12)
+    assert rel(w12, g["w_it12"]) < 1e-12
+    w32, i32 = sl.gsp_learn_graph_log_degrees(z, 1, 1, dtype="float32", return_info=True)
+    assert abs(i32.n_iter - 240) <= 2
+    assert rel(w32, g["w"]) < 1e-4
+
+
 def test_batched_shared_stop(golden, sl, batch_driver):
     g = golden("batched_n30")
     z = g["z"] * g["theta"]

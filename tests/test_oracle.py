@@ -69,6 +69,24 @@ def test_batched_shared_stop(golden):
     assert rel(g["w"], g["w_single"]) > 1e-7
 
 
+def _batched_n140(g):
+    return np.stack([orc.to_packed(((p[:, None] - p[None]) ** 2).sum(-1)) for p in g["pts"]]) * g["theta"]
+
+
+def test_batched_multitile_golden(golden):
+    """K = 5 graphs on n = 140 nodes (two tile rows on the device) from the unmodified reference: the shared
+    rule stops part-way (iteration 240 of 1,000), so agreement to 1e-12 pins the stop iteration too."""
+    g = golden("batched_n140_k5")
+    z = _batched_n140(g)
+    for solve in (orc.solve_two_pass, orc.solve_one_pass):
+        w, info = solve(z)
+        assert info.n_iter == 240
+        assert rel(w, g["w"]) < 1e-12
+        assert np.array_equal(w > 0, g["w"] > 0)
+        w, _ = solve(z, maxit=12)
+        assert rel(w, g["w_it12"]) < 1e-13
+
+
 def test_ndim_error():
     with pytest.raises(ValueError, match="vector or matrix"):
         orc.solve_two_pass(np.zeros((2, 2, 3)))
