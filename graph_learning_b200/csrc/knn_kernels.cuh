@@ -272,8 +272,8 @@ template <typename F> struct KnnFusedArgs {
 // Buffer reuse is safe without further flags: a rank writes into a peer's out buffer only after that peer
 // has published the end of the previous iteration, which was the last reader of that buffer.
 // U = columns of a slice in flight per batch (two batches are in flight), MINB = resident CTAs per SM the
-// register budget is sized for: (4, 4) = 64 registers, the default; the others are measurement variants
-// (GL_KNN_VARIANT).
+// register budget is sized for: (4, 4) = 64 registers.  Other (U, MINB) pairs were measured in round 2 and
+// none was faster (DESIGN K6); only this instantiation is built.
 template <typename F, bool PEER = false, int U = KNN_UNROLL, int MINB = (sizeof(F) == 4 ? 4 : 2)>
 __global__ void __launch_bounds__(KNN_THREADS, MINB) knn_fused_kernel(const KnnFusedArgs<F> A) {
   if (*reinterpret_cast<const volatile int *>(A.flags + FLAG_DONE)) return;

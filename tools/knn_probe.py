@@ -1,7 +1,6 @@
 """Measurement aid: where does the time of a kNN-support solve go?  Times, with CUDA events on one GPU at
 n = 1e6 / k = 20, (a) the resident solver (ShardedKNNSolver in its one-launch single-GPU mode) and (b) the
 one-shot C-ABI call for several iteration counts -- per-iteration time must not depend on the count.
-GL_KNN_VARIANT in the environment selects the sweep kernel's batch depth / register budget.
 
     python tools/knn_probe.py [n] [k]
 """
@@ -25,7 +24,7 @@ def main():
     z = d2 * theta_from_knn(d2l, 10)
     keys = locality_keys(x)
     nnz = z.numel()
-    out = {"n": n, "k": k, "edges": nnz, "variant": os.environ.get("GL_KNN_VARIANT", "0"), "resident_ms_per_it": {},
+    out = {"n": n, "k": k, "edges": nnz, "resident_ms_per_it": {},
            "oneshot_ms": {}}
     sv = ShardedKNNSolver(ei, ej, z, n, dtype=torch.float32, order_key=keys)
     for its in (100, 100, 300, 900, 2000):
