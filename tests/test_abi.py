@@ -82,3 +82,24 @@ def test_errors_without_device(nat):
     with pytest.raises(nat.GLError):
         nat.check(nat.GL_E_ARG)
     assert lib.gl_shard_tiles(100, 3, 2, None, None) == nat.GL_E_ARG
+    # a batch cannot be tile-sharded (shared spectral stop rule): refused before any allocation
+    assert lib.gl_solver_create(ctypes.byref(h), 300, 4, 0, 0, 2) == nat.GL_E_ARG
+    assert b"cannot be tile-sharded" in lib.gl_last_error()
+
+
+def test_theta_noalloc_limit_without_device(nat):
+    """The allocation-free theta entry point refuses sizes beyond its static scratch before touching the device;
+    the limit in the message is the header's GL_THETA_NOALLOC_MAX_NODES."""
+    lib = nat.lib()
+    src = open(os.path.join(ROOT, "include", "gl_b200.h")).read()
+    limit = int(re.search(r"#define\s+GL_THETA_NOALLOC_MAX_NODES\s+(\d+)", src).group(1))
+    th = ctypes.c_double(-1.0)
+    dummy = ctypes.c_void_p(256)       # never dereferenced: the checks come first
+    rc = lib.gl_theta_noalloc(dummy, nat.LAYOUT_PACKED, limit + 1, 3, nat.GL_F32, ctypes.byref(th), None)
+    assert rc == nat.GL_E_SHAPE and f"at most {limit} nodes".encode() in lib.gl_last_error()
+    assert lib.gl_theta_noalloc(dummy, 99, 100, 3, nat.GL_F32, ctypes.byref(th), None) == nat.GL_E_ARG
+    assert lib.gl_theta_noalloc(dummy, nat.LAYOUT_PACKED, 1, 3, nat.GL_F32, ctypes.byref(th), None) == nat.GL_E_SHAPE
+    assert lib.gl_theta_noalloc(dummy, nat.LAYOUT_PACKED, 100, 100, nat.GL_F32, ctypes.byref(th), None) == nat.GL_E_ARG
+    assert lib.gl_theta_noalloc(None, nat.LAYOUT_PACKED, 100, 3, nat.GL_F32, ctypes.byref(th), None) == nat.GL_E_ARG
+    assert lib.gl_theta_noalloc(dummy, nat.LAYOUT_PACKED, 100, 3, 9, ctypes.byref(th), None) == nat.GL_E_ARG
+    assert th.value == -1.0
