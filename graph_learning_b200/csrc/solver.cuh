@@ -40,7 +40,7 @@ struct gl_solver {
   int device = 0;
 
   // edge state (edge dtype), [K][ntl*TT]
-  void *w = nullptr, *z = nullptr, *r = nullptr /* K>1 only: q - y of the last pass */;
+  void *w = nullptr, *z = nullptr, *r = nullptr /* K>1 only: second iterate buffer of the resident batched kernel; q - y of the last pass on the per-iteration path */;
   int2 *tile_ij = nullptr;  // [ntl] global (I, J) of each local tile
   // node state
   double *d = nullptr, *yb = nullptr, *pb = nullptr, *rb = nullptr;  // [K][npad]
